@@ -1,0 +1,322 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the approx-FP8 hot path (BASELINE.json configs[1]):
+single QCustomLinearTorch 4096x4096 (4096 rows), approx_v9 with withComp / with_approx /
+with_s2nn2s_opt / quant_btw_mult_accu, metric approx-FP8 GMAC/s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mant-width M]
+
+One "step" = one pass of the hot path (operand predecode + approx GEMM) over one batch of synthetic
+activations.  `value` is timed with the operands resident in HBM; `e2e` goes through the operator
+class (QCustomLinearTorch.forward: activation fake-quant, weight fake-quant, approx GEMM, bias) with
+pinned HOST input and output buffers, copies inside the timed region.
+`--impl reference` times the CPU restatement of the reference (oracle port, all host threads) on a
+bounded column sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ROWS = K_DIM = N_DIM = 4096
+ALG_INT_OPS_PER_MAC = 8          # SURVEY.md 8(d) convention
+SEED = 10                        # scripts/image_net.sh:4
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mant-width", type=int, default=3)
+    ap.add_argument("--rows", type=int, default=ROWS)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sweep", action="store_true", help="also report mant_width 2..5 and the qamaa mode")
+    return ap.parse_args()
+
+
+def approx_params(M):
+    return dict(expo_width=7 - M, mant_width=M, dnsmp_factor=3, withComp=True, with_approx=True,
+                with_s2nn2s_opt=True, sim_hw_add_OFUF=False, with_OF_opt=False, with_UF_opt=False,
+                golden_clip_OF=False, quant_btw_mult_accu=True, debug_mode=False, self_check_mode=False)
+
+
+def host_inputs(rows, M):
+    """Synthetic operands: x = randn*0.5, W = randn*0.02, seed 10."""
+    import torch
+    g = torch.Generator().manual_seed(SEED)
+    x = torch.randn(rows, K_DIM, generator=g) * 0.5
+    w = torch.randn(N_DIM, K_DIM, generator=g) * 0.02
+    b = torch.randn(N_DIM, generator=g) * 0.01
+    return x, w, b
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i].startswith("Active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_port_rate(rows, M, target_s, x_q, w_q, bA, bB, bR):
+    """Times the oracle port (CPU restatement of the reference) on a column sample; returns MAC/s."""
+    import numpy as np
+    from oracle import oracle as orc
+    T = orc.get_error_table_NN(7 - M, M, True, 3)
+    kw = dict(E=7 - M, M=M, with_approx=1, with_s2nn2s_opt=1, quant_btw_mult_accu=1)
+    A = np.ascontiguousarray(x_q[:rows])
+
+    def run(ncols):
+        B = np.ascontiguousarray(w_q[:ncols].T)
+        t = time.perf_counter()
+        orc.approx_matmul(A, B, T, bA, bB[:ncols], bR, **kw)
+        return time.perf_counter() - t
+
+    t1 = run(2)
+    ncols = int(max(2, min(N_DIM, round(2 * target_s / max(t1, 1e-6)))))
+    dt = run(ncols)
+    return rows * K_DIM * ncols / dt, ncols, dt, orc.num_threads()
+
+
+def build_layer(M, device, w, b):
+    """The reference-facing plugin: QCustomLinearTorch with the flags of scripts/image_net.sh
+    (--fp8-set-maxval --per-channel --quantize-input, act allminmax / weight current_minmax)."""
+    import torch
+    from fp8_quantization_b200.approx_calculation import QCustomLinearTorch
+    layer = QCustomLinearTorch(
+        K_DIM, N_DIM, bias=True, method="fp_quantizer", act_method="fp_quantizer",
+        weight_range_method="current_minmax", act_range_method="allminmax", n_bits=8, n_bits_act=8,
+        per_channel_weights=True, quantize_input=True,
+        fp8_kwargs=dict(mantissa_bits=M, set_maxval=True),
+        custom_approx_params=approx_params(M),
+        run_method=dict(approx_flag=True, quantize_after_mult_and_add=False, res_quantizer_flag=True,
+                        original_quantize_res=False))
+    with torch.no_grad():
+        layer.weight.copy_(w)
+        layer.bias.copy_(b)
+    layer.to(device).eval()
+    layer.quantized()
+    return layer
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import fp8_quantization_b200 as pkg
+    from fp8_quantization_b200 import ops
+    import ctypes
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    M, rows = args.mant_width, args.rows
+    lib = pkg._lib.load()
+
+    x_host, w_host, b_host = host_inputs(rows, M)
+    layer = build_layer(M, dev, w_host, b_host)
+    with torch.inference_mode():
+        # calibration pass (estimate_ranges) then fixed ranges
+        layer.estimate_ranges()
+        x_dev = x_host.to(dev)
+        layer(x_dev)
+        layer.fix_ranges()
+        # operands of the hot path, resident in HBM
+        xq = layer.activation_quantizer(x_dev)
+        wq, _ = layer.get_params()
+        bA, bB, bR = layer.get_acts_fp_bias(), layer.get_weights_fp_bias(), layer.get_res_fp_bias()
+        params = ops.make_params(approx_params(M))
+        out = torch.empty((rows, N_DIM), device=dev, dtype=torch.float32)
+
+        def step():
+            ops.approx_matmul(xq, wq.t(), bA, bB, bR, params, out=out)
+
+        for _ in range(max(args.warmup, 3)):
+            step()
+        torch.cuda.synchronize()
+        path = ops.last_path()
+        macs = rows * K_DIM * N_DIM
+
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        l0 = ops.kernel_launches()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        launches = ops.kernel_launches() - l0
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.barrier()
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        clocks = sampler.stop() if rank == 0 else None
+        total_ms = float(ms.item())
+        value = world * args.steps * macs / (total_ms * 1e-3) / 1e9
+
+        # roofline leg: the dominant kernel (approx_gemm_lut_kernel) alone, CUDA events on its stream
+        lib.b200_profile_begin()
+        for _ in range(args.steps):
+            step()
+        tot, cnt = ctypes.c_double(0), ctypes.c_int(0)
+        lib.b200_profile_end(ctypes.byref(tot), ctypes.byref(cnt))
+        kern_ms = tot.value / max(cnt.value, 1)
+        tiops, pms = ctypes.c_double(0), ctypes.c_double(0)
+        lib.b200_int_peak_probe(4000, ctypes.byref(tiops), ctypes.byref(pms))
+        achieved = ALG_INT_OPS_PER_MAC * macs / (kern_ms * 1e-3) / 1e12 if kern_ms > 0 else 0.0
+
+        # e2e: through QCustomLinearTorch.forward with pinned HOST buffers, copies inside the timed region
+        x_pin = x_host.pin_memory()
+        y_pin = torch.empty((rows, N_DIM), dtype=torch.float32).pin_memory()
+
+        def e2e_step():
+            xd = x_pin.to(dev, non_blocking=True)
+            y = layer(xd)
+            y_pin.copy_(y, non_blocking=True)
+
+        for _ in range(3):
+            e2e_step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0.record()
+        for _ in range(args.steps):
+            e2e_step()
+        e1.record()
+        torch.cuda.synchronize()
+        ems = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ems, op=dist.ReduceOp.MAX)
+        e2e_value = world * args.steps * macs / (float(ems.item()) * 1e-3) / 1e9
+        checksum = float(y_pin.double().sum())
+
+    line = {
+        "metric": "approx_fp8_gmacs", "value": round(value, 2), "unit": "GMAC/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(total_ms / args.steps, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32-sim-of-fp8 (int fields)",
+        "data": "synthetic", "impl": "ours",
+        "config": {"workload": f"QCustomLinearTorch {rows}x{K_DIM}x{N_DIM} approx_v9 E{7 - M}M{M} "
+                               "withComp with_approx with_s2nn2s_opt quant_btw_mult_accu (BASELINE configs[1])",
+                   "rows_per_gpu": rows, "K": K_DIM, "N": N_DIM, "mant_width": M, "expo_width": 7 - M,
+                   "kernel_path": path, "l2": "operands+workspace 320 MB per step > 126 MB L2, no flush needed",
+                   "parallelism": f"replicated weights, rows sharded x{world}"},
+        "per_gpu": round(value / world, 2),
+        "e2e": {"value": round(e2e_value, 2), "unit": "GMAC/s", "h2d_bytes_per_step": rows * K_DIM * 4,
+                "d2h_bytes_per_step": rows * N_DIM * 4, "through": "QCustomLinearTorch.forward (fake-quant x, "
+                "fake-quant W, approx GEMM, +bias), pinned host in/out", "checksum": checksum},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "int-issue", "achieved": round(achieved, 3), "peak": round(tiops.value, 3),
+                     "unit": "Tiop/s", "frac": round(achieved / tiops.value, 4) if tiops.value else None,
+                     "traffic": None, "kernel": "approx_gemm_lut_kernel", "kernel_ms": round(kern_ms, 4),
+                     "alg_ops_per_mac": ALG_INT_OPS_PER_MAC,
+                     "peak_source": "measured live: IADD/LOP3 saturation kernel (b200_int_peak_probe); not in MEASURED_PEAKS.json",
+                     "kernel_gmacs": round(macs / (kern_ms * 1e-3) / 1e9, 1) if kern_ms > 0 else None},
+        "clocks": clocks,
+    }
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            rate, ncols, dt, thr = cpu_port_rate(rows, M, 12.0, xq.cpu().numpy(), wq.cpu().numpy(),
+                                                 int(bA.item()), bB.reshape(-1).to(torch.int32).cpu().numpy(),
+                                                 int(bR.item()))
+            line["cpu_baseline"] = {"value": round(rate / 1e9, 5), "unit": "GMAC/s", "cores": thr, "kind": "port",
+                                    "sample": f"{rows} rows x K={K_DIM} x {ncols} of {N_DIM} output columns, "
+                                              f"{dt:.1f} s (columns are independent and equal-cost)"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    """The reference's own algorithm on the host cores (oracle port; the Python reference cannot
+    travel to the GPU box).  Each step = a bounded column sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import numpy as np
+    from oracle import oracle as orc
+    M, rows = args.mant_width, args.rows
+    x, w, _ = host_inputs(rows, M)
+    x, w = x.numpy(), w.numpy()
+    xq, bA = orc.fp8_fakequant(x, [np.abs(x).max()], 8, float(M), 1)
+    ncols = 8
+    wq, bB = orc.fp8_fakequant(w[:ncols], np.abs(w[:ncols]).max(axis=1), 8, float(M), 1)
+    bR = int(bA[0]) + int(bB.max()) - 2 ** (7 - M) - 3
+    T = orc.get_error_table_NN(7 - M, M, True, 3)
+    kw = dict(E=7 - M, M=M, with_approx=1, with_s2nn2s_opt=1, quant_btw_mult_accu=1)
+    B = np.ascontiguousarray(wq.T)
+    # keep the whole run within minutes: shrink rows if one step would take > ~6 s
+    t = time.perf_counter()
+    orc.approx_matmul(xq[:256], B, T, int(bA[0]), bB.astype(np.int32), bR, **kw)
+    est = (time.perf_counter() - t) * rows / 256
+    r = rows if est < 6 else max(256, int(rows * 6 / est) // 256 * 256)
+    A = np.ascontiguousarray(xq[:r])
+    for _ in range(args.warmup):
+        orc.approx_matmul(A, B, T, int(bA[0]), bB.astype(np.int32), bR, **kw)
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        orc.approx_matmul(A, B, T, int(bA[0]), bB.astype(np.int32), bR, **kw)
+    dt = time.perf_counter() - t
+    macs = r * K_DIM * ncols
+    value = args.steps * macs / dt / 1e9
+    thr = orc.num_threads()
+    sample = f"{r} rows x K={K_DIM} x {ncols} of {N_DIM} output columns per step"
+    print(json.dumps({
+        "impl": "reference", "metric": "approx_fp8_gmacs", "value": round(value, 5), "unit": "GMAC/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 2),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32-sim-of-fp8 (int fields)",
+        "data": "synthetic",
+        "config": {"workload": f"QCustomLinearTorch {rows}x{K_DIM}x{N_DIM} approx_v9 E{7 - M}M{M} "
+                               "withComp with_approx with_s2nn2s_opt quant_btw_mult_accu (BASELINE configs[1])",
+                   "mant_width": M, "expo_width": 7 - M, "sample": sample},
+        "cpu_baseline": {"value": round(value, 5), "unit": "GMAC/s", "cores": thr, "kind": "port", "sample": sample},
+        "e2e": {"value": round(value, 5), "unit": "GMAC/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

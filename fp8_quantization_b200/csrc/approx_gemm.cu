@@ -1,0 +1,630 @@
+// approx_gemm.cu -- K1: the approx_v9 simulated-FP8 GEMM.
+//
+// Replaces the per-column Python loop approx/approx_calculation.py:946-971 (Linear) / :774-799
+// (BN-conv) over custom_matmul_vectorize (approx/approx_matmul_whole_v9.py:10-169).
+//
+// Two kernels implement the same function:
+//   * approx_gemm_generic_kernel : evaluates pair_generic() (pair_math.cuh) per operand pair; valid
+//     for ANY fp32 operands and every flag combination, including the single-column tensor-bias
+//     quirk.  Slow (tens of fp32/int ops per pair); it is the fallback and the definition.
+//   * approx_gemm_lut_kernel     : table-driven register-blocked CUDA-core tile for the main mode
+//     (with_s2nn2s_opt && quant_btw_mult_accu) when every operand lies on the FP8 grid, which is
+//     what the fake-quantizer guarantees (lut.cuh).  Per pair: IADD, LDS.U16, shift, FFMA.
+// The choice between them is made ON THE DEVICE (no host sync): the predecode kernels raise a flag
+// if any operand is off-grid; both GEMM kernels are enqueued and the wrong one exits at once.
+//
+// Accumulation: fp32, k ascending, one thread owns an output element for the whole K loop -- the
+// same order as the oracle, hence bit-identical to it; identical to the reference whenever fp32
+// summation is exact (always, in the calibrated quant_btw_mult_accu regime: DESIGN.md).
+#include <map>
+#include <mutex>
+#include <tuple>
+#include <vector>
+
+#include "common.cuh"
+#include "lut.cuh"
+#include "pair_math.cuh"
+#include "tables.h"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------
+// Pair-table builder: one thread per table cell, evaluating the reference op chain in "unit" space
+// (value / u, i.e. with result bias 1-M so that u == 1).
+// ------------------------------------------------------------------------------------------------
+// Exponent biases either come from the host (python ints) or stay on the device as the fp32 tensors
+// the fake-quantizer produced (FPQuantizer.custom_bias): no .item() sync on the hot path.
+struct BiasSrc {
+    int bA, bR;             // used when fA / fR are null
+    const float* fA;        // device [1] or null
+    const float* fR;        // device [1] or null
+    const int32_t* iB;      // device [N] int32, or null
+    const float* fB;        // device fp32, element n at fB[n * sB] (cast like .to(torch.int32))
+    int64_t sB;
+    __device__ __forceinline__ int A() const { return fA ? (int)__ldg(fA) : bA; }
+    __device__ __forceinline__ int R() const { return fR ? (int)__ldg(fR) : bR; }
+    __device__ __forceinline__ int B(int64_t n) const { return iB ? __ldg(iB + n) : (int)__ldg(fB + n * sB); }
+};
+
+struct LutFlags {
+    int sign_quirk;        // cells where F is not odd in the operand sign (v9 :68 after :36)
+    int unrepresentable;   // cells whose value does not fit bf16 exactly
+};
+
+__global__ void lut_build_kernel(LutGeom g, const signed char* __restrict__ T, int has_table, int with_approx,
+                                 int clip_OF, uint16_t* __restrict__ lut, LutFlags* __restrict__ flags)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= g.total_entries) return;
+    uint16_t out = 0;
+    if (idx < g.zeroA_off) {
+        const int M = g.M;
+        const int mB = idx & ((1 << M) - 1);
+        const int sb = (idx >> M) & 1;
+        const int row = idx / g.row_entries;
+        const int idx_t = row % g.NT;
+        const int mA = row / g.NT;
+        const int t = idx_t - g.RA - M - 2;
+        if (idx_t > g.RA) {
+            const FmtParam pR = make_param(g.E, M, 1 - M, false);   // unit space: u = 2^(1-bias-M) = 1
+            const float s = ldexpf(1.0f, -M);
+            const float pex = (1.0f + (float)mA * s) * (1.0f + (float)mB * s);
+            const float p = has_table ? mult_mant(M, mA, mB, T, with_approx != 0)
+                                      : mult_mant<signed char>(M, mA, mB, nullptr, false);
+            const float scale = pow2f_i(t + M - 1);
+            float val[2];
+#pragma unroll
+            for (int sa = 0; sa < 2; ++sa) {
+                const float sg = ((sa ^ sb) & 1) ? -1.0f : 1.0f;
+                float gq = pex * scale * sg;                       // golden product, exact
+                gq = fpany_quant(pR, gq, clip_OF != 0);            // v9 :36
+                const float sgn = (gq < 0.0f) ? -1.0f : 1.0f;      // v9 :68
+                float r = scale * p * sgn;                         // v9 :73-77 (+ :79-80 folded in t)
+                val[sa] = fpany_quant(pR, r, clip_OF != 0);        // v9 :108
+            }
+            if (val[1] != -val[0]) atomicAdd(&flags->sign_quirk, 1);
+            const uint32_t bits = __float_as_uint(val[0]);
+            if (bits & 0xFFFFu) atomicAdd(&flags->unrepresentable, 1);
+            out = (uint16_t)(bits >> 16);
+        }
+    }
+    lut[idx] = out;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Operand predecode: fp32 -> packed table offsets, transposed to [K][rows] so that the GEMM reads
+// 128-bit vectors of consecutive rows/columns.  HBM-bound, one pass.
+// ------------------------------------------------------------------------------------------------
+struct PredecodeArgs {
+    const float* src;
+    int64_t s_row, s_k;    // element (row, k) at src[row*s_row + k*s_k]   (row = m for A, n for B)
+    uint32_t* dst;         // [Kpad][Rpad]
+    int64_t rows, K, Rpad, Kpad;
+    int M;
+    BiasSrc bias;
+    int* offgrid;          // raised if any element cannot take the table path
+};
+
+__device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int bA, int& off)
+{
+    const uint32_t bits = __float_as_uint(v);
+    const uint32_t mag = bits & 0x7FFFFFFFu;
+    if (mag == 0) return 2u * (uint32_t)g.zeroA_off;
+    const int M = g.M;
+    const int L = (int)(mag >> 23) - 127;
+    const uint32_t frac = mag & 0x7FFFFFu;
+    const int LA_lo = 1 - bA - M;
+    const int tA = L - LA_lo;
+    // on grid: <= M fractional bits, at least min_subnorm, not above the top binade, finite/normal fp32
+    if ((frac & ((1u << (23 - M)) - 1u)) != 0 || tA < 0 || tA > g.RA || (mag >> 23) == 0 || (mag >> 23) == 255) {
+        off = 1;
+        return 2u * (uint32_t)g.zeroA_off;
+    }
+    const uint32_t mA = frac >> (23 - M);
+    return (bits & kSignBit) | (2u * (uint32_t)(g.row_entries * (tA + g.NT * (int)mA)));
+}
+
+__device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int bA, int bB, int bR, int& off)
+{
+    const uint32_t bits = __float_as_uint(v);
+    const uint32_t mag = bits & 0x7FFFFFFFu;
+    if (mag == 0) return 0u;                                  // tB_idx = 0: every product rounds to 0
+    const int M = g.M;
+    const int L = (int)(mag >> 23) - 127;
+    const uint32_t frac = mag & 0x7FFFFFu;
+    int tB = L + bR - bA + 3;                                 // (t + M + 2) - tA_idx
+    if ((frac & ((1u << (23 - M)) - 1u)) != 0 || L < 1 - bB - M || (mag >> 23) == 0 || (mag >> 23) == 255 ||
+        tB + g.RA > g.NTB - 1 || (1 - bA - M) + (1 - bB - M) < -120) {
+        off = 1;
+        return 0u;
+    }
+    if (tB < -g.RA) tB = -g.RA;
+    const uint32_t mB = frac >> (23 - M);
+    const uint32_t sb = bits >> 31;
+    return 2u * (mB + (sb << M) + (uint32_t)(g.row_entries * (tB + g.RA)));
+}
+
+// 32x32 tile transpose: reads along k (SRC_K_CONTIG) or along rows, writes along rows.
+template <bool IS_B, bool SRC_K_CONTIG>
+__global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom g)
+{
+    __shared__ uint32_t tile[32][33];
+    const int64_t r0 = (int64_t)blockIdx.x * 32, k0 = (int64_t)blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+    int off = 0;
+    const int bA = a.bias.A(), bR = a.bias.R();
+    if (bA <= -64 || bA >= 64 || bR <= -64 || bR >= 64) off = 1;
+    if (SRC_K_CONTIG) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int64_t r = r0 + ty + i * 8, k = k0 + tx;
+            uint32_t w = IS_B ? 0u : 2u * (uint32_t)g.zeroA_off;
+            if (r < a.rows && k < a.K) {
+                const float v = a.src[r * a.s_row + k * a.s_k];
+                w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off) : predecode_a(g, v, bA, off);
+            }
+            tile[tx][ty + i * 8] = w;   // [k][r]
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int64_t k = k0 + ty + i * 8, r = r0 + tx;
+            if (k < a.Kpad && r < a.Rpad) a.dst[k * a.Rpad + r] = tile[ty + i * 8][tx];
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int64_t k = k0 + ty + i * 8, r = r0 + tx;
+            uint32_t w = IS_B ? 0u : 2u * (uint32_t)g.zeroA_off;
+            if (r < a.rows && k < a.K) {
+                const float v = a.src[r * a.s_row + k * a.s_k];
+                w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off) : predecode_a(g, v, bA, off);
+            }
+            if (k < a.Kpad && r < a.Rpad) a.dst[k * a.Rpad + r] = w;
+        }
+    }
+    if (off) *a.offgrid = 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Table-driven GEMM.  CTA tile (16*WARPS) x 128, one warp = 16 rows x 128 columns, one lane =
+// 16 rows x 4 consecutive columns (64 fp32 accumulators).  For a fixed k all lanes of a warp use the
+// same 16 A words (broadcast LDS.128) and their own 4 B words (one conflict-free LDS.128).
+// Operand tiles are staged through a 3-deep cp.async ring; the pair table lives in shared memory for
+// the life of the CTA.
+// ------------------------------------------------------------------------------------------------
+constexpr int LUT_BN = 128;
+constexpr int LUT_KT = 16;
+constexpr int LUT_STAGES = 3;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr)
+{
+    uint32_t v;
+    asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+struct LutGemmArgs {
+    const uint32_t* Aw;   // [Kpad][Mpad]
+    const uint32_t* Bw;   // [Kpad][Npad]
+    const uint16_t* lut;  // total_entries (padded to 16 B)
+    float* C;
+    int64_t ldc, Mrows, N, Mpad, Npad;
+    int Kpad;
+    int lut_bytes;        // multiple of 16
+    BiasSrc bias;
+    int M;                // unit u = 2^(1 - bR - M)
+    const int* offgrid;
+};
+
+template <int WARPS>
+__global__ void __launch_bounds__(32 * WARPS, (WARPS == 8) ? 2 : 1) approx_gemm_lut_kernel(LutGemmArgs a)
+{
+    constexpr int BM = 16 * WARPS, BN = LUT_BN, KT = LUT_KT, ST = LUT_STAGES, NTHR = 32 * WARPS;
+    if (*a.offgrid != 0) return;   // some operand is off the FP8 grid: the generic kernel takes over
+    extern __shared__ __align__(16) unsigned char smem[];
+    uint32_t* As = reinterpret_cast<uint32_t*>(smem + a.lut_bytes);   // [ST][KT][BM]
+    uint32_t* Bs = As + ST * KT * BM;                                 // [ST][KT][BN]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t m0 = (int64_t)blockIdx.x * BM, n0 = (int64_t)blockIdx.y * BN;
+
+    // pair table -> shared memory
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(a.lut);
+        uint4* dst = reinterpret_cast<uint4*>(smem);
+        for (int i = tid; i < a.lut_bytes / 16; i += NTHR) dst[i] = __ldg(src + i);
+    }
+    const uint32_t lut_base = smem_u32(smem);
+    const uint32_t As_u = smem_u32(As), Bs_u = smem_u32(Bs);
+
+    auto load_tile = [&](int kt, int stage) {
+        const uint32_t* ga = a.Aw + (int64_t)kt * KT * a.Mpad + m0;
+        const uint32_t* gb = a.Bw + (int64_t)kt * KT * a.Npad + n0;
+#pragma unroll
+        for (int i = tid; i < KT * BM / 4; i += NTHR) {
+            const int r = i / (BM / 4), c = i % (BM / 4);
+            cp_async16(As_u + 4u * (uint32_t)((stage * KT + r) * BM + c * 4), ga + (int64_t)r * a.Mpad + c * 4);
+        }
+#pragma unroll
+        for (int i = tid; i < KT * BN / 4; i += NTHR) {
+            const int r = i / (BN / 4), c = i % (BN / 4);
+            cp_async16(Bs_u + 4u * (uint32_t)((stage * KT + r) * BN + c * 4), gb + (int64_t)r * a.Npad + c * 4);
+        }
+    };
+
+    float acc[16][4];
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+
+    const int nk = a.Kpad / KT;
+#pragma unroll
+    for (int s = 0; s < ST - 1; ++s) {
+        if (s < nk) load_tile(s, s);
+        cp_async_commit();
+    }
+    for (int kt = 0; kt < nk; ++kt) {
+        cp_async_wait<ST - 2>();
+        __syncthreads();
+        if (kt + ST - 1 < nk) load_tile(kt + ST - 1, (kt + ST - 1) % ST);
+        cp_async_commit();
+        const uint32_t* Asm = As + (kt % ST) * KT * BM + warp * 16;
+        const uint32_t* Bsm = Bs + (kt % ST) * KT * BN + lane * 4;
+#pragma unroll 4
+        for (int kk = 0; kk < KT; ++kk) {
+            const uint4 bq = *reinterpret_cast<const uint4*>(Bsm + kk * BN);
+            const uint32_t bw[4] = {bq.x + lut_base, bq.y + lut_base, bq.z + lut_base, bq.w + lut_base};
+#pragma unroll
+            for (int i4 = 0; i4 < 4; ++i4) {
+                const uint4 aq = *reinterpret_cast<const uint4*>(Asm + kk * BM + i4 * 4);
+                const uint32_t aw[4] = {aq.x, aq.y, aq.z, aq.w};
+#pragma unroll
+                for (int ii = 0; ii < 4; ++ii) {
+                    const float sa = __uint_as_float((aw[ii] & kSignBit) | 0x3F800000u);
+                    const uint32_t ao = aw[ii] & ~kSignBit;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint32_t e = lds_u16(ao + bw[j]);
+                        acc[i4 * 4 + ii][j] = __fmaf_rn(__uint_as_float(e << 16), sa, acc[i4 * 4 + ii][j]);
+                    }
+                }
+            }
+        }
+    }
+    cp_async_wait<0>();
+
+    // epilogue: C = acc * u (exact power-of-two scaling)
+    const float unit = pow2f_i(1 - a.bias.R() - a.M);
+    const int64_t n = n0 + lane * 4;
+    const bool vec = ((a.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.C) & 15) == 0) && (n + 3 < a.N);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const int64_t m = m0 + warp * 16 + i;
+        if (m >= a.Mrows) break;
+        float* crow = a.C + m * a.ldc;
+        if (vec) {
+            *reinterpret_cast<float4*>(crow + n) =
+                make_float4(acc[i][0] * unit, acc[i][1] * unit, acc[i][2] * unit, acc[i][3] * unit);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (n + j < a.N) crow[n + j] = acc[i][j] * unit;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Generic kernel: one thread per output element, pair_generic() per operand pair.
+// ------------------------------------------------------------------------------------------------
+struct GenericArgs {
+    const float* A;
+    int64_t lda;
+    const float* B;
+    int64_t sb_k, sb_n;
+    float* C;
+    int64_t ldc, Mrows, K, N;
+    BiasSrc bias;
+    PairCfg cfg;
+    const signed char* T;   // device table (4^M int8) or nullptr (= zeros)
+    const int* offgrid;     // nullptr: always run; else run only if *offgrid != 0
+};
+
+__global__ void __launch_bounds__(256) approx_gemm_generic_kernel(GenericArgs a)
+{
+    if (a.offgrid && *a.offgrid == 0) return;
+    __shared__ float As[8][33];
+    __shared__ float Bs[32][33];
+    __shared__ signed char Ts[1024];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int tsize = (1 << a.cfg.M) * (1 << a.cfg.M);
+    for (int i = threadIdx.x; i < tsize; i += 256) Ts[i] = a.T ? a.T[i] : (signed char)0;
+    const int64_t n = (int64_t)blockIdx.y * 32 + tx, m = (int64_t)blockIdx.x * 8 + ty;
+    const int bBn = (n < a.N) ? a.bias.B(n) : 0;
+    const FmtParam pA = make_param(a.cfg.E, a.cfg.M, a.bias.A(), a.cfg.quirk);
+    const FmtParam pB = make_param(a.cfg.E, a.cfg.M, bBn, a.cfg.quirk);
+    const FmtParam pR = make_param(a.cfg.E, a.cfg.M, a.bias.R(), a.cfg.quirk);
+    float acc = 0.0f;
+    for (int64_t k0 = 0; k0 < a.K; k0 += 32) {
+        __syncthreads();
+        {
+            const int64_t mm = (int64_t)blockIdx.x * 8 + ty, kk = k0 + tx;
+            As[ty][tx] = (mm < a.Mrows && kk < a.K) ? a.A[mm * a.lda + kk] : 0.0f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int64_t kb = k0 + ty + i * 8, nn = (int64_t)blockIdx.y * 32 + tx;
+                Bs[ty + i * 8][tx] = (kb < a.K && nn < a.N) ? a.B[kb * a.sb_k + nn * a.sb_n] : 0.0f;
+            }
+        }
+        __syncthreads();
+        const int kmax = (int)((a.K - k0 < 32) ? (a.K - k0) : 32);
+        if (m < a.Mrows && n < a.N)
+            for (int kk = 0; kk < kmax; ++kk)
+                acc += pair_generic(a.cfg, pA, pB, pR, Ts, As[ty][kk], Bs[kk][tx]);
+    }
+    if (m < a.Mrows && n < a.N) a.C[m * a.ldc + n] = acc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host side: table cache, dispatch, C ABI.
+// ------------------------------------------------------------------------------------------------
+struct LutEntry {
+    LutGeom geom;
+    uint16_t* d_lut = nullptr;
+    int lut_bytes = 0;
+    LutFlags flags{0, 0};
+};
+
+static std::mutex g_cache_mu;
+static std::map<std::tuple<int, const void*>, signed char*> g_dev_tables;            // (device, host table) -> device copy
+static std::map<std::tuple<int, int, int, const void*, int, int>, LutEntry> g_luts;   // (device,E,M,table,with_approx,clip)
+
+static int device_table(const signed char* host, int M, const signed char** dev_out)
+{
+    *dev_out = nullptr;
+    if (!host) return B200_OK;
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    auto key = std::make_tuple(dev, (const void*)host);
+    auto it = g_dev_tables.find(key);
+    if (it == g_dev_tables.end()) {
+        signed char* d = nullptr;
+        const size_t n = (size_t)(1 << M) * (1 << M);
+        B200_CUDA_TRY(cudaMalloc(&d, n));
+        B200_CUDA_TRY(cudaMemcpy(d, host, n, cudaMemcpyHostToDevice));
+        it = g_dev_tables.emplace(key, d).first;
+    }
+    *dev_out = it->second;
+    return B200_OK;
+}
+
+// Builds (once per configuration and device) the pair table of lut.cuh.  First use synchronises.
+static int get_lut(int E, int M, const signed char* host_table, const signed char* dev_table, int with_approx,
+                   int clip_OF, const LutEntry** out)
+{
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    auto key = std::make_tuple(dev, E, M, (const void*)host_table, with_approx, clip_OF);
+    auto it = g_luts.find(key);
+    if (it == g_luts.end()) {
+        LutEntry e;
+        e.geom = make_lut_geom(E, M);
+        e.lut_bytes = (int)round_up((int64_t)e.geom.total_entries * 2, 16);
+        LutFlags* d_flags = nullptr;
+        B200_CUDA_TRY(cudaMalloc(&e.d_lut, e.lut_bytes));
+        B200_CUDA_TRY(cudaMalloc(&d_flags, sizeof(LutFlags)));
+        B200_CUDA_TRY(cudaMemset(e.d_lut, 0, e.lut_bytes));
+        B200_CUDA_TRY(cudaMemset(d_flags, 0, sizeof(LutFlags)));
+        lut_build_kernel<<<(int)ceil_div(e.geom.total_entries, 256), 256>>>(e.geom, dev_table, dev_table != nullptr,
+                                                                           with_approx, clip_OF, e.d_lut, d_flags);
+        B200_LAUNCH_CHECK("lut_build_kernel");
+        B200_CUDA_TRY(cudaMemcpy(&e.flags, d_flags, sizeof(LutFlags), cudaMemcpyDeviceToHost));
+        cudaFree(d_flags);
+        it = g_luts.emplace(key, e).first;
+    }
+    *out = &it->second;
+    return B200_OK;
+}
+
+static size_t lut_gemm_smem(int warps, int lut_bytes)
+{
+    return (size_t)lut_bytes + (size_t)LUT_STAGES * LUT_KT * (16 * warps + LUT_BN) * 4;
+}
+
+// Optional per-launch timing of the dominant kernel (bench.py's roofline leg): CUDA events recorded
+// on the launching stream right around the table GEMM.
+static std::mutex g_prof_mu;
+static bool g_prof_on = false;
+static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_prof_events;
+
+static void prof_record(bool start, cudaStream_t st)
+{
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (!g_prof_on) return;
+    if (start) {
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        g_prof_events.emplace_back(e0, e1);
+        cudaEventRecord(e0, st);
+    } else if (!g_prof_events.empty()) {
+        cudaEventRecord(g_prof_events.back().second, st);
+    }
+}
+
+constexpr int64_t kPadM = 256, kPadN = LUT_BN, kPadK = 32;
+constexpr size_t kFlagBytes = 256;
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" size_t b200_approx_gemm_workspace_bytes(int64_t Mrows, int64_t K, int64_t N)
+{
+    if (Mrows < 0 || K < 0 || N < 0) return 0;
+    const int64_t Mpad = round_up(Mrows > 0 ? Mrows : 1, kPadM), Npad = round_up(N > 0 ? N : 1, kPadN);
+    const int64_t Kpad = round_up(K > 0 ? K : 1, kPadK);
+    return kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4;
+}
+
+static int approx_gemm_impl(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, float* C,
+                            int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias,
+                            const b200_approx_params* p, void* workspace, size_t workspace_bytes, void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (!p || Mrows < 0 || K < 0 || N < 0) { set_error("b200_approx_gemm: bad argument"); return B200_ERR_ARGUMENT; }
+    const int E = p->expo_width, M = p->mant_width;
+    const signed char* host_table = nullptr;
+    if (p->custom_table) {
+        if (E < 1 || M < 1 || M > 5 || E + M > 7) { set_error("Invalid combination of expo_width and mant_width"); return B200_ERR_INVALID_FORMAT; }
+        host_table = intern_table(reinterpret_cast<const signed char*>(p->custom_table), M);
+    } else if (int rc = select_table(E, M, p->withComp, p->dnsmp_factor, p->allow_unpinned_format, &host_table)) {
+        return rc;
+    }
+    if (Mrows == 0 || N == 0) return B200_OK;
+    if (!A || !B || !C || (!bias.iB && !bias.fB)) { set_error("b200_approx_gemm: NULL operand"); return B200_ERR_ARGUMENT; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const signed char* dev_table = nullptr;
+    if (int rc = device_table(host_table, M, &dev_table)) return rc;
+
+    GenericArgs ga;
+    ga.A = A; ga.lda = lda; ga.B = B; ga.sb_k = sb_k; ga.sb_n = sb_n; ga.C = C; ga.ldc = ldc;
+    ga.Mrows = Mrows; ga.K = K; ga.N = N; ga.bias = bias;
+    ga.cfg.E = E; ga.cfg.M = M;
+    ga.cfg.with_approx = p->with_approx != 0;
+    ga.cfg.s2nn2s = p->with_s2nn2s_opt != 0;
+    ga.cfg.clip_OF = p->golden_clip_OF != 0;
+    ga.cfg.qbma = p->quant_btw_mult_accu != 0;
+    ga.cfg.quirk = p->single_column_quirk != 0;
+    ga.T = (p->with_approx ? dev_table : nullptr);
+    ga.offgrid = nullptr;
+    const dim3 ggrid((unsigned)ceil_div(Mrows, 8), (unsigned)ceil_div(N, 32));
+
+    const bool lut_mode = !p->force_generic && p->with_s2nn2s_opt && p->quant_btw_mult_accu && !p->single_column_quirk && K > 0;
+    const LutEntry* lut = nullptr;
+    if (lut_mode) {
+        if (int rc = get_lut(E, M, p->with_approx ? host_table : nullptr, p->with_approx ? dev_table : nullptr,
+                             p->with_approx != 0, p->golden_clip_OF != 0, &lut))
+            return rc;
+    }
+    if (!lut || lut->flags.sign_quirk || lut->flags.unrepresentable) {
+        approx_gemm_generic_kernel<<<ggrid, 256, 0, st>>>(ga);
+        B200_LAUNCH_CHECK("approx_gemm_generic_kernel");
+        set_path("generic");
+        return B200_OK;
+    }
+
+    const int64_t Mpad = round_up(Mrows, kPadM), Npad = round_up(N, kPadN), Kpad = round_up(K, kPadK);
+    const size_t need = kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4;
+    if (!workspace || workspace_bytes < need) {
+        set_error("b200_approx_gemm: workspace too small (see b200_approx_gemm_workspace_bytes)");
+        return B200_ERR_WORKSPACE;
+    }
+    int* flag = reinterpret_cast<int*>(workspace);
+    uint32_t* Aw = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(workspace) + kFlagBytes);
+    uint32_t* Bw = Aw + (size_t)Kpad * Mpad;
+    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
+
+    PredecodeArgs pa;
+    pa.src = A; pa.s_row = lda; pa.s_k = 1; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad; pa.Kpad = Kpad;
+    pa.M = M; pa.bias = bias; pa.offgrid = flag;
+    predecode_kernel<false, true><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, lut->geom);
+    B200_LAUNCH_CHECK("predecode_kernel<A>");
+    PredecodeArgs pb = pa;
+    pb.src = B; pb.s_row = sb_n; pb.s_k = sb_k; pb.dst = Bw; pb.rows = N; pb.Rpad = Npad;
+    const dim3 pgrid((unsigned)(Npad / 32), (unsigned)(Kpad / 32));
+    if (sb_k == 1 && sb_n != 1) predecode_kernel<true, true><<<pgrid, 256, 0, st>>>(pb, lut->geom);
+    else                        predecode_kernel<true, false><<<pgrid, 256, 0, st>>>(pb, lut->geom);
+    B200_LAUNCH_CHECK("predecode_kernel<B>");
+
+    LutGemmArgs la;
+    la.Aw = Aw; la.Bw = Bw; la.lut = lut->d_lut; la.C = C; la.ldc = ldc; la.Mrows = Mrows; la.N = N;
+    la.Mpad = Mpad; la.Npad = Npad; la.Kpad = (int)Kpad; la.lut_bytes = lut->lut_bytes;
+    la.bias = bias; la.M = M;
+    la.offgrid = flag;
+    prof_record(true, st);
+    const size_t smem8 = lut_gemm_smem(8, lut->lut_bytes);
+    if (2 * (smem8 + 1024) <= 227 * 1024) {
+        static bool attr8 = false;
+        if (!attr8) {
+            B200_CUDA_TRY(cudaFuncSetAttribute(approx_gemm_lut_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
+            attr8 = true;
+        }
+        approx_gemm_lut_kernel<8><<<dim3((unsigned)(Mpad / 128), (unsigned)(Npad / LUT_BN)), 256, smem8, st>>>(la);
+    } else {
+        static bool attr16 = false;
+        if (!attr16) {
+            B200_CUDA_TRY(cudaFuncSetAttribute(approx_gemm_lut_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            attr16 = true;
+        }
+        approx_gemm_lut_kernel<16><<<dim3((unsigned)(Mpad / 256), (unsigned)(Npad / LUT_BN)), 512,
+                                     lut_gemm_smem(16, lut->lut_bytes), st>>>(la);
+    }
+    prof_record(false, st);
+    B200_LAUNCH_CHECK("approx_gemm_lut_kernel");
+    ga.offgrid = flag;   // runs only if the predecode found an off-grid operand
+    approx_gemm_generic_kernel<<<ggrid, 256, 0, st>>>(ga);
+    B200_LAUNCH_CHECK("approx_gemm_generic_kernel(conditional)");
+    set_path("lut");
+    return B200_OK;
+}
+
+extern "C" int b200_approx_gemm(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, float* C,
+                                int64_t ldc, int64_t Mrows, int64_t K, int64_t N, int bA, const int32_t* bB, int bR,
+                                const b200_approx_params* p, void* workspace, size_t workspace_bytes, void* stream)
+{
+    BiasSrc b{bA, bR, nullptr, nullptr, bB, nullptr, 1};
+    return approx_gemm_impl(A, lda, B, sb_k, sb_n, C, ldc, Mrows, K, N, b, p, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200_approx_gemm_fbias(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n,
+                                      float* C, int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float* bA_dev,
+                                      const float* bB_dev, int64_t bB_stride, const float* bR_dev,
+                                      const b200_approx_params* p, void* workspace, size_t workspace_bytes,
+                                      void* stream)
+{
+    if (!p) { set_error("b200_approx_gemm_fbias: params is NULL"); return B200_ERR_ARGUMENT; }
+    const int dflt = 1 << (p->expo_width > 0 ? p->expo_width - 1 : 0);   // approx_calculation.py:938-939
+    BiasSrc b{dflt, dflt, bA_dev, bR_dev, nullptr, bB_dev, bB_stride};
+    return approx_gemm_impl(A, lda, B, sb_k, sb_n, C, ldc, Mrows, K, N, b, p, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200_profile_begin(void)
+{
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    for (auto& e : g_prof_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    g_prof_events.clear();
+    g_prof_on = true;
+    return B200_OK;
+}
+
+extern "C" int b200_profile_end(double* total_ms, int* launches)
+{
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    double tot = 0.0;
+    int n = 0;
+    for (auto& e : g_prof_events) {
+        float ms = 0.0f;
+        if (cudaEventSynchronize(e.second) == cudaSuccess && cudaEventElapsedTime(&ms, e.first, e.second) == cudaSuccess) {
+            tot += ms;
+            ++n;
+        }
+        cudaEventDestroy(e.first);
+        cudaEventDestroy(e.second);
+    }
+    g_prof_events.clear();
+    g_prof_on = false;
+    if (total_ms) *total_ms = tot;
+    if (launches) *launches = n;
+    return B200_OK;
+}

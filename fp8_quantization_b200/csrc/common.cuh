@@ -1,0 +1,41 @@
+// common.cuh -- error plumbing, launch accounting and small helpers shared by the .cu files.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <atomic>
+#include <string>
+
+#include "../../include/fp8approx_b200.h"
+
+namespace b200 {
+
+extern std::atomic<uint64_t> g_launches;
+void set_error(const std::string& msg);
+void set_path(const char* name);
+int check_device();   // B200_OK, or B200_ERR_NO_DEVICE (there is no CPU fallback)
+
+inline int cuda_fail(cudaError_t e, const char* what)
+{
+    set_error(std::string(what) + ": " + cudaGetErrorString(e));
+    return B200_ERR_CUDA;
+}
+
+#define B200_CUDA_TRY(expr)                                          \
+    do {                                                             \
+        cudaError_t _e = (expr);                                     \
+        if (_e != cudaSuccess) return ::b200::cuda_fail(_e, #expr);  \
+    } while (0)
+
+#define B200_LAUNCH_CHECK(name)                                          \
+    do {                                                                 \
+        ::b200::g_launches.fetch_add(1, std::memory_order_relaxed);      \
+        cudaError_t _e = cudaGetLastError();                             \
+        if (_e != cudaSuccess) return ::b200::cuda_fail(_e, name);       \
+    } while (0)
+
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+inline int64_t round_up(int64_t a, int64_t b) { return ceil_div(a, b) * b; }
+
+}  // namespace b200

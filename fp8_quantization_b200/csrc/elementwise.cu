@@ -1,0 +1,204 @@
+// elementwise.cu -- HBM-bound elementwise kernels of the path:
+//   K4  FP8 fake-quantizer   quantize_to_fp8_ste_MM, quantization/quantizers/fp8_quantizer.py:97-173
+//   K5  field codec          approx/approx_matmul_whole_v9.py:233-362, approx/fp_any_int_v5.py:55-162
+// 128-bit vectorised loads/stores, grid = multiple of the SM count, grid-stride loops.
+// Algorithmic traffic: 8 B per element (4 read + 4 written).
+#include "common.cuh"
+#include "pair_math.cuh"
+
+namespace b200 {
+
+static int g_sm_count = 0;
+
+static int elementwise_grid(int64_t work_items, int threads)
+{
+    if (g_sm_count == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (g_sm_count <= 0) g_sm_count = 148;
+    }
+    int64_t blocks = ceil_div(work_items, threads);
+    int64_t cap = (int64_t)g_sm_count * 8;   // 8 resident CTAs of 256 threads per SM
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+// ---- K4 -------------------------------------------------------------------------------------
+__global__ void fp8_bias_kernel(const float* __restrict__ maxval, int64_t n_channels, int n_bits,
+                                float mantissa_bits, int sign_bits, float* __restrict__ bias_out)
+{
+    int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < n_channels) bias_out[c] = fp8_ste_bias(maxval[c], n_bits, mantissa_bits, sign_bits, nullptr);
+}
+
+// per-tensor: every thread derives the (same) bias once; vectorised body.
+__global__ void __launch_bounds__(256)
+fp8_fakequant_tensor_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t n,
+                            const float* __restrict__ maxval, int n_bits, float mantissa_bits,
+                            int sign_bits, float* __restrict__ bias_out, int vec_ok)
+{
+    float Mf;
+    const float mx = __ldg(maxval);
+    const float bias = fp8_ste_bias(mx, n_bits, mantissa_bits, sign_bits, &Mf);
+    if (blockIdx.x == 0 && threadIdx.x == 0) bias_out[0] = bias;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    if (vec_ok) {
+        const int64_t n4 = n >> 2;
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        float4* y4 = reinterpret_cast<float4*>(y);
+        for (int64_t i = tid; i < n4; i += stride) {
+            float4 v = __ldcs(x4 + i);
+            v.x = fp8_ste_quant(v.x, mx, bias, Mf, sign_bits);
+            v.y = fp8_ste_quant(v.y, mx, bias, Mf, sign_bits);
+            v.z = fp8_ste_quant(v.z, mx, bias, Mf, sign_bits);
+            v.w = fp8_ste_quant(v.w, mx, bias, Mf, sign_bits);
+            y4[i] = v;
+        }
+        for (int64_t i = (n4 << 2) + tid; i < n; i += stride) y[i] = fp8_ste_quant(x[i], mx, bias, Mf, sign_bits);
+    } else {
+        for (int64_t i = tid; i < n; i += stride) y[i] = fp8_ste_quant(x[i], mx, bias, Mf, sign_bits);
+    }
+}
+
+// per-channel (maxval viewed as [C,1,..,1], fp8_quantizer.py:114-115): channel = (i / inner) % C
+__global__ void __launch_bounds__(256)
+fp8_fakequant_channel_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t n,
+                             const float* __restrict__ maxval, const float* __restrict__ bias,
+                             int64_t n_channels, int64_t inner, int n_bits, float mantissa_bits,
+                             int sign_bits, int vec_ok)
+{
+    float Mf = rintf(mantissa_bits);
+    Mf = fminf(fmaxf(Mf, 1.0f), (float)(n_bits - sign_bits));
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    if (vec_ok) {   // inner % 4 == 0: a float4 never straddles two channels
+        const int64_t n4 = n >> 2;
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        float4* y4 = reinterpret_cast<float4*>(y);
+        for (int64_t i = tid; i < n4; i += stride) {
+            const int64_t c = ((i << 2) / inner) % n_channels;
+            const float mx = __ldg(maxval + c), b = __ldg(bias + c);
+            float4 v = __ldcs(x4 + i);
+            v.x = fp8_ste_quant(v.x, mx, b, Mf, sign_bits);
+            v.y = fp8_ste_quant(v.y, mx, b, Mf, sign_bits);
+            v.z = fp8_ste_quant(v.z, mx, b, Mf, sign_bits);
+            v.w = fp8_ste_quant(v.w, mx, b, Mf, sign_bits);
+            y4[i] = v;
+        }
+    } else {
+        for (int64_t i = tid; i < n; i += stride) {
+            const int64_t c = (i / inner) % n_channels;
+            y[i] = fp8_ste_quant(x[i], __ldg(maxval + c), __ldg(bias + c), Mf, sign_bits);
+        }
+    }
+}
+
+// ---- K5 -------------------------------------------------------------------------------------
+__global__ void fpany_encode_kernel(const float* __restrict__ v, int64_t n, int E, int M, int bias, int mode,
+                                    int quirk, int clip, int* __restrict__ expo, int* __restrict__ mant)
+{
+    const FmtParam p = make_param(E, M, bias, quirk != 0);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        int e, m;
+        if (mode == 0) fpany_encode(p, v[i], clip != 0, e, m);
+        else           allnorm_encode(E, M, bias, v[i], clip != 0, e, m);
+        expo[i] = e;
+        mant[i] = m;
+    }
+}
+
+__global__ void fpany_decode_kernel(const int* __restrict__ expo, const int* __restrict__ mant,
+                                    const float* __restrict__ sign, int64_t n, int E, int M, int bias, int mode,
+                                    float* __restrict__ out)
+{
+    const FmtParam p = make_param(E, M, bias, false);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float s = sign ? sign[i] : 1.0f;
+        out[i] = (mode == 0) ? fpany_decode(p, s, expo[i], mant[i]) : allnorm_decode(M, bias, s, expo[i], mant[i]);
+    }
+}
+
+__global__ void fpany_quant_kernel(const float* __restrict__ v, int64_t n, int E, int M, int bias, int quirk,
+                                   int clip, float* __restrict__ out)
+{
+    const FmtParam p = make_param(E, M, bias, quirk != 0);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        out[i] = fpany_quant(p, v[i], clip != 0);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_fp8_fakequant(const float* x, float* y, int64_t n, const float* maxval, int64_t n_channels,
+                                  int64_t inner, int n_bits, float mantissa_bits, int sign_bits, float* bias_out,
+                                  void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (n < 0 || n_channels < 1 || !maxval || !bias_out || (n > 0 && (!x || !y))) {
+        set_error("b200_fp8_fakequant: bad argument");
+        return B200_ERR_ARGUMENT;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) == 0;
+    if (n_channels == 1) {
+        const int grid = elementwise_grid(ceil_div(n > 0 ? n : 1, 4), 256);
+        fp8_fakequant_tensor_kernel<<<grid, 256, 0, st>>>(x, y, n, maxval, n_bits, mantissa_bits, sign_bits,
+                                                         bias_out, aligned ? 1 : 0);
+        B200_LAUNCH_CHECK("fp8_fakequant_tensor_kernel");
+    } else {
+        if (inner < 1) {
+            set_error("b200_fp8_fakequant: inner must be >= 1 for per-channel maxval");
+            return B200_ERR_ARGUMENT;
+        }
+        fp8_bias_kernel<<<(int)ceil_div(n_channels, 128), 128, 0, st>>>(maxval, n_channels, n_bits, mantissa_bits,
+                                                                       sign_bits, bias_out);
+        B200_LAUNCH_CHECK("fp8_bias_kernel");
+        if (n > 0) {
+            const int vec = (aligned && (inner % 4 == 0) && (n % 4 == 0)) ? 1 : 0;
+            const int grid = elementwise_grid(vec ? n / 4 : n, 256);
+            fp8_fakequant_channel_kernel<<<grid, 256, 0, st>>>(x, y, n, maxval, bias_out, n_channels, inner, n_bits,
+                                                              mantissa_bits, sign_bits, vec);
+            B200_LAUNCH_CHECK("fp8_fakequant_channel_kernel");
+        }
+    }
+    return B200_OK;
+}
+
+extern "C" int b200_fpany_encode(const float* v, int64_t n, int E, int M, int bias, int mode, int quirk, int clip,
+                                 int32_t* expo_out, int32_t* mant_out, void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (n <= 0) return B200_OK;
+    fpany_encode_kernel<<<elementwise_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(v, n, E, M, bias, mode, quirk,
+                                                                                  clip, expo_out, mant_out);
+    B200_LAUNCH_CHECK("fpany_encode_kernel");
+    return B200_OK;
+}
+
+extern "C" int b200_fpany_decode(const int32_t* expo, const int32_t* mant, const float* sign, int64_t n, int E, int M,
+                                 int bias, int mode, float* out, void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (n <= 0) return B200_OK;
+    fpany_decode_kernel<<<elementwise_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(expo, mant, sign, n, E, M, bias,
+                                                                                  mode, out);
+    B200_LAUNCH_CHECK("fpany_decode_kernel");
+    return B200_OK;
+}
+
+extern "C" int b200_fpany_quant(const float* v, int64_t n, int E, int M, int bias, int quirk, int clip, float* out,
+                                void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (n <= 0) return B200_OK;
+    fpany_quant_kernel<<<elementwise_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(v, n, E, M, bias, quirk, clip, out);
+    B200_LAUNCH_CHECK("fpany_quant_kernel");
+    return B200_OK;
+}

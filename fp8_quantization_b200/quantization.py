@@ -1,0 +1,440 @@
+"""Host-side mirror of the reference's quantization plumbing on the hot path (SURVEY.md 8(a) rows
+A8, A10): FPQuantizer, the min/max range estimators the scripts select, QuantizationManager and the
+two hijacker mixins whose `forward` protocol the operator classes inherit.
+
+Same class names, constructor keywords, attributes (`custom_bias`, `fix_ranges_flag`, `_quant_a` ...)
+and error behaviour as
+  quantization/quantizers/fp8_quantizer.py:191-319   (FPQuantizer)
+  quantization/range_estimators.py:56-125            (CurrentMinMax / AllMinMax / RunningMinMax)
+  quantization/quantization_manager.py:28-138        (QuantizationManager, Qstates)
+  quantization/base_quantized_classes.py:49-206      (QuantizedModule, QuantizedActivation)
+  quantization/hijacker.py:32-151                    (QuantizationHijacker)
+  quantization/quantized_folded_bn.py:12-95          (BNFusedHijacker)
+so that the parity tests read like the reference's own usage.  The elementwise arithmetic runs in
+the sm_100a fake-quant kernel (ops.fp8_fakequant); torch is used for min/max reductions only
+(calibration).  INT quantizers and MSE/line-search estimators are out of scope.
+"""
+import copy
+from enum import Enum
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+from torch.nn.modules.conv import _ConvNd
+
+from .fp8_quantizer import quantize_to_fp8_ste_MM
+
+
+class Qstates(Enum):
+    estimate_ranges = 1
+    fix_ranges = 2
+    learn_ranges = 3
+    estimate_ranges_train = 4
+
+
+# ---- range estimators (range_estimators.py:56-125) ---------------------------------------------
+class RangeEstimatorBase(nn.Module):
+    def __init__(self, per_channel=False, quantizer=None, **kwargs):
+        super().__init__()
+        self.current_xmin = None
+        self.current_xmax = None
+        self.per_channel = per_channel
+        self.quantizer = quantizer
+
+    def _minmax(self, x):
+        x = x.detach()
+        if self.per_channel:
+            mn, mx = torch.aminmax(x.reshape(x.shape[0], -1), dim=-1)
+        else:
+            mn, mx = torch.aminmax(x)
+        return mn, mx
+
+    def reset(self):
+        self.current_xmin = None
+        self.current_xmax = None
+
+    def __repr__(self):
+        return self._get_name() + "()"
+
+
+class CurrentMinMaxEstimator(RangeEstimatorBase):
+    def __init__(self, percentile=None, **kwargs):
+        super().__init__(**kwargs)
+        if percentile:
+            raise NotImplementedError("percentile range estimation is outside the hot path (SURVEY.md 2 row 6)")
+
+    def forward(self, x):
+        self.current_xmin, self.current_xmax = self._minmax(x)
+        return self.current_xmin, self.current_xmax
+
+
+class AllMinMaxEstimator(RangeEstimatorBase):
+    def forward(self, x):
+        mn, mx = self._minmax(x)
+        if self.current_xmin is None:
+            self.current_xmin, self.current_xmax = mn, mx
+        else:
+            self.current_xmin = torch.min(self.current_xmin, mn)
+            self.current_xmax = torch.max(self.current_xmax, mx)
+        return self.current_xmin, self.current_xmax
+
+
+class RunningMinMaxEstimator(RangeEstimatorBase):
+    def __init__(self, momentum=0.9, **kwargs):
+        super().__init__(**kwargs)
+        self.momentum = momentum
+
+    def forward(self, x):
+        mn, mx = self._minmax(x)
+        if self.current_xmin is None:
+            self.current_xmin, self.current_xmax = mn, mx
+        else:
+            self.current_xmin = (1 - self.momentum) * mn + self.momentum * self.current_xmin
+            self.current_xmax = (1 - self.momentum) * mx + self.momentum * self.current_xmax
+        return self.current_xmin, self.current_xmax
+
+
+RANGE_ESTIMATORS = {"current_minmax": CurrentMinMaxEstimator, "allminmax": AllMinMaxEstimator,
+                    "running_minmax": RunningMinMaxEstimator}
+
+
+def _resolve_estimator(spec):
+    if isinstance(spec, str):
+        return RANGE_ESTIMATORS[spec]
+    if isinstance(spec, type) and issubclass(spec, RangeEstimatorBase):
+        return spec
+    name = getattr(spec, "name", None) or getattr(spec, "__name__", "")
+    for key, cls in RANGE_ESTIMATORS.items():      # reference enum members / classes, matched by name
+        if key == name or cls.__name__ == name:
+            return cls
+    raise NotImplementedError(f"range estimator {spec!r} is outside the hot path")
+
+
+# ---- FPQuantizer (fp8_quantizer.py:191-319) ---------------------------------------------------
+class FPQuantizer(nn.Module):
+    """8-bit floating point fake-quantizer; `forward` stores `custom_bias` (fp8_quantizer.py:244),
+    which the operator classes read back through QuantizationManager.get_fp_bias()."""
+
+    def __init__(self, n_bits=8, per_channel=False, scale_domain=None, mantissa_bits=4, maxval=3,
+                 set_maxval=False, learn_maxval=False, learn_mantissa_bits=False,
+                 mse_include_mantissa_bits=True, allow_unsigned=False, **kwargs):
+        super().__init__()
+        self.n_bits = n_bits
+        self.per_channel = per_channel
+        self.state = None
+        self.ebits = n_bits - mantissa_bits - 1
+        self.default_bias = 2 ** (self.ebits - 1)
+        default_maxval = (2 - 2 ** (-mantissa_bits)) * 2 ** (2 ** self.ebits - 1 - self.default_bias)
+        self.maxval = torch.Tensor([maxval if maxval is not None else default_maxval])
+        self.mantissa_bits = torch.Tensor([float(mantissa_bits)])
+        self.set_maxval = set_maxval
+        self.allow_unsigned = allow_unsigned
+        self.sign_bits = 1
+        self.custom_bias = None
+        if learn_maxval or learn_mantissa_bits:
+            raise NotImplementedError("learned ranges belong to QAT, which the reference never wires up (SURVEY.md 2 row 16)")
+
+    def forward(self, x_float):
+        if self.maxval.device != x_float.device:
+            self.maxval = self.maxval.to(x_float.device)
+        res, self.custom_bias = quantize_to_fp8_ste_MM(x_float, self.n_bits, self.maxval, self.mantissa_bits,
+                                                       self.sign_bits)
+        return res
+
+    @property
+    def is_initialized(self):
+        return True
+
+    def set_quant_range(self, x_min, x_max):
+        """fp8_quantizer.py:268-287."""
+        if self.allow_unsigned and bool(torch.all(torch.as_tensor(x_min) >= 0)):
+            self.sign_bits = 0
+        if self.set_maxval:
+            if not isinstance(x_max, torch.Tensor):
+                x_max = torch.Tensor([x_max]).to(self.maxval.device)
+                x_min = torch.Tensor([x_min]).to(self.maxval.device)
+            mx = torch.abs(torch.max(torch.abs(x_min), x_max))
+            self.maxval = mx if mx.dim() > 0 else mx.reshape(1)
+
+    def make_range_trainable(self):
+        pass
+
+    def fix_ranges(self):
+        pass
+
+    def reset(self):
+        pass
+
+    def extra_repr(self):
+        return f"n_bits={self.n_bits}, mantissa_bits={self.mantissa_bits.item()}, per_channel={self.per_channel}"
+
+
+def _resolve_quantizer(spec):
+    if spec is None or spec is FPQuantizer:
+        return FPQuantizer
+    name = spec if isinstance(spec, str) else (getattr(spec, "__name__", "") or getattr(spec, "name", ""))
+    if name in ("fp_quantizer", "FPQuantizer"):
+        return FPQuantizer
+    raise NotImplementedError(f"quantizer {spec!r}: only fp_quantizer is on the hot path (scripts/image_net.sh)")
+
+
+# ---- QuantizationManager (quantization_manager.py:28-131) ---------------------------------------
+class QuantizationManager(nn.Module):
+    def __init__(self, qmethod=FPQuantizer, init=CurrentMinMaxEstimator, per_channel=False, x_min=None, x_max=None,
+                 qparams=None, range_estim_params=None):
+        super().__init__()
+        self.state = Qstates.estimate_ranges
+        self.qmethod = _resolve_quantizer(qmethod)
+        self.init = _resolve_estimator(init)
+        self.per_channel = per_channel
+        self.qparams = qparams if qparams else {}
+        self.range_estim_params = range_estim_params if range_estim_params else {}
+        self.range_estimator = None
+        self.quantizer = self.qmethod(per_channel=self.per_channel, **self.qparams)
+        self.quantizer.state = self.state
+        if x_min is not None and x_max is not None:
+            self.set_quant_range(x_min, x_max)
+            self.fix_ranges()
+        else:
+            self.range_estimator = self.init(per_channel=self.per_channel, quantizer=self.quantizer,
+                                             **self.range_estim_params)
+
+    @property
+    def n_bits(self):
+        return self.quantizer.n_bits
+
+    def estimate_ranges(self):
+        self.state = Qstates.estimate_ranges
+        self.quantizer.state = self.state
+
+    def fix_ranges(self):
+        self.state = Qstates.fix_ranges
+        self.quantizer.state = self.state
+
+    def reset_ranges(self):
+        self.range_estimator.reset()
+        self.quantizer.reset()
+        self.estimate_ranges()
+
+    def forward(self, x):
+        if self.state == Qstates.estimate_ranges or (self.state == Qstates.estimate_ranges_train and self.training):
+            cur_xmin, cur_xmax = self.range_estimator(x)
+            self.set_quant_range(cur_xmin, cur_xmax)
+        return self.quantizer(x)
+
+    def get_fp_bias(self):
+        return self.quantizer.custom_bias
+
+    def set_quant_range(self, x_min, x_max):
+        self.quantizer.set_quant_range(x_min, x_max)
+
+    def extra_repr(self):
+        return "state={}".format(self.state.name)
+
+
+# ---- QuantizedModule (base_quantized_classes.py:49-187) ----------------------------------------
+def _set_layer_fix_ranges(layer):
+    if isinstance(layer, QuantizationManager):
+        layer.fix_ranges()
+    if isinstance(layer, QuantizedModule):
+        layer.fix_ranges_flag = True
+
+
+def _set_layer_estimate_ranges(layer):
+    if isinstance(layer, QuantizationManager):
+        layer.estimate_ranges()
+    if isinstance(layer, QuantizedModule):
+        layer.fix_ranges_flag = False
+
+
+DEFAULT_RUN_METHOD = dict(approx_flag=False, quantize_after_mult_and_add=False, res_quantizer_flag=True,
+                          original_quantize_res=True)
+
+
+class QuantizedModule(nn.Module):
+    """Keyword contract of base_quantized_classes.py:56-82: `custom_approx_params` (13 keys) and
+    `run_method` (4 keys) are popped here and read on every forward."""
+
+    def __init__(self, *args, method=FPQuantizer, act_method=None, weight_range_method=CurrentMinMaxEstimator,
+                 act_range_method=RunningMinMaxEstimator, n_bits=8, n_bits_act=None, per_channel_weights=False,
+                 percentile=None, weight_range_options=None, act_range_options=None, scale_domain="linear",
+                 act_quant_kwargs=None, weight_quant_kwargs=None, quantize_input=False, fp8_kwargs=None, **kwargs):
+        kwargs.pop("act_quant_dict", None)
+        self.custom_approx_params = kwargs.pop("custom_approx_params", None)
+        self.run_method = kwargs.pop("run_method", None) or dict(DEFAULT_RUN_METHOD)
+        self.approx_flag = self.run_method["approx_flag"]
+        self.quantize_after_mult_and_add = self.run_method["quantize_after_mult_and_add"]
+        self.res_quantizer_flag = self.run_method["res_quantizer_flag"]
+        self.original_quantize_res = self.run_method["original_quantize_res"]
+        super().__init__(*args, **kwargs)
+        self.method = method
+        self.act_method = act_method or method
+        self.n_bits = n_bits
+        self.n_bits_act = n_bits_act or n_bits
+        self.per_channel_weights = per_channel_weights
+        self.percentile = percentile
+        self.weight_range_method = weight_range_method
+        self.weight_range_options = weight_range_options if weight_range_options else {}
+        self.act_range_method = act_range_method
+        self.act_range_options = act_range_options if act_range_options else {}
+        self.scale_domain = scale_domain
+        self.quantize_input = quantize_input
+        self.fp8_kwargs = fp8_kwargs or {}
+        self.register_buffer("_quant_w", torch.BoolTensor([False]))
+        self.register_buffer("_quant_a", torch.BoolTensor([False]))
+        self.act_qparams = dict(n_bits=self.n_bits_act, scale_domain=self.scale_domain, **(act_quant_kwargs or {}),
+                                **self.fp8_kwargs)
+        self.weight_qparams = dict(n_bits=self.n_bits, scale_domain=self.scale_domain, **(weight_quant_kwargs or {}),
+                                   **self.fp8_kwargs)
+        self.fix_ranges_flag = False
+
+    def quantized_weights(self):
+        self._quant_w = torch.BoolTensor([True])
+
+    def full_precision_weights(self):
+        self._quant_w = torch.BoolTensor([False])
+
+    def quantized_acts(self):
+        self._quant_a = torch.BoolTensor([True])
+
+    def full_precision_acts(self):
+        self._quant_a = torch.BoolTensor([False])
+
+    def quantized(self):
+        self.quantized_weights()
+        self.quantized_acts()
+
+    def full_precision(self):
+        self.full_precision_weights()
+        self.full_precision_acts()
+
+    def fix_ranges(self):
+        self.apply(_set_layer_fix_ranges)
+        self.fix_ranges_flag = True
+
+    def estimate_ranges(self):
+        self.apply(_set_layer_estimate_ranges)
+        self.fix_ranges_flag = False
+
+
+class QuantizedActivation(QuantizedModule):
+    """Stand-alone activation quantizer (base_quantized_classes.py:189-206)."""
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        self.activation_quantizer = QuantizationManager(qmethod=self.act_method, qparams=self.act_qparams,
+                                                        init=self.act_range_method,
+                                                        range_estim_params=self.act_range_options)
+
+    def quantize_activations(self, x):
+        return self.activation_quantizer(x) if self._quant_a else x
+
+    def forward(self, x):
+        return self.quantize_activations(x)
+
+
+ACTIVATIONS = (nn.ReLU, nn.ReLU6, nn.Hardtanh, nn.Sigmoid, nn.Tanh, nn.GELU, nn.PReLU)
+
+
+# ---- QuantizationHijacker (hijacker.py:32-151) -------------------------------------------------
+class QuantizationHijacker(QuantizedModule):
+    def __init__(self, *args, activation=None, **kwargs):
+        super().__init__(*args, **kwargs)
+        if activation:
+            assert isinstance(activation, ACTIVATIONS), str(activation)
+        self.activation_function = copy.deepcopy(activation) if activation else None
+        mk = lambda: QuantizationManager(qmethod=self.act_method, init=self.act_range_method, qparams=self.act_qparams,
+                                         range_estim_params=self.act_range_options)
+        self.activation_quantizer = mk()
+        self.res_quantizer = mk()                      # hijacker.py:57-62
+        if _resolve_estimator(self.weight_range_method) is CurrentMinMaxEstimator:
+            weight_init_params = dict(percentile=self.percentile)
+        else:
+            weight_init_params = self.weight_range_options
+        self.weight_quantizer = QuantizationManager(qmethod=self.method, init=self.weight_range_method,
+                                                    per_channel=self.per_channel_weights, qparams=self.weight_qparams,
+                                                    range_estim_params=weight_init_params)
+
+    def _core(self, x, offsets=None):
+        """hijacker.py:79-106 == quantized_folded_bn.py:34-58: calibrate twice / fixed once."""
+        if self.quantize_input and self._quant_a:
+            x = self.activation_quantizer(x)
+        weight, bias = self.get_params()
+        res = None
+        if self.fix_ranges_flag is False or self.original_quantize_res:
+            res = self.run_forward(x, weight, bias, offsets=offsets)
+            if self.quantize_input and self._quant_a and self.res_quantizer_flag:
+                res = self.res_quantizer(res)
+        if self.res_quantizer_flag and self.quantize_after_mult_and_add:
+            res = self.run_forward(x, weight, bias)
+        if self.res_quantizer_flag and self.approx_flag:
+            res = self.run_forward(x, weight, bias, offsets=offsets)
+        if (self.quantize_after_mult_and_add or self.approx_flag) and not self.res_quantizer_flag:
+            raise ValueError("quantize_after_mult_and_add or approx_flag is set but res_quantizer_flag is not set. "
+                             "you need to set res_quantizer_flag to True if you want to use "
+                             "quantize_after_mult_and_add or approx_flag")
+        return res
+
+    def forward(self, x, offsets=None):
+        res = self._core(x, offsets)
+        if self.activation_function is not None:
+            res = self.activation_function(res)
+        if not self.quantize_input and self._quant_a:
+            res = self.activation_quantizer(res)
+        return res
+
+    def get_params(self):
+        weight, bias = self.get_weight_bias()
+        if self._quant_w:
+            weight = self.quantize_weights(weight)
+        return weight, bias
+
+    def quantize_weights(self, weights):
+        return self.weight_quantizer(weights)
+
+    def get_weights_fp_bias(self):
+        return self.weight_quantizer.get_fp_bias()
+
+    def get_acts_fp_bias(self):
+        return self.activation_quantizer.get_fp_bias()
+
+    def get_res_fp_bias(self):
+        return self.res_quantizer.get_fp_bias()
+
+    def get_weight_bias(self):
+        return self.weight, getattr(self, "bias", None)
+
+    def run_forward(self, x, weight, bias, offsets=None):
+        raise NotImplementedError()
+
+
+# ---- BNFusedHijacker (quantized_folded_bn.py:12-95) ---------------------------------------------
+class BNFusedHijacker(QuantizationHijacker):
+    def __init__(self, *args, **kwargs):
+        kwargs.pop("bias", None)
+        momentum = kwargs.pop("momentum", 0.1)
+        eps = kwargs.pop("eps", 1e-5)
+        super().__init__(*args, **kwargs, bias=False)
+        if isinstance(self, nn.Linear):
+            bn_dim = self.out_features
+        elif isinstance(self, _ConvNd):
+            bn_dim = self.out_channels
+        else:
+            raise NotImplementedError(f"Unsupported type used: {self}")
+        self.register_buffer("running_mean", torch.zeros(bn_dim))
+        self.register_buffer("running_var", torch.ones(bn_dim))
+        self.momentum = momentum
+        self.gamma = nn.Parameter(torch.ones(bn_dim))
+        self.beta = nn.Parameter(torch.zeros(bn_dim))
+        self.epsilon = eps
+        self.bias = None
+
+    def forward(self, x):
+        res = self._core(x)
+        res = F.batch_norm(res, self.running_mean, self.running_var, self.gamma, self.beta, self.training,
+                           self.momentum, self.epsilon)
+        if self.activation_function is not None:
+            res = self.activation_function(res)
+        if not self.quantize_input and self._quant_a:
+            res = self.activation_quantizer(res)
+        return res

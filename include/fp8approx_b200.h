@@ -1,0 +1,134 @@
+/*
+ * fp8approx_b200.h -- C ABI of libfp8approx_b200.so: the B200 (sm_100a) implementation of the
+ * approx-FP8 simulated matmul hot path of revollllt/FP8_quantization.
+ *
+ * This is the drop-in boundary.  The reference is pure Python/PyTorch, so there is no existing FFI:
+ * each entry point below replaces a *Python call edge* of the reference (file:line cited per
+ * function; paths relative to the reference root) and is bound from Python with ctypes
+ * (fp8_quantization_b200/_lib.py; the reference-side stub is shown in INTEGRATION.md).
+ *
+ * Conventions
+ *   - plain C types only; every `const float*` / `float*` / `int32_t*` is a DEVICE pointer unless the
+ *     parameter name starts with `host_`;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); every call is
+ *     asynchronous on that stream and performs no host synchronisation and no allocation, except
+ *     the first call for a new (format, flags) combination, which builds and caches the pair
+ *     table (one small cudaMalloc + one kernel + one 4-byte read-back);
+ *   - the caller owns all buffers, including the scratch `workspace` whose size is returned by the
+ *     matching *_workspace_bytes function;
+ *   - return value: B200_OK or a negative B200_ERR_* code; b200_last_error() gives the text.
+ *     The Python host maps codes to the exceptions the reference raises at the same condition.
+ */
+#ifndef FP8APPROX_B200_H
+#define FP8APPROX_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_ERR_INVALID_FORMAT (-1) /* ValueError("Invalid combination of expo_width and mant_width"), approx_matmul_whole_v9.py:590 */
+#define B200_ERR_UNBOUND_TABLE (-2)  /* UnboundLocalError: withComp and dnsmp_factor < 3, approx_matmul_whole_v9.py:566-572,575-586 */
+#define B200_ERR_SHAPE (-3)          /* AssertionError: A.shape[1] == B.shape[0], approx_matmul_whole_v9.py:20 */
+#define B200_ERR_ARGUMENT (-4)
+#define B200_ERR_WORKSPACE (-5)
+#define B200_ERR_CUDA (-6)           /* RuntimeError */
+#define B200_ERR_NO_DEVICE (-7)      /* no sm_100 device: there is NO CPU fallback */
+
+/* custom_approx_params, utils/click_options.py:589-606 (13 keys) + run-mode bits.
+ * sim_hw_add_OFUF / with_OF_opt / with_UF_opt are accepted and IGNORED exactly like approx_v9 does
+ * (approx_matmul_whole_v9.py:15 vs :20-169).  */
+typedef struct b200_approx_params {
+    int32_t expo_width;
+    int32_t mant_width;
+    int32_t dnsmp_factor;
+    uint8_t withComp;
+    uint8_t with_approx;
+    uint8_t with_s2nn2s_opt;
+    uint8_t sim_hw_add_OFUF;
+    uint8_t with_OF_opt;
+    uint8_t with_UF_opt;
+    uint8_t golden_clip_OF;
+    uint8_t quant_btw_mult_accu;
+    uint8_t self_check_mode;     /* prints nothing here; kept for struct parity */
+    uint8_t single_column_quirk; /* 1: int32-tensor-bias numerics of the N==1 branch, approx_calculation.py:801-809 */
+    uint8_t allow_unpinned_format; /* 1: accept (E,M) outside {(4,3),(3,4),(2,5)} with an all-zero table (no reference answer) */
+    uint8_t force_generic;       /* 1: skip the table kernel, use the per-pair arithmetic kernel (tests) */
+    const int8_t *custom_table;  /* HOST pointer or NULL.  Non-NULL: use this 2^M x 2^M int8 table (the
+                                    error_table_NN argument of custom_matmul_vectorize,
+                                    approx_matmul_whole_v9.py:12) instead of selecting by withComp/dnsmp_factor */
+} b200_approx_params;
+
+/* ---- library / device ---------------------------------------------------------------------- */
+const char *b200_version(void);
+const char *b200_last_error(void);
+/* number of kernels this library has launched since load (bench.py's gpu_launches claim) */
+uint64_t b200_kernel_launches(void);
+/* name of the kernel path the last b200_approx_gemm / conv call took: "lut", "generic", ... */
+const char *b200_last_path(void);
+
+/* ---- A5: get_error_table_NN, approx/approx_matmul_whole_v9.py:555-592 ------------------------ */
+/* host_out: 2^M * 2^M int8, row-major, HOST memory. */
+int b200_error_table(int expo_width, int mant_width, int withComp, int dnsmp_factor,
+                     int allow_unpinned_format, int8_t *host_out);
+
+/* ---- A8: quantize_to_fp8_ste_MM, quantization/quantizers/fp8_quantizer.py:97-173 ------------- */
+/* maxval: device [n_channels]; n_channels == 1 -> per tensor, else channel = (i / inner) % n_channels
+ * (maxval viewed as [C,1,...,1], :114-115).  bias_out: device [n_channels] fp32 (integer valued),
+ * the second return value of the reference function (-> FPQuantizer.custom_bias, :244). */
+int b200_fp8_fakequant(const float *x, float *y, int64_t n, const float *maxval, int64_t n_channels,
+                       int64_t inner, int n_bits, float mantissa_bits, int sign_bits, float *bias_out,
+                       void *stream);
+
+/* ---- A2/A3/A4/A11: field codec (elementwise; used by tests and tools) ------------------------ */
+/* mode 0: float_to_fpany_absint_torch (approx_matmul_whole_v9.py:233-291)
+ * mode 1: float_to_fpany_absint_torch_allnorm (approx/fp_any_int_v5.py:55-110) */
+int b200_fpany_encode(const float *v, int64_t n, int expo_width, int mant_width, int bias, int mode,
+                      int tensor_bias_quirk, int clip_OF, int32_t *expo_out, int32_t *mant_out,
+                      void *stream);
+/* fpany_absint_to_float_torch (:295-329) / _allnorm (fp_any_int_v5.py:116-162); sign may be NULL */
+int b200_fpany_decode(const int32_t *expo, const int32_t *mant, const float *sign, int64_t n,
+                      int expo_width, int mant_width, int bias, int mode, float *out, void *stream);
+/* quant_to_fp_any_vectorize_torch (:333-362) */
+int b200_fpany_quant(const float *v, int64_t n, int expo_width, int mant_width, int bias,
+                     int tensor_bias_quirk, int clip_OF, float *out, void *stream);
+
+/* ---- A1/A6: approx_multiply -> custom_matmul_vectorize ---------------------------------------- */
+/* Replaces the whole per-column Python loop of approx_multiply
+ * (approx/approx_calculation.py:946-971 Linear, :774-799 BN-conv; one column =
+ * approx/approx_matmul_whole_v9.py:10-169) by ONE call.
+ *   A  : [Mrows, K] fp32, element (m,k) at A[m*lda + k]           (activations / im2col rows)
+ *   B  : [K, N] fp32, element (k,n) at B[k*sb_k + n*sb_n]          (weight.t(): sb_k=1, sb_n=ldw)
+ *   C  : [Mrows, N] fp32, element (m,n) at C[m*ldc + n]
+ *   bB : device int32 [N], per-column weight exponent bias (y_bias[i], :952); bA,bR scalars.
+ * C[m,n] = sum_{k ascending, fp32} addend(A[m,k], B[k,n]).                                       */
+size_t b200_approx_gemm_workspace_bytes(int64_t Mrows, int64_t K, int64_t N);
+int b200_approx_gemm(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n,
+                     float *C, int64_t ldc, int64_t Mrows, int64_t K, int64_t N, int bA,
+                     const int32_t *bB, int bR, const b200_approx_params *p, void *workspace,
+                     size_t workspace_bytes, void *stream);
+/* Same, with the biases left ON THE DEVICE as the fp32 tensors the fake-quantizer produced
+ * (FPQuantizer.custom_bias, fp8_quantizer.py:244): removes the three .item() host syncs per column
+ * of approx_calculation.py:952.  bA_dev / bR_dev: device [1] fp32 or NULL (-> 2^(E-1), :938-939);
+ * bB_dev: device fp32, column n at bB_dev[n*bB_stride]; values are truncated like .to(torch.int32). */
+int b200_approx_gemm_fbias(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n,
+                           float *C, int64_t ldc, int64_t Mrows, int64_t K, int64_t N,
+                           const float *bA_dev, const float *bB_dev, int64_t bB_stride,
+                           const float *bR_dev, const b200_approx_params *p, void *workspace,
+                           size_t workspace_bytes, void *stream);
+
+/* ---- measurement tool: CUDA-core integer issue peak (roofline denominator) ------ */
+/* Synchronous.  tiops_out: IADD3/LOP3 lane-ops per second in Tiop/s over all SMs; ms_out may be NULL. */
+int b200_int_peak_probe(int iters, double *tiops_out, double *ms_out);
+/* Between begin and end, every table-GEMM launch is bracketed by CUDA events on its own stream;
+ * end synchronises those events and returns their summed duration and the launch count. */
+int b200_profile_begin(void);
+int b200_profile_end(double *total_ms, int *launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FP8APPROX_B200_H */

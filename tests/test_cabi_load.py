@@ -1,0 +1,65 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads and exports every symbol
+include/fp8approx_b200.h declares; error codes map to the reference's exceptions; nothing computes
+without a GPU (no CPU fallback)."""
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+
+
+def declared_symbols():
+    txt = open(os.path.join(ROOT, "include", "fp8approx_b200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_every_declared_symbol_is_exported_and_bound():
+    import fp8_quantization_b200 as pkg
+    lib = pkg._lib.load()
+    syms = declared_symbols()
+    assert len(syms) >= 12
+    for s in syms:
+        assert hasattr(lib, s), f"{s} declared in include/fp8approx_b200.h but not exported"
+        assert s in pkg._lib.SIGNATURES, f"{s} has no ctypes signature"
+    assert set(pkg._lib.SIGNATURES) == set(syms)
+
+
+def test_table_selector_matches_reference_rules():
+    import numpy as np
+    import fp8_quantization_b200 as pkg
+    from oracle import oracle as orc
+    for (E, M) in [(4, 3), (3, 4), (2, 5)]:
+        for wc in (True, False):
+            for dn in (3, 4, 5):
+                assert np.array_equal(pkg.ops.error_table(E, M, wc, dn).numpy(), orc.get_error_table_NN(E, M, wc, dn))
+    with pytest.raises(ValueError, match="Invalid combination"):
+        pkg.ops.error_table(5, 2, True, 3)
+    with pytest.raises(UnboundLocalError):
+        pkg.ops.error_table(3, 4, True, 2)
+    with pytest.raises(UnboundLocalError):
+        pkg.ops.error_table(2, 5, True, 6)
+    assert int(pkg.ops.error_table(5, 2, True, 3, allow_unpinned_format=True).abs().sum()) == 0
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")
+def test_no_cpu_fallback():
+    import fp8_quantization_b200 as pkg
+    with pytest.raises(pkg._lib.B200Error):
+        pkg.quantize_to_fp8_ste_MM(torch.randn(8), 8, torch.tensor([1.0]), torch.tensor([3.0]), 1)
+    with pytest.raises(pkg._lib.B200Error):
+        pkg.custom_matmul_vectorize(torch.zeros(2, 2), torch.zeros(2, 2), 4, 3, 8, 8, 8, None)
+    import ctypes
+    t = ctypes.c_double(0)
+    assert pkg._lib.load().b200_int_peak_probe(10, ctypes.byref(t), None) == pkg._lib.ERR_NO_DEVICE
+
+
+def test_param_struct_layout():
+    import ctypes
+    import fp8_quantization_b200 as pkg
+    p = pkg.ops.make_params(dict(expo_width=3, mant_width=4, dnsmp_factor=5, withComp=False, golden_clip_OF=True))
+    assert (p.expo_width, p.mant_width, p.dnsmp_factor, p.withComp, p.golden_clip_OF) == (3, 4, 5, 0, 1)
+    assert ctypes.sizeof(pkg._lib.ApproxParams) == 32
+    assert pkg._lib.ApproxParams.custom_table.offset == 24
