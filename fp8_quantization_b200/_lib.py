@@ -38,6 +38,15 @@ class ApproxParams(ctypes.Structure):
     ]
 
 
+class ConvGeom(ctypes.Structure):
+    """struct b200_conv_geom (conv geometry of QCustomBNConv2dTorch.run_forward, approx_calculation.py:822-857)."""
+    _fields_ = [("batch", ctypes.c_int64), ("C_in", ctypes.c_int32), ("H", ctypes.c_int32), ("W", ctypes.c_int32),
+                ("C_out", ctypes.c_int32), ("kh", ctypes.c_int32), ("kw", ctypes.c_int32),
+                ("stride_h", ctypes.c_int32), ("stride_w", ctypes.c_int32), ("pad_h", ctypes.c_int32),
+                ("pad_w", ctypes.c_int32), ("dil_h", ctypes.c_int32), ("dil_w", ctypes.c_int32),
+                ("groups", ctypes.c_int32)]
+
+
 # every symbol include/fp8approx_b200.h declares: name -> (restype, argtypes)
 SIGNATURES = {
     "b200_version": (ctypes.c_char_p, []),
@@ -54,6 +63,16 @@ SIGNATURES = {
                                  c_int, ctypes.POINTER(ApproxParams), c_vp, c_sz, c_vp]),
     "b200_approx_gemm_fbias": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp,
                                        c_i64, c_vp, ctypes.POINTER(ApproxParams), c_vp, c_sz, c_vp]),
+    "b200_qamaa_gemm": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_int, c_f32,
+                                c_int, c_vp]),
+    "b200_conv_out_shape": (c_int, [ctypes.POINTER(ConvGeom), ctypes.POINTER(c_i64), ctypes.POINTER(ctypes.c_int32),
+                                    ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32),
+                                    ctypes.POINTER(ctypes.c_int32)]),
+    "b200_im2col": (c_int, [c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp]),
+    "b200_approx_conv2d_workspace_bytes": (c_sz, [ctypes.POINTER(ConvGeom)]),
+    "b200_approx_conv2d_fbias": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_vp, c_i64, c_vp,
+                                         ctypes.POINTER(ApproxParams), c_vp, c_sz, c_vp]),
+    "b200_qamaa_conv2d": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_int, c_f32, c_int, c_vp]),
     "b200_int_peak_probe": (c_int, [c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
     "b200_profile_begin": (c_int, []),
     "b200_profile_end": (c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_int)]),

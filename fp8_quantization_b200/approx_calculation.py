@@ -11,7 +11,6 @@ column); here ONE C-ABI call computes all columns with the biases read on the de
 The debugging prints of the reference's Linear variant (:972-984) are not reproduced.
 """
 import torch
-import torch.nn.functional as F
 from torch import nn
 
 from . import ops
@@ -71,30 +70,39 @@ def _conv_out_hw(h, w, kh, kw, stride, padding, dilation):
 class _ConvMixin(_ApproxMixin):
     def im2col(self, input_data, kernel_height, kernel_width, stride, padding, dilation):
         """[B,C,H,W] -> [B*Ho*Wo, C*kh*kw], K order (c,ky,kx) (approx_calculation.py:724-747)."""
-        col = F.unfold(input_data, (kernel_height, kernel_width), dilation=dilation, padding=padding, stride=stride)
-        return col.transpose(1, 2).reshape(-1, col.shape[1])
+        return ops.im2col(input_data, (kernel_height, kernel_width), stride, padding, dilation)
 
     def _conv_forward_cols(self, x, weight, bias, use_approx):
+        """run_forward of the conv operators (approx_calculation.py:822-917 / :655-719).
+
+        approx_flag: ONE C-ABI call does im2col + group loop + approx_multiply (implicit im2col for
+        groups with several output channels, the single-column kernel for depthwise groups).
+        quantize_after_mult_and_add: one call as well, except single-output-channel groups, which the
+        reference computes exactly (:810-811).  Otherwise: explicit im2col kernel + exact matmul."""
         x = x.contiguous().detach()
         weight = weight.contiguous().detach()
-        w_b, a_b, r_b = self.get_weights_fp_bias(), self.get_acts_fp_bias(), self.get_res_fp_bias()
         B, C, H, W = x.shape
         Cout, Cg, kh, kw = weight.shape
         Ho, Wo = _conv_out_hw(H, W, kh, kw, self.stride, self.padding, self.dilation)
-        col = self.im2col(x, kh, kw, self.stride, self.padding, self.dilation)
-        Kg = Cg * kh * kw
         Ng = Cout // self.groups
-        wcol = weight.reshape(Cout, -1)
-        out = torch.empty((B * Ho * Wo, Cout), device=x.device, dtype=x.dtype)
-        for g in range(self.groups):          # approx_calculation.py:858-906
-            xg = col[:, g * Kg:(g + 1) * Kg]
-            wg = wcol[g * Ng:(g + 1) * Ng, :]
-            if use_approx:
-                wb = w_b.reshape(-1)[g * Ng:(g + 1) * Ng] if w_b is not None and w_b.numel() > 1 else w_b
-                out[:, g * Ng:(g + 1) * Ng] = self.approx_multiply(xg, wg.t(), a_b, wb, r_b)
-            else:
-                out[:, g * Ng:(g + 1) * Ng] = self.multiply(xg, wg.t())
-        out = out.reshape(B, Ho, Wo, Cout).permute(0, 3, 1, 2)
+        if use_approx and self.approx_flag:
+            out = ops.approx_conv2d(x, weight, self.get_acts_fp_bias(), self.get_weights_fp_bias(),
+                                    self.get_res_fp_bias(), self._params(Ng == 1), self.stride, self.padding,
+                                    self.dilation, self.groups)
+        elif use_approx and self.quantize_after_mult_and_add and Ng != 1:
+            q = self.res_quantizer.quantizer
+            out = ops.qamaa_conv2d(x, weight, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits, self.stride,
+                                   self.padding, self.dilation, self.groups)
+        else:
+            col = self.im2col(x, kh, kw, self.stride, self.padding, self.dilation)
+            Kg = Cg * kh * kw
+            wcol = weight.reshape(Cout, -1)
+            if self.groups == 1:
+                out = self.multiply(col, wcol.t())
+            else:                                 # approx_calculation.py:858-906, exact branch
+                out = torch.bmm(col.view(-1, self.groups, Kg).transpose(0, 1),
+                                wcol.view(self.groups, Ng, Kg).transpose(1, 2)).permute(1, 0, 2).reshape(-1, Cout)
+        out = out.reshape(B, Ho, Wo, Cout).permute(0, 3, 1, 2)      # :909-910 (a view, like the reference)
         if bias is not None:
             out = out + bias.view(1, -1, 1, 1)
         return out

@@ -23,8 +23,10 @@
 
 #include "common.cuh"
 #include "lut.cuh"
+#include "pair_gemm.cuh"
 #include "pair_math.cuh"
 #include "tables.h"
+#include "gemm_impl.cuh"
 
 namespace b200 {
 
@@ -32,20 +34,6 @@ namespace b200 {
 // Pair-table builder: one thread per table cell, evaluating the reference op chain in "unit" space
 // (value / u, i.e. with result bias 1-M so that u == 1).
 // ------------------------------------------------------------------------------------------------
-// Exponent biases either come from the host (python ints) or stay on the device as the fp32 tensors
-// the fake-quantizer produced (FPQuantizer.custom_bias): no .item() sync on the hot path.
-struct BiasSrc {
-    int bA, bR;             // used when fA / fR are null
-    const float* fA;        // device [1] or null
-    const float* fR;        // device [1] or null
-    const int32_t* iB;      // device [N] int32, or null
-    const float* fB;        // device fp32, element n at fB[n * sB] (cast like .to(torch.int32))
-    int64_t sB;
-    __device__ __forceinline__ int A() const { return fA ? (int)__ldg(fA) : bA; }
-    __device__ __forceinline__ int R() const { return fR ? (int)__ldg(fR) : bR; }
-    __device__ __forceinline__ int B(int64_t n) const { return iB ? __ldg(iB + n) : (int)__ldg(fB + n * sB); }
-};
-
 struct LutFlags {
     int sign_quirk;        // cells where F is not odd in the operand sign (v9 :68 after :36)
     int unrepresentable;   // cells whose value does not fit bf16 exactly
@@ -98,6 +86,7 @@ __global__ void lut_build_kernel(LutGeom g, const signed char* __restrict__ T, i
 struct PredecodeArgs {
     const float* src;
     int64_t s_row, s_k;    // element (row, k) at src[row*s_row + k*s_k]   (row = m for A, n for B)
+    ASrc asrc;             // A operand only: GEMM rows or implicit im2col
     uint32_t* dst;         // [Kpad][Rpad]
     int64_t rows, K, Rpad, Kpad;
     int M;
@@ -160,7 +149,7 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
             const int64_t r = r0 + ty + i * 8, k = k0 + tx;
             uint32_t w = IS_B ? 0u : 2u * (uint32_t)g.zeroA_off;
             if (r < a.rows && k < a.K) {
-                const float v = a.src[r * a.s_row + k * a.s_k];
+                const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
                 w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off) : predecode_a(g, v, bA, off);
             }
             tile[tx][ty + i * 8] = w;   // [k][r]
@@ -177,7 +166,7 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
             const int64_t k = k0 + ty + i * 8, r = r0 + tx;
             uint32_t w = IS_B ? 0u : 2u * (uint32_t)g.zeroA_off;
             if (r < a.rows && k < a.K) {
-                const float v = a.src[r * a.s_row + k * a.s_k];
+                const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
                 w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off) : predecode_a(g, v, bA, off);
             }
             if (k < a.Kpad && r < a.Rpad) a.dst[k * a.Rpad + r] = w;
@@ -323,55 +312,26 @@ __global__ void __launch_bounds__(32 * WARPS, (WARPS == 8) ? 2 : 1) approx_gemm_
 }
 
 // ------------------------------------------------------------------------------------------------
-// Generic kernel: one thread per output element, pair_generic() per operand pair.
+// Arithmetic ("generic") kernel: pair_generic() per operand pair on the pair_gemm skeleton.
 // ------------------------------------------------------------------------------------------------
-struct GenericArgs {
-    const float* A;
-    int64_t lda;
-    const float* B;
-    int64_t sb_k, sb_n;
-    float* C;
-    int64_t ldc, Mrows, K, N;
+struct ApproxPairOp {
+    typedef FmtParam Col;
     BiasSrc bias;
     PairCfg cfg;
     const signed char* T;   // device table (4^M int8) or nullptr (= zeros)
-    const int* offgrid;     // nullptr: always run; else run only if *offgrid != 0
-};
-
-__global__ void __launch_bounds__(256) approx_gemm_generic_kernel(GenericArgs a)
-{
-    if (a.offgrid && *a.offgrid == 0) return;
-    __shared__ float As[8][33];
-    __shared__ float Bs[32][33];
-    __shared__ signed char Ts[1024];
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int tsize = (1 << a.cfg.M) * (1 << a.cfg.M);
-    for (int i = threadIdx.x; i < tsize; i += 256) Ts[i] = a.T ? a.T[i] : (signed char)0;
-    const int64_t n = (int64_t)blockIdx.y * 32 + tx, m = (int64_t)blockIdx.x * 8 + ty;
-    const int bBn = (n < a.N) ? a.bias.B(n) : 0;
-    const FmtParam pA = make_param(a.cfg.E, a.cfg.M, a.bias.A(), a.cfg.quirk);
-    const FmtParam pB = make_param(a.cfg.E, a.cfg.M, bBn, a.cfg.quirk);
-    const FmtParam pR = make_param(a.cfg.E, a.cfg.M, a.bias.R(), a.cfg.quirk);
-    float acc = 0.0f;
-    for (int64_t k0 = 0; k0 < a.K; k0 += 32) {
-        __syncthreads();
-        {
-            const int64_t mm = (int64_t)blockIdx.x * 8 + ty, kk = k0 + tx;
-            As[ty][tx] = (mm < a.Mrows && kk < a.K) ? a.A[mm * a.lda + kk] : 0.0f;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int64_t kb = k0 + ty + i * 8, nn = (int64_t)blockIdx.y * 32 + tx;
-                Bs[ty + i * 8][tx] = (kb < a.K && nn < a.N) ? a.B[kb * a.sb_k + nn * a.sb_n] : 0.0f;
-            }
-        }
-        __syncthreads();
-        const int kmax = (int)((a.K - k0 < 32) ? (a.K - k0) : 32);
-        if (m < a.Mrows && n < a.N)
-            for (int kk = 0; kk < kmax; ++kk)
-                acc += pair_generic(a.cfg, pA, pB, pR, Ts, As[ty][kk], Bs[kk][tx]);
+    FmtParam pA, pR;
+    __device__ __forceinline__ void begin()
+    {
+        pA = make_param(cfg.E, cfg.M, bias.A(), cfg.quirk);
+        pR = make_param(cfg.E, cfg.M, bias.R(), cfg.quirk);
     }
-    if (m < a.Mrows && n < a.N) a.C[m * a.ldc + n] = acc;
-}
+    __device__ __forceinline__ Col column(int64_t n) const { return make_param(cfg.E, cfg.M, bias.B(n), cfg.quirk); }
+    __device__ __forceinline__ float pair(float a, float b, const Col& pB) const
+    {
+        return T ? pair_generic(cfg, pA, pB, pR, T, a, b) : pair_generic<signed char>(cfg, pA, pB, pR, nullptr, a, b);
+    }
+    __device__ __forceinline__ float finish(float acc, const Col&) const { return acc; }
+};
 
 // ------------------------------------------------------------------------------------------------
 // Host side: table cache, dispatch, C ABI.
@@ -387,7 +347,7 @@ static std::mutex g_cache_mu;
 static std::map<std::tuple<int, const void*>, signed char*> g_dev_tables;            // (device, host table) -> device copy
 static std::map<std::tuple<int, int, int, const void*, int, int>, LutEntry> g_luts;   // (device,E,M,table,with_approx,clip)
 
-static int device_table(const signed char* host, int M, const signed char** dev_out)
+int device_table(const signed char* host, int M, const signed char** dev_out)
 {
     *dev_out = nullptr;
     if (!host) return B200_OK;
@@ -477,9 +437,11 @@ extern "C" size_t b200_approx_gemm_workspace_bytes(int64_t Mrows, int64_t K, int
     return kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4;
 }
 
-static int approx_gemm_impl(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, float* C,
-                            int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias,
-                            const b200_approx_params* p, void* workspace, size_t workspace_bytes, void* stream)
+// Shared by the GEMM and conv entry points (conv.cu): `A` is either a row-major matrix or an
+// implicit-im2col view of an NCHW tensor.
+int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc,
+                           int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const b200_approx_params* p,
+                           void* workspace, size_t workspace_bytes, void* stream)
 {
     if (int rc = check_device()) return rc;
     if (!p || Mrows < 0 || K < 0 || N < 0) { set_error("b200_approx_gemm: bad argument"); return B200_ERR_ARGUMENT; }
@@ -492,23 +454,22 @@ static int approx_gemm_impl(const float* A, int64_t lda, const float* B, int64_t
         return rc;
     }
     if (Mrows == 0 || N == 0) return B200_OK;
-    if (!A || !B || !C || (!bias.iB && !bias.fB)) { set_error("b200_approx_gemm: NULL operand"); return B200_ERR_ARGUMENT; }
+    if (!A.p || !B || !C || (!bias.iB && !bias.fB)) { set_error("b200_approx_gemm: NULL operand"); return B200_ERR_ARGUMENT; }
     cudaStream_t st = (cudaStream_t)stream;
     const signed char* dev_table = nullptr;
     if (int rc = device_table(host_table, M, &dev_table)) return rc;
 
-    GenericArgs ga;
-    ga.A = A; ga.lda = lda; ga.B = B; ga.sb_k = sb_k; ga.sb_n = sb_n; ga.C = C; ga.ldc = ldc;
-    ga.Mrows = Mrows; ga.K = K; ga.N = N; ga.bias = bias;
-    ga.cfg.E = E; ga.cfg.M = M;
-    ga.cfg.with_approx = p->with_approx != 0;
-    ga.cfg.s2nn2s = p->with_s2nn2s_opt != 0;
-    ga.cfg.clip_OF = p->golden_clip_OF != 0;
-    ga.cfg.qbma = p->quant_btw_mult_accu != 0;
-    ga.cfg.quirk = p->single_column_quirk != 0;
-    ga.T = (p->with_approx ? dev_table : nullptr);
-    ga.offgrid = nullptr;
-    const dim3 ggrid((unsigned)ceil_div(Mrows, 8), (unsigned)ceil_div(N, 32));
+    ApproxPairOp op;
+    op.bias = bias;
+    op.cfg.E = E; op.cfg.M = M;
+    op.cfg.with_approx = p->with_approx != 0 && dev_table != nullptr;   // zero table == no correction
+    op.cfg.s2nn2s = p->with_s2nn2s_opt != 0;
+    op.cfg.clip_OF = p->golden_clip_OF != 0;
+    op.cfg.qbma = p->quant_btw_mult_accu != 0;
+    op.cfg.quirk = p->single_column_quirk != 0;
+    op.T = op.cfg.with_approx ? dev_table : nullptr;
+    const BSrc bsrc{B, sb_k, sb_n};
+    const dim3 ggrid = pair_gemm_grid(Mrows, N);
 
     const bool lut_mode = !p->force_generic && p->with_s2nn2s_opt && p->quant_btw_mult_accu && !p->single_column_quirk && K > 0;
     const LutEntry* lut = nullptr;
@@ -518,8 +479,8 @@ static int approx_gemm_impl(const float* A, int64_t lda, const float* B, int64_t
             return rc;
     }
     if (!lut || lut->flags.sign_quirk || lut->flags.unrepresentable) {
-        approx_gemm_generic_kernel<<<ggrid, 256, 0, st>>>(ga);
-        B200_LAUNCH_CHECK("approx_gemm_generic_kernel");
+        pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, nullptr, 0);
+        B200_LAUNCH_CHECK("pair_gemm_kernel<ApproxPairOp>");
         set_path("generic");
         return B200_OK;
     }
@@ -536,8 +497,8 @@ static int approx_gemm_impl(const float* A, int64_t lda, const float* B, int64_t
     B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
 
     PredecodeArgs pa;
-    pa.src = A; pa.s_row = lda; pa.s_k = 1; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad; pa.Kpad = Kpad;
-    pa.M = M; pa.bias = bias; pa.offgrid = flag;
+    pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
+    pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
     predecode_kernel<false, true><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, lut->geom);
     B200_LAUNCH_CHECK("predecode_kernel<A>");
     PredecodeArgs pb = pa;
@@ -572,9 +533,9 @@ static int approx_gemm_impl(const float* A, int64_t lda, const float* B, int64_t
     }
     prof_record(false, st);
     B200_LAUNCH_CHECK("approx_gemm_lut_kernel");
-    ga.offgrid = flag;   // runs only if the predecode found an off-grid operand
-    approx_gemm_generic_kernel<<<ggrid, 256, 0, st>>>(ga);
-    B200_LAUNCH_CHECK("approx_gemm_generic_kernel(conditional)");
+    // runs only if the predecode found an off-grid operand
+    pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
+    B200_LAUNCH_CHECK("pair_gemm_kernel<ApproxPairOp>(conditional)");
     set_path("lut");
     return B200_OK;
 }
@@ -584,7 +545,7 @@ extern "C" int b200_approx_gemm(const float* A, int64_t lda, const float* B, int
                                 const b200_approx_params* p, void* workspace, size_t workspace_bytes, void* stream)
 {
     BiasSrc b{bA, bR, nullptr, nullptr, bB, nullptr, 1};
-    return approx_gemm_impl(A, lda, B, sb_k, sb_n, C, ldc, Mrows, K, N, b, p, workspace, workspace_bytes, stream);
+    return approx_gemm_impl(make_gemm_asrc(A, lda), B, sb_k, sb_n, C, ldc, Mrows, K, N, b, p, workspace, workspace_bytes, stream);
 }
 
 extern "C" int b200_approx_gemm_fbias(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n,
@@ -596,7 +557,7 @@ extern "C" int b200_approx_gemm_fbias(const float* A, int64_t lda, const float* 
     if (!p) { set_error("b200_approx_gemm_fbias: params is NULL"); return B200_ERR_ARGUMENT; }
     const int dflt = 1 << (p->expo_width > 0 ? p->expo_width - 1 : 0);   // approx_calculation.py:938-939
     BiasSrc b{dflt, dflt, bA_dev, bR_dev, nullptr, bB_dev, bB_stride};
-    return approx_gemm_impl(A, lda, B, sb_k, sb_n, C, ldc, Mrows, K, N, b, p, workspace, workspace_bytes, stream);
+    return approx_gemm_impl(make_gemm_asrc(A, lda), B, sb_k, sb_n, C, ldc, Mrows, K, N, b, p, workspace, workspace_bytes, stream);
 }
 
 extern "C" int b200_profile_begin(void)

@@ -1,0 +1,30 @@
+// gemm_impl.cuh -- internal interface between the C-ABI entry points (approx_gemm.cu, conv.cu).
+#pragma once
+#include "common.cuh"
+#include "pair_gemm.cuh"
+
+namespace b200 {
+
+// Exponent biases either come from the host (python ints) or stay on the device as the fp32 tensors
+// the fake-quantizer produced (FPQuantizer.custom_bias): no .item() sync on the hot path.
+struct BiasSrc {
+    int bA, bR;             // used when fA / fR are null
+    const float* fA;        // device [1] or null
+    const float* fR;        // device [1] or null
+    const int32_t* iB;      // device [N] int32, or null
+    const float* fB;        // device fp32, element n at fB[n * sB] (cast like .to(torch.int32))
+    int64_t sB;
+    __device__ __forceinline__ int A() const { return fA ? (int)__ldg(fA) : bA; }
+    __device__ __forceinline__ int R() const { return fR ? (int)__ldg(fR) : bR; }
+    __device__ __forceinline__ int B(int64_t n) const { return iB ? __ldg(iB + n) : (int)__ldg(fB + n * sB); }
+};
+
+
+// (device, host table) -> cached device copy of a 4^M int8 table; nullptr stays nullptr (zero table)
+int device_table(const signed char* host, int M, const signed char** dev_out);
+
+int approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc,
+                     int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const b200_approx_params* p,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+}  // namespace b200

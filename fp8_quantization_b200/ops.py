@@ -143,6 +143,124 @@ def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out
     return out
 
 
+def _dev_scalar(b, device):
+    if b is None:
+        return None
+    if not torch.is_tensor(b):
+        b = torch.tensor([float(b)])
+    return b.reshape(-1)[:1].to(device=device, dtype=torch.float32)
+
+
+def qamaa_matmul(x, y, n_bits, maxval, mantissa_bits, sign_bits, out=None):
+    """quantize_after_mult_and_add column loop (approx/approx_calculation.py:959-967) in ONE launch:
+    C = Q(sum_k Q(x[:,k] * y[k,:])) with Q = quantize_to_fp8_ste_MM(., n_bits, maxval, mantissa_bits,
+    sign_bits)[0]; `maxval` is the result quantizer's per-tensor range (read on the device)."""
+    lib = _lib.load()
+    _require_cuda(x, y)
+    assert x.dim() == 2 and y.dim() == 2 and x.shape[1] == y.shape[0]
+    x = x.float() if x.dtype != torch.float32 else x
+    y = y.float() if y.dtype != torch.float32 else y
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    mv = torch.as_tensor(maxval).to(device=x.device, dtype=torch.float32).reshape(-1)
+    if mv.numel() != 1:
+        raise ValueError("quantize_after_mult_and_add needs a per-tensor result range")
+    mbits = float(mantissa_bits.item()) if torch.is_tensor(mantissa_bits) else float(mantissa_bits)
+    Mrows, K = x.shape
+    N = y.shape[1]
+    if out is None:
+        out = torch.empty((Mrows, N), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = lib.b200_qamaa_gemm(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out), out.stride(0),
+                                 Mrows, K, N, _ptr(mv), int(n_bits), mbits, int(sign_bits), _stream())
+    _lib.check(rc)
+    return out
+
+
+def conv_geom(x_shape, w_shape, stride, padding, dilation, groups):
+    g = _lib.ConvGeom()
+    g.batch, g.C_in, g.H, g.W = (int(v) for v in x_shape)
+    g.C_out, _, g.kh, g.kw = (int(v) for v in w_shape)
+    g.stride_h, g.stride_w = (int(v) for v in stride)
+    g.pad_h, g.pad_w = (int(v) for v in padding)
+    g.dil_h, g.dil_w = (int(v) for v in dilation)
+    g.groups = int(groups)
+    return g
+
+
+def conv_out_shape(g):
+    lib = _lib.load()
+    rows = ctypes.c_int64()
+    ho, wo, kg, ng = (ctypes.c_int32() for _ in range(4))
+    _lib.check(lib.b200_conv_out_shape(ctypes.byref(g), ctypes.byref(rows), ctypes.byref(ho), ctypes.byref(wo),
+                                       ctypes.byref(kg), ctypes.byref(ng)))
+    return rows.value, ho.value, wo.value, kg.value, ng.value
+
+
+def im2col(x, kernel_size, stride, padding, dilation):
+    """[B,C,H,W] -> [B*Ho*Wo, C*kh*kw], K order (c,ky,kx) (approx/approx_calculation.py:724-747)."""
+    lib = _lib.load()
+    _require_cuda(x)
+    x = x.float().contiguous()
+    g = conv_geom(x.shape, (1, x.shape[1], kernel_size[0], kernel_size[1]), stride, padding, dilation, 1)
+    rows, _, _, kg, _ = conv_out_shape(g)
+    out = torch.empty((rows, kg), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.b200_im2col(_ptr(x), _ptr(out), ctypes.byref(g), _stream()))
+    return out
+
+
+def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, dilation, groups):
+    """im2col + group loop + approx_multiply of QCustomBNConv2dTorch.run_forward
+    (approx/approx_calculation.py:846-906) in one C-ABI call.  Returns [B*Ho*Wo, C_out] fp32.
+    Biases are the fake-quantizers' fp32 tensors (or None -> 2^(E-1)); read on the device."""
+    lib = _lib.load()
+    _require_cuda(x, weight)
+    x = x.float().contiguous()
+    weight = weight.float().contiguous()
+    g = conv_geom(x.shape, weight.shape, stride, padding, dilation, groups)
+    rows, _, _, _, _ = conv_out_shape(g)
+    out = torch.empty((rows, g.C_out), dtype=torch.float32, device=x.device)
+    fa, fr = _dev_scalar(x_bias, x.device), _dev_scalar(res_bias, x.device)
+    fb = w_bias if torch.is_tensor(w_bias) else torch.tensor([float(w_bias if w_bias is not None else
+                                                                    2 ** (params.expo_width - 1))])
+    fb = fb.reshape(-1).to(device=x.device, dtype=torch.float32)
+    if fb.numel() == 1:
+        sB = 0
+    else:
+        if fb.numel() != g.C_out:
+            raise IndexError("weight fp bias does not have one entry per output channel")
+        sB = fb.stride(0)
+    nbytes = lib.b200_approx_conv2d_workspace_bytes(ctypes.byref(g))
+    ws = _workspace(x.device, nbytes) if nbytes else None
+    with torch.cuda.device(x.device):
+        rc = lib.b200_approx_conv2d_fbias(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(fa), _ptr(fb), sB,
+                                          _ptr(fr), ctypes.byref(params), _ptr(ws), ws.numel() if ws is not None else 0,
+                                          _stream())
+    _lib.check(rc)
+    return out
+
+
+def qamaa_conv2d(x, weight, n_bits, maxval, mantissa_bits, sign_bits, stride, padding, dilation, groups):
+    """quantize_after_mult_and_add conv (approx/approx_calculation.py:787-795 in the group loop)."""
+    lib = _lib.load()
+    _require_cuda(x, weight)
+    x = x.float().contiguous()
+    weight = weight.float().contiguous()
+    g = conv_geom(x.shape, weight.shape, stride, padding, dilation, groups)
+    rows, _, _, _, _ = conv_out_shape(g)
+    out = torch.empty((rows, g.C_out), dtype=torch.float32, device=x.device)
+    mv = torch.as_tensor(maxval).to(device=x.device, dtype=torch.float32).reshape(-1)
+    if mv.numel() != 1:
+        raise ValueError("quantize_after_mult_and_add needs a per-tensor result range")
+    mbits = float(mantissa_bits.item()) if torch.is_tensor(mantissa_bits) else float(mantissa_bits)
+    with torch.cuda.device(x.device):
+        rc = lib.b200_qamaa_conv2d(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(mv), int(n_bits), mbits,
+                                   int(sign_bits), _stream())
+    _lib.check(rc)
+    return out
+
+
 def fp8_fakequant(x_float, n_bits, maxval, num_mantissa_bits, sign_bits):
     """quantize_to_fp8_ste_MM (quantization/quantizers/fp8_quantizer.py:97-173) -> (x_q, bias)."""
     lib = _lib.load()

@@ -120,6 +120,43 @@ int b200_approx_gemm_fbias(const float *A, int64_t lda, const float *B, int64_t 
                            const float *bR_dev, const b200_approx_params *p, void *workspace,
                            size_t workspace_bytes, void *stream);
 
+/* ---- A6 (second mode): quantize_after_mult_and_add -------------------------------------------- */
+/* C[m,n] = Q(sum_k Q(A[m,k]*B[k,n])), Q = quantize_to_fp8_ste_MM(., n_bits, maxval, mantissa_bits,
+ * sign_bits)[0] with the RESULT quantizer's per-tensor maxval (device [1]); replaces the column loop
+ * approx/approx_calculation.py:959-967 (Linear) / :787-795 (BN-conv).  Same operand layout as
+ * b200_approx_gemm.  fp32 accumulation, k ascending. */
+int b200_qamaa_gemm(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n, float *C,
+                    int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *maxval_dev, int n_bits,
+                    float mantissa_bits, int sign_bits, void *stream);
+
+/* ---- A9: conv form, QCustomBNConv2dTorch.run_forward, approx/approx_calculation.py:822-917 -------- */
+typedef struct b200_conv_geom {
+    int64_t batch;
+    int32_t C_in, H, W;          /* input  [batch, C_in, H, W], contiguous NCHW fp32 */
+    int32_t C_out, kh, kw;       /* weight [C_out, C_in/groups, kh, kw], contiguous   */
+    int32_t stride_h, stride_w, pad_h, pad_w, dil_h, dil_w, groups;
+} b200_conv_geom;
+/* rows = batch*Ho*Wo, Kg = (C_in/groups)*kh*kw, Ng = C_out/groups; any out pointer may be NULL */
+int b200_conv_out_shape(const b200_conv_geom *g, int64_t *rows, int32_t *Ho, int32_t *Wo, int32_t *Kg,
+                        int32_t *Ng);
+/* im2col (:724-747): out [rows, C_in*kh*kw] row-major, K order (c, ky, kx), zero padded borders */
+int b200_im2col(const float *x, float *out, const b200_conv_geom *g, void *stream);
+/* im2col + group loop + approx_multiply (:846-906) in one call; out is [rows, C_out] row-major (the
+ * tensor the reference then views as [B,Ho,Wo,C_out] and permutes, :909-910).  Groups with more than
+ * one output channel: table GEMM over an implicit im2col view (no im2col matrix in HBM).  Groups
+ * with ONE output channel (depthwise): the reference's int32-tensor-bias numerics (:800-809), one
+ * launch for all groups; p->single_column_quirk is set by the library from the geometry.
+ * bB_dev: per-output-channel weight bias, channel c at bB_dev[c*bB_stride] (stride 0 = per tensor). */
+size_t b200_approx_conv2d_workspace_bytes(const b200_conv_geom *g);
+int b200_approx_conv2d_fbias(const float *x, const float *w, float *out, const b200_conv_geom *g,
+                             const float *bA_dev, const float *bB_dev, int64_t bB_stride,
+                             const float *bR_dev, const b200_approx_params *p, void *workspace,
+                             size_t workspace_bytes, void *stream);
+/* quantize_after_mult_and_add conv (:787-795); groups with one output channel are refused
+ * (B200_ERR_ARGUMENT): the reference computes those exactly (:810-811). */
+int b200_qamaa_conv2d(const float *x, const float *w, float *out, const b200_conv_geom *g,
+                      const float *maxval_dev, int n_bits, float mantissa_bits, int sign_bits, void *stream);
+
 /* ---- measurement tool: CUDA-core integer issue peak (roofline denominator) ------ */
 /* Synchronous.  tiops_out: IADD3/LOP3 lane-ops per second in Tiop/s over all SMs; ms_out may be NULL. */
 int b200_int_peak_probe(int iters, double *tiops_out, double *ms_out);
