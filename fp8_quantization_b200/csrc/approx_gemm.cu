@@ -454,7 +454,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
         return rc;
     }
     if (Mrows == 0 || N == 0) return B200_OK;
-    if (!A.p || !B || !C || (!bias.iB && !bias.fB)) { set_error("b200_approx_gemm: NULL operand"); return B200_ERR_ARGUMENT; }
+    if ((K > 0 && (!A.p || !B)) || !C || (!bias.iB && !bias.fB)) { set_error("b200_approx_gemm: NULL operand"); return B200_ERR_ARGUMENT; }
     cudaStream_t st = (cudaStream_t)stream;
     const signed char* dev_table = nullptr;
     if (int rc = device_table(host_table, M, &dev_table)) return rc;
