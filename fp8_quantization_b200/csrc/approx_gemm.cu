@@ -48,10 +48,11 @@ __global__ void lut_build_kernel(LutGeom g, const signed char* __restrict__ T, i
     if (idx < g.zeroA_off) {
         const int M = g.M;
         const int mB = idx & ((1 << M) - 1);
-        const int sb = (idx >> M) & 1;
-        const int row = idx / g.row_entries;
+        const int row = idx >> M;
         const int idx_t = row % g.NT;
-        const int mA = row / g.NT;
+        const int q = row / g.NT;
+        const int mA = q & ((1 << M) - 1);
+        const int sa = q >> M;
         const int t = idx_t - g.RA - M - 2;
         if (idx_t > g.RA) {
             const FmtParam pR = make_param(g.E, M, 1 - M, false);   // unit space: u = 2^(1-bias-M) = 1
@@ -62,15 +63,15 @@ __global__ void lut_build_kernel(LutGeom g, const signed char* __restrict__ T, i
             const float scale = pow2f_i(t + M - 1);
             float val[2];
 #pragma unroll
-            for (int sa = 0; sa < 2; ++sa) {
+            for (int sb = 0; sb < 2; ++sb) {
                 const float sg = ((sa ^ sb) & 1) ? -1.0f : 1.0f;
                 float gq = pex * scale * sg;                       // golden product, exact
                 gq = fpany_quant(pR, gq, clip_OF != 0);            // v9 :36
                 const float sgn = (gq < 0.0f) ? -1.0f : 1.0f;      // v9 :68
                 float r = scale * p * sgn;                         // v9 :73-77 (+ :79-80 folded in t)
-                val[sa] = fpany_quant(pR, r, clip_OF != 0);        // v9 :108
+                val[sb] = fpany_quant(pR, r, clip_OF != 0);        // v9 :108
             }
-            if (val[1] != -val[0]) atomicAdd(&flags->sign_quirk, 1);
+            if (val[1] != -val[0]) atomicAdd(&flags->sign_quirk, 1);   // not odd in the sign of b
             const uint32_t bits = __float_as_uint(val[0]);
             if (bits & 0xFFFFu) atomicAdd(&flags->unrepresentable, 1);
             out = (uint16_t)(bits >> 16);
@@ -110,14 +111,15 @@ __device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int b
         return 2u * (uint32_t)g.zeroA_off;
     }
     const uint32_t mA = frac >> (23 - M);
-    return (bits & kSignBit) | (2u * (uint32_t)(g.row_entries * (tA + g.NT * (int)mA)));
+    const uint32_t sa = bits >> 31;
+    return 2u * (uint32_t)(g.row_entries * (tA + g.NT * (int)(mA + (sa << M))));
 }
 
 __device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int bA, int bB, int bR, int& off)
 {
     const uint32_t bits = __float_as_uint(v);
     const uint32_t mag = bits & 0x7FFFFFFFu;
-    if (mag == 0) return 0u;                                  // tB_idx = 0: every product rounds to 0
+    if (mag == 0) return kBf16One << 16;                      // tB_idx = 0: every product rounds to 0
     const int M = g.M;
     const int L = (int)(mag >> 23) - 127;
     const uint32_t frac = mag & 0x7FFFFFu;
@@ -125,12 +127,12 @@ __device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int b
     if ((frac & ((1u << (23 - M)) - 1u)) != 0 || L < 1 - bB - M || (mag >> 23) == 0 || (mag >> 23) == 255 ||
         tB + g.RA > g.NTB - 1 || (1 - bA - M) + (1 - bB - M) < -120) {
         off = 1;
-        return 0u;
+        return kBf16One << 16;
     }
     if (tB < -g.RA) tB = -g.RA;
     const uint32_t mB = frac >> (23 - M);
-    const uint32_t sb = bits >> 31;
-    return 2u * (mB + (sb << M) + (uint32_t)(g.row_entries * (tB + g.RA)));
+    const uint32_t mult = (bits >> 31) ? kBf16MinusOne : kBf16One;
+    return (mult << 16) | (2u * (mB + (uint32_t)(g.row_entries * (tB + g.RA))));
 }
 
 // 32x32 tile transpose: reads along k (SRC_K_CONTIG) or along rows, writes along rows.
@@ -147,7 +149,7 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int64_t r = r0 + ty + i * 8, k = k0 + tx;
-            uint32_t w = IS_B ? 0u : 2u * (uint32_t)g.zeroA_off;
+            uint32_t w = IS_B ? (kBf16One << 16) : 2u * (uint32_t)g.zeroA_off;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
                 w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off) : predecode_a(g, v, bA, off);
@@ -164,7 +166,7 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int64_t k = k0 + ty + i * 8, r = r0 + tx;
-            uint32_t w = IS_B ? 0u : 2u * (uint32_t)g.zeroA_off;
+            uint32_t w = IS_B ? (kBf16One << 16) : 2u * (uint32_t)g.zeroA_off;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
                 w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off) : predecode_a(g, v, bA, off);
@@ -187,11 +189,18 @@ constexpr int LUT_KT = 16;
 constexpr int LUT_STAGES = 3;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ uint32_t lds_u16(uint32_t addr)
+__device__ __forceinline__ unsigned short lds_u16(uint32_t addr)
 {
-    uint32_t v;
-    asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr));
+    unsigned short v;
+    asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
     return v;
+}
+// acc += e * m with e, m bf16 and acc fp32 (PTX ISA 8.6 mixed-precision fma, SASS FHFMA.BF16):
+// the product of two bf16 is exact in fp32 and the add rounds once -- identical to an fp32 add of
+// the (exactly representable) table value.
+__device__ __forceinline__ void fma_bf16(float& acc, unsigned short e, unsigned short m)
+{
+    asm("fma.rn.f32.bf16 %0, %1, %2, %0;" : "+f"(acc) : "h"(e), "h"(m));
 }
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src)
 {
@@ -271,20 +280,22 @@ __global__ void __launch_bounds__(32 * WARPS, (WARPS == 8) ? 2 : 1) approx_gemm_
 #pragma unroll 4
         for (int kk = 0; kk < KT; ++kk) {
             const uint4 bq = *reinterpret_cast<const uint4*>(Bsm + kk * BN);
-            const uint32_t bw[4] = {bq.x + lut_base, bq.y + lut_base, bq.z + lut_base, bq.w + lut_base};
+            const uint32_t bw[4] = {bq.x, bq.y, bq.z, bq.w};
+            uint32_t bo[4];
+            unsigned short bm[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                bo[j] = (bw[j] & 0xFFFFu) + lut_base;          // table byte address of the (tB_idx, mB) part
+                bm[j] = (unsigned short)(bw[j] >> 16);         // bf16 sign of b
+            }
 #pragma unroll
             for (int i4 = 0; i4 < 4; ++i4) {
                 const uint4 aq = *reinterpret_cast<const uint4*>(Asm + kk * BM + i4 * 4);
                 const uint32_t aw[4] = {aq.x, aq.y, aq.z, aq.w};
 #pragma unroll
                 for (int ii = 0; ii < 4; ++ii) {
-                    const float sa = __uint_as_float((aw[ii] & kSignBit) | 0x3F800000u);
-                    const uint32_t ao = aw[ii] & ~kSignBit;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const uint32_t e = lds_u16(ao + bw[j]);
-                        acc[i4 * 4 + ii][j] = __fmaf_rn(__uint_as_float(e << 16), sa, acc[i4 * 4 + ii][j]);
-                    }
+                    for (int j = 0; j < 4; ++j) fma_bf16(acc[i4 * 4 + ii][j], lds_u16(aw[ii] + bo[j]), bm[j]);
                 }
             }
         }
