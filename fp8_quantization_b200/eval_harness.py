@@ -1,0 +1,99 @@
+"""Synthetic-batch evaluation of a quantized model, sharded by batch across ranks.
+
+The reference is single-process (image_net.py:59-202: estimate_ranges -> one calibration batch ->
+fix_ranges -> eval batches).  Rows (images) are independent given replicated weights and calibrated
+ranges, so N GPUs run N replicas on disjoint slices of the eval batch:
+  * weights are replicated by seeding every rank identically (no broadcast);
+  * calibration runs on the SAME full calibration batch on every rank (replicated: bit-identical
+    ranges, one extra forward) -- or, with `shard_calibration=True`, on each rank's slice followed by
+    an all_reduce(MIN/MAX) of every range estimator before fix_ranges();
+  * the only data-path collective is ONE all_gather of the logits (latency bound, nothing to fuse).
+Works with any torch.distributed backend (NCCL on the B200 box, gloo in the CPU tests).
+"""
+import torch
+import torch.distributed as dist
+
+from .quantization import QuantizationManager
+
+
+def shard_range(n, rank, world):
+    """Contiguous, balanced slice [lo, hi) of n items for `rank` (first n % world ranks get one more)."""
+    base, extra = divmod(n, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def _world(group=None):
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(group), dist.get_world_size(group)
+    return 0, 1
+
+
+def sync_ranges(model, group=None):
+    """all_reduce(MIN) / all_reduce(MAX) of every range estimator's running min / max, then push the
+    merged range into its quantizer (quantization/range_estimators.py:56-100 state)."""
+    rank, world = _world(group)
+    if world == 1:
+        return
+    for m in model.modules():
+        if isinstance(m, QuantizationManager) and m.range_estimator is not None \
+                and m.range_estimator.current_xmin is not None:
+            est = m.range_estimator
+            dist.all_reduce(est.current_xmin, op=dist.ReduceOp.MIN, group=group)
+            dist.all_reduce(est.current_xmax, op=dist.ReduceOp.MAX, group=group)
+            m.set_quant_range(est.current_xmin, est.current_xmax)
+
+
+def calibrate(model, calib_batch, shard_calibration=False, group=None):
+    """estimate_ranges -> forward -> fix_ranges (image_net.py:100-112)."""
+    rank, world = _world(group)
+    model.quantized()
+    model.estimate_ranges()
+    x = calib_batch
+    if shard_calibration and world > 1:
+        lo, hi = shard_range(x.shape[0], rank, world)
+        x = x[lo:hi]
+    with torch.inference_mode():
+        out = model(x)
+    if shard_calibration:
+        sync_ranges(model, group)
+    model.fix_ranges()
+    return out
+
+
+def gather_rows(local, n_total, group=None):
+    """all_gather of per-rank row blocks of unequal size (pads to the largest block)."""
+    rank, world = _world(group)
+    if world == 1:
+        return local
+    sizes = [shard_range(n_total, r, world) for r in range(world)]
+    width = max(hi - lo for lo, hi in sizes)
+    padded = local.new_zeros((width,) + tuple(local.shape[1:]))
+    padded[: local.shape[0]] = local
+    out = local.new_empty((world * width,) + tuple(local.shape[1:]))
+    dist.all_gather_into_tensor(out, padded, group=group)
+    return torch.cat([out[r * width: r * width + (hi - lo)] for r, (lo, hi) in enumerate(sizes)], dim=0)
+
+
+def evaluate(model, images, labels=None, group=None):
+    """Forward this rank's slice of `images`, gather the logits of the whole batch on every rank.
+    Returns (logits [B, classes], metrics dict with top-1 / top-5 when labels are given)."""
+    rank, world = _world(group)
+    n = images.shape[0]
+    lo, hi = shard_range(n, rank, world)
+    with torch.inference_mode():
+        local = model(images[lo:hi]) if hi > lo else images.new_zeros((0, 1))
+    if world > 1 and hi == lo:     # an empty shard still has to take part in the collective
+        cls = torch.zeros(1, dtype=torch.int64, device=images.device)
+        dist.all_reduce(cls, op=dist.ReduceOp.MAX, group=group)
+        local = images.new_zeros((0, int(cls.item())))
+    elif world > 1:
+        cls = torch.tensor([local.shape[1]], dtype=torch.int64, device=images.device)
+        dist.all_reduce(cls, op=dist.ReduceOp.MAX, group=group)
+    logits = gather_rows(local.float().contiguous(), n, group)
+    metrics = {}
+    if labels is not None:
+        top5 = logits.topk(min(5, logits.shape[1]), dim=1).indices
+        metrics["top1"] = float((top5[:, 0] == labels).float().mean())
+        metrics["top5"] = float((top5 == labels[:, None]).any(dim=1).float().mean())
+    return logits, metrics

@@ -1,0 +1,80 @@
+"""GPU parity at model level (run with `-m gpu`): ResNet-18 and MobileNetV2 built by our mirror of the
+reference's graph surgery (fp8_quantization_b200/model_wrap.py) over the same seeded FP32 models,
+against tests/golden/models.npz -- produced by the UNMODIFIED reference wrappers on CPU
+(tests/golden/make_models.py).
+
+Two checks per model:
+  * teacher forcing: every tapped hot-path layer is fed the reference's own calibration and eval
+    inputs and must reproduce the reference's outputs (tolerance 1e-6 of the output scale: the approx
+    core is bit exact, BN / activation after it are plain fp32 torch on another device);
+  * end to end: logits of the whole network.  A 1-ulp difference in a BN output can move one
+    activation across an FP8 rounding boundary (one grid step, ~2^-M relative) in a later layer; in
+    practice the logits come out bit identical, and the test asserts 1e-6 of the logit scale.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import model_cases as mc
+
+pytestmark = pytest.mark.gpu
+# Round 1 on B200: 0.0 for all cases (the logits are bit identical to the reference's CPU run).
+END_TO_END_TOL = 1e-6
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "models.npz")
+
+
+def qparams(E, M):
+    return dict(method="fp_quantizer", act_method="fp_quantizer", n_bits=8, n_bits_act=8, per_channel_weights=True,
+                weight_range_method="current_minmax", act_range_method="allminmax", quantize_input=True,
+                fp8_kwargs=dict(mantissa_bits=M, set_maxval=True), custom_approx_params=mc.approx_params(E, M),
+                run_method=dict(mc.RUN_APPROX))
+
+
+def build(kind, size, E, M):
+    from fp8_quantization_b200 import model_wrap as mw
+    if kind == "resnet18":
+        model = mw.QuantizedResNet(mc.fp_resnet18(), **qparams(E, M))
+    else:
+        model = mw.QuantizedMobileNetV2(mc.fp_mobilenetv2(mw.MobileNetV2, size), **qparams(E, M))
+    return model.cuda().eval()
+
+
+@pytest.mark.parametrize("case", mc.MODEL_CASES, ids=[c[0] for c in mc.MODEL_CASES])
+def test_model_against_reference(case):
+    name, kind, size, batch, (E, M) = case
+    z = np.load(GOLD)
+    if f"{name}_yeval" not in z.files:
+        pytest.skip(f"{name}: golden logits not generated yet (tests/golden/make_models.py {name})")
+    model = build(kind, size, E, M)
+    dev = lambda a: torch.from_numpy(a).cuda()
+    mods = dict(model.named_modules())
+    bad = []
+    with torch.inference_mode():
+        model.quantized()
+        for lname in mc.TAPPED_LAYERS[name]:
+            layer = mods[lname]
+            layer.estimate_ranges()
+            got_cal = layer(dev(z[f"{name}_{lname}_xcal"]))
+            layer.fix_ranges()
+            got_eval = layer(dev(z[f"{name}_{lname}_xeval"]))
+            for tag, got in (("cal", got_cal), ("eval", got_eval)):
+                want = z[f"{name}_{lname}_y{tag}"]
+                got = got.contiguous().cpu().numpy()
+                tol = 1e-6 * float(np.abs(want).max())
+                err = float(np.abs(got.astype(np.float64) - want).max())
+                if got.shape != want.shape or err > tol:
+                    bad.append((lname, tag, err, tol))
+        assert not bad, bad
+        # end to end (fresh calibration of the whole network)
+        model.estimate_ranges()
+        y_cal = model(mc.images(batch, size, 1).cuda())
+        model.fix_ranges()
+        y_eval = model(mc.images(batch, size, 2).cuda())
+    for tag, got in (("cal", y_cal), ("eval", y_eval)):
+        want = z[f"{name}_y{tag}"]
+        err = float(np.abs(got.cpu().numpy().astype(np.float64) - want).max())
+        scale = float(np.abs(want).max())
+        print(f"{name} {tag}: end-to-end max |dlogit| = {err:.3e} (logit scale {scale:.3e})")
+        assert err <= END_TO_END_TOL * scale, (name, tag, err, scale)
