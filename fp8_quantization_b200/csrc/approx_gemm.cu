@@ -16,6 +16,7 @@
 // Accumulation: fp32, k ascending, one thread owns an output element for the whole K loop -- the
 // same order as the oracle, hence bit-identical to it; identical to the reference whenever fp32
 // summation is exact (always, in the calibrated quant_btw_mult_accu regime: DESIGN.md).
+#include <algorithm>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -178,13 +179,13 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
 }
 
 // ------------------------------------------------------------------------------------------------
-// Table-driven GEMM.  CTA tile (16*WARPS) x 128, one warp = 16 rows x 128 columns, one lane =
-// 16 rows x 4 consecutive columns (64 fp32 accumulators).  For a fixed k all lanes of a warp use the
-// same 16 A words (broadcast LDS.128) and their own 4 B words (one conflict-free LDS.128).
-// Operand tiles are staged through a 3-deep cp.async ring; the pair table lives in shared memory for
-// the life of the CTA.
+// Table-driven GEMM.  Template <WARPS, RPW, CPL>: CTA tile (RPW*WARPS) x (32*CPL); one warp =
+// RPW rows x 32*CPL columns; one lane = RPW rows x CPL consecutive columns (RPW*CPL = 64 or 32 fp32
+// accumulators).  For a fixed k all lanes of a warp use the same RPW A words (broadcast LDS.128) and
+// their own CPL B words (one conflict-free LDS.128 / LDS.64).  Operand tiles are staged through a
+// 3-deep cp.async ring; the pair table lives in shared memory for the life of the CTA.
+// Per MAC: IADD (table address) + LDS.U16 + FHFMA.BF16.
 // ------------------------------------------------------------------------------------------------
-constexpr int LUT_BN = 128;
 constexpr int LUT_KT = 16;
 constexpr int LUT_STAGES = 3;
 
@@ -223,10 +224,13 @@ struct LutGemmArgs {
     const int* offgrid;
 };
 
-template <int WARPS>
-__global__ void __launch_bounds__(32 * WARPS, (WARPS == 8) ? 2 : 1) approx_gemm_lut_kernel(LutGemmArgs a)
+template <int WARPS, int RPW, int CPL>
+__global__ void __launch_bounds__(32 * WARPS, (WARPS >= 16) ? 1 : ((RPW * CPL >= 64) ? 16 / WARPS : 24 / WARPS))
+approx_gemm_lut_kernel(LutGemmArgs a)
 {
-    constexpr int BM = 16 * WARPS, BN = LUT_BN, KT = LUT_KT, ST = LUT_STAGES, NTHR = 32 * WARPS;
+    constexpr int BM = RPW * WARPS, BN = 32 * CPL, KT = LUT_KT, ST = LUT_STAGES, NTHR = 32 * WARPS;
+    static_assert(CPL == 4 || CPL == 2, "a lane owns 2 or 4 consecutive columns");
+    static_assert(RPW % 4 == 0, "A words are read 4 at a time");
     if (*a.offgrid != 0) return;   // some operand is off the FP8 grid: the generic kernel takes over
     extern __shared__ __align__(16) unsigned char smem[];
     uint32_t* As = reinterpret_cast<uint32_t*>(smem + a.lut_bytes);   // [ST][KT][BM]
@@ -258,11 +262,11 @@ __global__ void __launch_bounds__(32 * WARPS, (WARPS == 8) ? 2 : 1) approx_gemm_
         }
     };
 
-    float acc[16][4];
+    float acc[RPW][CPL];
 #pragma unroll
-    for (int i = 0; i < 16; ++i)
+    for (int i = 0; i < RPW; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+        for (int j = 0; j < CPL; ++j) acc[i][j] = 0.0f;
 
     const int nk = a.Kpad / KT;
 #pragma unroll
@@ -275,27 +279,33 @@ __global__ void __launch_bounds__(32 * WARPS, (WARPS == 8) ? 2 : 1) approx_gemm_
         __syncthreads();
         if (kt + ST - 1 < nk) load_tile(kt + ST - 1, (kt + ST - 1) % ST);
         cp_async_commit();
-        const uint32_t* Asm = As + (kt % ST) * KT * BM + warp * 16;
-        const uint32_t* Bsm = Bs + (kt % ST) * KT * BN + lane * 4;
+        const uint32_t* Asm = As + (kt % ST) * KT * BM + warp * RPW;
+        const uint32_t* Bsm = Bs + (kt % ST) * KT * BN + lane * CPL;
 #pragma unroll 4
         for (int kk = 0; kk < KT; ++kk) {
-            const uint4 bq = *reinterpret_cast<const uint4*>(Bsm + kk * BN);
-            const uint32_t bw[4] = {bq.x, bq.y, bq.z, bq.w};
-            uint32_t bo[4];
-            unsigned short bm[4];
+            uint32_t bw[CPL];
+            if (CPL == 4) {
+                const uint4 bq = *reinterpret_cast<const uint4*>(Bsm + kk * BN);
+                bw[0] = bq.x; bw[1] = bq.y; bw[CPL - 2] = bq.z; bw[CPL - 1] = bq.w;
+            } else {
+                const uint2 bq = *reinterpret_cast<const uint2*>(Bsm + kk * BN);
+                bw[0] = bq.x; bw[1] = bq.y;
+            }
+            uint32_t bo[CPL];
+            unsigned short bm[CPL];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < CPL; ++j) {
                 bo[j] = (bw[j] & 0xFFFFu) + lut_base;          // table byte address of the (tB_idx, mB) part
                 bm[j] = (unsigned short)(bw[j] >> 16);         // bf16 sign of b
             }
 #pragma unroll
-            for (int i4 = 0; i4 < 4; ++i4) {
+            for (int i4 = 0; i4 < RPW / 4; ++i4) {
                 const uint4 aq = *reinterpret_cast<const uint4*>(Asm + kk * BM + i4 * 4);
                 const uint32_t aw[4] = {aq.x, aq.y, aq.z, aq.w};
 #pragma unroll
                 for (int ii = 0; ii < 4; ++ii) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) fma_bf16(acc[i4 * 4 + ii][j], lds_u16(aw[ii] + bo[j]), bm[j]);
+                    for (int j = 0; j < CPL; ++j) fma_bf16(acc[i4 * 4 + ii][j], lds_u16(aw[ii] + bo[j]), bm[j]);
                 }
             }
         }
@@ -304,22 +314,68 @@ __global__ void __launch_bounds__(32 * WARPS, (WARPS == 8) ? 2 : 1) approx_gemm_
 
     // epilogue: C = acc * u (exact power-of-two scaling)
     const float unit = pow2f_i(1 - a.bias.R() - a.M);
-    const int64_t n = n0 + lane * 4;
-    const bool vec = ((a.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.C) & 15) == 0) && (n + 3 < a.N);
+    const int64_t n = n0 + lane * CPL;
+    const bool vec = ((a.ldc & (CPL - 1)) == 0) && ((reinterpret_cast<uintptr_t>(a.C) & (4 * CPL - 1)) == 0) &&
+                     (n + CPL - 1 < a.N);
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        const int64_t m = m0 + warp * 16 + i;
+    for (int i = 0; i < RPW; ++i) {
+        const int64_t m = m0 + warp * RPW + i;
         if (m >= a.Mrows) break;
         float* crow = a.C + m * a.ldc;
-        if (vec) {
+        if (vec && CPL == 4) {
             *reinterpret_cast<float4*>(crow + n) =
-                make_float4(acc[i][0] * unit, acc[i][1] * unit, acc[i][2] * unit, acc[i][3] * unit);
+                make_float4(acc[i][0] * unit, acc[i][1] * unit, acc[i][CPL - 2] * unit, acc[i][CPL - 1] * unit);
+        } else if (vec) {
+            *reinterpret_cast<float2*>(crow + n) = make_float2(acc[i][0] * unit, acc[i][1] * unit);
         } else {
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
+            for (int j = 0; j < CPL; ++j)
                 if (n + j < a.N) crow[n + j] = acc[i][j] * unit;
         }
     }
+}
+
+// Tile configurations and the host-side choice between them.
+struct LutTileCfg {
+    int warps, rpw, cpl;
+    void (*kernel)(LutGemmArgs);
+    int BM() const { return warps * rpw; }
+    int BN() const { return 32 * cpl; }
+    size_t smem(int lut_bytes) const { return (size_t)lut_bytes + (size_t)LUT_STAGES * LUT_KT * (BM() + BN()) * 4; }
+};
+static const LutTileCfg kLutTiles[] = {
+    {8, 16, 4, approx_gemm_lut_kernel<8, 16, 4>},     // 128 x 128
+    {8, 32, 2, approx_gemm_lut_kernel<8, 32, 2>},     // 256 x  64   (N <= 64)
+    {4, 16, 4, approx_gemm_lut_kernel<4, 16, 4>},     //  64 x 128   (few rows)
+    {4, 32, 2, approx_gemm_lut_kernel<4, 32, 2>},     // 128 x  64
+    {4, 16, 2, approx_gemm_lut_kernel<4, 16, 2>},     //  64 x  64
+    {16, 16, 4, approx_gemm_lut_kernel<16, 16, 4>},   // 256 x 128   (large tables: one CTA per SM)
+};
+
+// Cost model: an SM's table-lookup rate saturates with 8 resident warps; a CTA's work is BM*BN per
+// k; CTAs are dealt round-robin over the SMs, `r` resident at a time.
+static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int lut_bytes, int sms)
+{
+    const LutTileCfg* best = nullptr;
+    double best_cost = 0;
+    for (const LutTileCfg& c : kLutTiles) {
+        const size_t sm = c.smem(lut_bytes) + 1024;
+        if (sm > 227 * 1024) continue;
+        int r = (int)((227 * 1024) / sm);
+        const int acc_regs = c.rpw * c.cpl >= 64 ? 128 : 80;
+        r = std::min(r, 65536 / (acc_regs * 32 * c.warps));
+        r = std::min(r, 64 / c.warps);
+        if (r < 1) continue;
+        const int64_t nc = ceil_div(Mrows, c.BM()) * ceil_div(N, c.BN());
+        const int64_t full = nc / ((int64_t)sms * r), rem = nc - full * sms * r;
+        const int rem_per_sm = (int)ceil_div(rem, sms);
+        const double T = (double)c.BM() * c.BN() * (c.cpl == 2 ? 1.06 : 1.0);
+        auto rate = [&](int ctas) { return std::min(1.0, ctas * c.warps / 8.0); };
+        double cost = full * r * T / rate(r);
+        if (rem_per_sm > 0) cost += rem_per_sm * T / rate(rem_per_sm);
+        if (!best || cost < best_cost) { best = &c; best_cost = cost; }
+    }
+    return best;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -407,10 +463,6 @@ static int get_lut(int E, int M, const signed char* host_table, const signed cha
     return B200_OK;
 }
 
-static size_t lut_gemm_smem(int warps, int lut_bytes)
-{
-    return (size_t)lut_bytes + (size_t)LUT_STAGES * LUT_KT * (16 * warps + LUT_BN) * 4;
-}
 
 // Optional per-launch timing of the dominant kernel (bench.py's roofline leg): CUDA events recorded
 // on the launching stream right around the table GEMM.
@@ -433,7 +485,7 @@ static void prof_record(bool start, cudaStream_t st)
     }
 }
 
-constexpr int64_t kPadM = 256, kPadN = LUT_BN, kPadK = 32;
+constexpr int64_t kPadM = 256, kPadN = 128, kPadK = 32;
 constexpr size_t kFlagBytes = 256;
 
 }  // namespace b200
@@ -510,7 +562,10 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     PredecodeArgs pa;
     pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
     pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
-    predecode_kernel<false, true><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, lut->geom);
+    // GEMM rows are k-contiguous (transpose through shared memory); an im2col view is contiguous along
+    // the output pixel, i.e. along rows: read and write row-fastest
+    if (A.conv) predecode_kernel<false, false><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, lut->geom);
+    else        predecode_kernel<false, true><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, lut->geom);
     B200_LAUNCH_CHECK("predecode_kernel<A>");
     PredecodeArgs pb = pa;
     pb.src = B; pb.s_row = sb_n; pb.s_k = sb_k; pb.dst = Bw; pb.rows = N; pb.Rpad = Npad;
@@ -525,23 +580,19 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     la.bias = bias; la.M = M;
     la.offgrid = flag;
     prof_record(true, st);
-    const size_t smem8 = lut_gemm_smem(8, lut->lut_bytes);
-    if (2 * (smem8 + 1024) <= 227 * 1024) {
-        static bool attr8 = false;
-        if (!attr8) {
-            B200_CUDA_TRY(cudaFuncSetAttribute(approx_gemm_lut_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
-            attr8 = true;
-        }
-        approx_gemm_lut_kernel<8><<<dim3((unsigned)(Mpad / 128), (unsigned)(Npad / LUT_BN)), 256, smem8, st>>>(la);
-    } else {
-        static bool attr16 = false;
-        if (!attr16) {
-            B200_CUDA_TRY(cudaFuncSetAttribute(approx_gemm_lut_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            attr16 = true;
-        }
-        approx_gemm_lut_kernel<16><<<dim3((unsigned)(Mpad / 256), (unsigned)(Npad / LUT_BN)), 512,
-                                     lut_gemm_smem(16, lut->lut_bytes), st>>>(la);
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+        for (const LutTileCfg& c : kLutTiles)
+            B200_CUDA_TRY(cudaFuncSetAttribute(c.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     }
+    const LutTileCfg* tc = choose_lut_tile(Mrows, N, lut->lut_bytes, sms);
+    if (!tc) { set_error("b200_approx_gemm: pair table does not fit shared memory"); return B200_ERR_ARGUMENT; }
+    tc->kernel<<<dim3((unsigned)ceil_div(Mrows, tc->BM()), (unsigned)ceil_div(N, tc->BN())), 32 * tc->warps,
+                 tc->smem(lut->lut_bytes), st>>>(la);
     prof_record(false, st);
     B200_LAUNCH_CHECK("approx_gemm_lut_kernel");
     // runs only if the predecode found an off-grid operand
