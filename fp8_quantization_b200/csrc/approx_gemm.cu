@@ -53,7 +53,7 @@ __global__ void lut_build_kernel(LutGeom g, const signed char* __restrict__ T, i
         const int idx_t = row % g.NT;
         const int q = row / g.NT;
         const int mA = q & ((1 << M) - 1);
-        const int sa = q >> M;
+        const int s0 = (q >> M) & 1;   // plain layout: [a<0]; signed-index layout: region & 1 = [a<0] xor [b<0]
         const int t = idx_t - g.RA - M - 2;
         if (idx_t > g.RA) {
             const FmtParam pR = make_param(g.E, M, 1 - M, false);   // unit space: u = 2^(1-bias-M) = 1
@@ -65,14 +65,14 @@ __global__ void lut_build_kernel(LutGeom g, const signed char* __restrict__ T, i
             float val[2];
 #pragma unroll
             for (int sb = 0; sb < 2; ++sb) {
-                const float sg = ((sa ^ sb) & 1) ? -1.0f : 1.0f;
+                const float sg = ((s0 ^ sb) & 1) ? -1.0f : 1.0f;
                 float gq = pex * scale * sg;                       // golden product, exact
                 gq = fpany_quant(pR, gq, clip_OF != 0);            // v9 :36
                 const float sgn = (gq < 0.0f) ? -1.0f : 1.0f;      // v9 :68
                 float r = scale * p * sgn;                         // v9 :73-77 (+ :79-80 folded in t)
                 val[sb] = fpany_quant(pR, r, clip_OF != 0);        // v9 :108
             }
-            if (val[1] != -val[0]) atomicAdd(&flags->sign_quirk, 1);   // not odd in the sign of b
+            if (!g.sidx && val[1] != -val[0]) atomicAdd(&flags->sign_quirk, 1);   // not odd in the sign of b
             const uint32_t bits = __float_as_uint(val[0]);
             if (bits & 0xFFFFu) atomicAdd(&flags->unrepresentable, 1);
             out = (uint16_t)(bits >> 16);
@@ -120,7 +120,8 @@ __device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int b
 {
     const uint32_t bits = __float_as_uint(v);
     const uint32_t mag = bits & 0x7FFFFFFFu;
-    if (mag == 0) return kBf16One << 16;                      // tB_idx = 0: every product rounds to 0
+    const uint32_t zero_b = g.sidx ? 0u : (kBf16One << 16);   // tB_idx = 0: every product rounds to 0
+    if (mag == 0) return zero_b;
     const int M = g.M;
     const int L = (int)(mag >> 23) - 127;
     const uint32_t frac = mag & 0x7FFFFFu;
@@ -128,12 +129,14 @@ __device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int b
     if ((frac & ((1u << (23 - M)) - 1u)) != 0 || L < 1 - bB - M || (mag >> 23) == 0 || (mag >> 23) == 255 ||
         tB + g.RA > g.NTB - 1 || (1 - bA - M) + (1 - bB - M) < -120) {
         off = 1;
-        return kBf16One << 16;
+        return zero_b;
     }
     if (tB < -g.RA) tB = -g.RA;
     const uint32_t mB = frac >> (23 - M);
+    const uint32_t boff = 2u * (mB + (uint32_t)(g.row_entries * (tB + g.RA)));
+    if (g.sidx) return boff + ((bits >> 31) ? 2u * (uint32_t)g.s_stride : 0u);   // sign of b selects a region
     const uint32_t mult = (bits >> 31) ? kBf16MinusOne : kBf16One;
-    return (mult << 16) | (2u * (mB + (uint32_t)(g.row_entries * (tB + g.RA))));
+    return (mult << 16) | boff;
 }
 
 // 32x32 tile transpose: reads along k (SRC_K_CONTIG) or along rows, writes along rows.
@@ -150,7 +153,7 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int64_t r = r0 + ty + i * 8, k = k0 + tx;
-            uint32_t w = IS_B ? (kBf16One << 16) : 2u * (uint32_t)g.zeroA_off;
+            uint32_t w = IS_B ? (g.sidx ? 0u : (kBf16One << 16)) : 2u * (uint32_t)g.zeroA_off;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
                 w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off) : predecode_a(g, v, bA, off);
@@ -167,7 +170,7 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int64_t k = k0 + ty + i * 8, r = r0 + tx;
-            uint32_t w = IS_B ? (kBf16One << 16) : 2u * (uint32_t)g.zeroA_off;
+            uint32_t w = IS_B ? (g.sidx ? 0u : (kBf16One << 16)) : 2u * (uint32_t)g.zeroA_off;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
                 w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off) : predecode_a(g, v, bA, off);
@@ -186,7 +189,6 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
 // 3-deep cp.async ring; the pair table lives in shared memory for the life of the CTA.
 // Per MAC: IADD (table address) + LDS.U16 + FHFMA.BF16.
 // ------------------------------------------------------------------------------------------------
-constexpr int LUT_KT = 16;
 constexpr int LUT_STAGES = 3;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -202,6 +204,36 @@ __device__ __forceinline__ unsigned short lds_u16(uint32_t addr)
 __device__ __forceinline__ void fma_bf16(float& acc, unsigned short e, unsigned short m)
 {
     asm("fma.rn.f32.bf16 %0, %1, %2, %0;" : "+f"(acc) : "h"(e), "h"(m));
+}
+// One A element against CPL B elements: table address add, 16-bit table load, fp32 += bf16 * bf16,
+// skipped as a whole when a == 0.  The test is warp-uniform (all lanes of a warp hold the same A
+// word), which `bra.uni` tells ptxas: a plain branch, no BSSY/BSYNC reconvergence pair.  Zero
+// activations -- about half of a post-ReLU tensor -- issue no shared-memory lookups at all.
+__device__ __forceinline__ void mac_row4(float& c0, float& c1, float& c2, float& c3, uint32_t aw, uint32_t zero_word,
+                                         uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3, unsigned short m0,
+                                         unsigned short m1, unsigned short m2, unsigned short m3)
+{
+    asm("{\n\t.reg .pred p;\n\t.reg .b16 e0, e1, e2, e3;\n\t.reg .u32 x0, x1, x2, x3;\n\t"
+        "setp.ne.u32 p, %4, %5;\n\t"
+        "add.u32 x0, %4, %6;\n\tadd.u32 x1, %4, %7;\n\tadd.u32 x2, %4, %8;\n\tadd.u32 x3, %4, %9;\n\t"
+        "@p ld.shared.u16 x0, [x0];\n\t@p ld.shared.u16 x1, [x1];\n\t@p ld.shared.u16 x2, [x2];\n\t@p ld.shared.u16 x3, [x3];\n\t"
+        "cvt.u16.u32 e0, x0;\n\tcvt.u16.u32 e1, x1;\n\tcvt.u16.u32 e2, x2;\n\tcvt.u16.u32 e3, x3;\n\t"
+        "@p fma.rn.f32.bf16 %0, e0, %10, %0;\n\t@p fma.rn.f32.bf16 %1, e1, %11, %1;\n\t"
+        "@p fma.rn.f32.bf16 %2, e2, %12, %2;\n\t@p fma.rn.f32.bf16 %3, e3, %13, %3;\n\t}"
+        : "+f"(c0), "+f"(c1), "+f"(c2), "+f"(c3)
+        : "r"(aw), "r"(zero_word), "r"(b0), "r"(b1), "r"(b2), "r"(b3), "h"(m0), "h"(m1), "h"(m2), "h"(m3));
+}
+__device__ __forceinline__ void mac_row2(float& c0, float& c1, uint32_t aw, uint32_t zero_word, uint32_t b0,
+                                         uint32_t b1, unsigned short m0, unsigned short m1)
+{
+    asm("{\n\t.reg .pred p;\n\t.reg .b16 e0, e1;\n\t.reg .u32 x0, x1;\n\t"
+        "setp.ne.u32 p, %2, %3;\n\t"
+        "add.u32 x0, %2, %4;\n\tadd.u32 x1, %2, %5;\n\t"
+        "@p ld.shared.u16 x0, [x0];\n\t@p ld.shared.u16 x1, [x1];\n\t"
+        "cvt.u16.u32 e0, x0;\n\tcvt.u16.u32 e1, x1;\n\t"
+        "@p fma.rn.f32.bf16 %0, e0, %6, %0;\n\t@p fma.rn.f32.bf16 %1, e1, %7, %1;\n\t}"
+        : "+f"(c0), "+f"(c1)
+        : "r"(aw), "r"(zero_word), "r"(b0), "r"(b1), "h"(m0), "h"(m1));
 }
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src)
 {
@@ -221,14 +253,17 @@ struct LutGemmArgs {
     int lut_bytes;        // multiple of 16
     BiasSrc bias;
     int M;                // unit u = 2^(1 - bR - M)
+    uint32_t zero_word;   // the A word of a == 0
     const int* offgrid;
 };
 
-template <int WARPS, int RPW, int CPL>
+// KT: k-tile depth (8 where a large table leaves little shared memory for the operand ring).
+// SIDX: signed-index table layout (lut.cuh): the B word is a full 32-bit byte offset, multiplier +1.0.
+template <int WARPS, int RPW, int CPL, int KT, bool SIDX>
 __global__ void __launch_bounds__(32 * WARPS, (WARPS >= 16) ? 1 : ((RPW * CPL >= 64) ? 16 / WARPS : 24 / WARPS))
 approx_gemm_lut_kernel(LutGemmArgs a)
 {
-    constexpr int BM = RPW * WARPS, BN = 32 * CPL, KT = LUT_KT, ST = LUT_STAGES, NTHR = 32 * WARPS;
+    constexpr int BM = RPW * WARPS, BN = 32 * CPL, ST = LUT_STAGES, NTHR = 32 * WARPS;
     static_assert(CPL == 4 || CPL == 2, "a lane owns 2 or 4 consecutive columns");
     static_assert(RPW % 4 == 0, "A words are read 4 at a time");
     if (*a.offgrid != 0) return;   // some operand is off the FP8 grid: the generic kernel takes over
@@ -269,6 +304,7 @@ approx_gemm_lut_kernel(LutGemmArgs a)
         for (int j = 0; j < CPL; ++j) acc[i][j] = 0.0f;
 
     const int nk = a.Kpad / KT;
+    const uint32_t zero_word = a.zero_word;
 #pragma unroll
     for (int s = 0; s < ST - 1; ++s) {
         if (s < nk) load_tile(s, s);
@@ -281,7 +317,7 @@ approx_gemm_lut_kernel(LutGemmArgs a)
         cp_async_commit();
         const uint32_t* Asm = As + (kt % ST) * KT * BM + warp * RPW;
         const uint32_t* Bsm = Bs + (kt % ST) * KT * BN + lane * CPL;
-#pragma unroll 4
+#pragma unroll (KT >= 16 ? 4 : 2)
         for (int kk = 0; kk < KT; ++kk) {
             uint32_t bw[CPL];
             if (CPL == 4) {
@@ -295,8 +331,8 @@ approx_gemm_lut_kernel(LutGemmArgs a)
             unsigned short bm[CPL];
 #pragma unroll
             for (int j = 0; j < CPL; ++j) {
-                bo[j] = (bw[j] & 0xFFFFu) + lut_base;          // table byte address of the (tB_idx, mB) part
-                bm[j] = (unsigned short)(bw[j] >> 16);         // bf16 sign of b
+                bo[j] = (SIDX ? bw[j] : (bw[j] & 0xFFFFu)) + lut_base;   // table byte address of the (tB_idx, mB) part
+                bm[j] = SIDX ? (unsigned short)kBf16One : (unsigned short)(bw[j] >> 16);   // bf16 sign of b
             }
 #pragma unroll
             for (int i4 = 0; i4 < RPW / 4; ++i4) {
@@ -304,8 +340,11 @@ approx_gemm_lut_kernel(LutGemmArgs a)
                 const uint32_t aw[4] = {aq.x, aq.y, aq.z, aq.w};
 #pragma unroll
                 for (int ii = 0; ii < 4; ++ii) {
-#pragma unroll
-                    for (int j = 0; j < CPL; ++j) fma_bf16(acc[i4 * 4 + ii][j], lds_u16(aw[ii] + bo[j]), bm[j]);
+                    if (CPL == 4) mac_row4(acc[i4 * 4 + ii][0], acc[i4 * 4 + ii][1], acc[i4 * 4 + ii][CPL - 2],
+                                           acc[i4 * 4 + ii][CPL - 1], aw[ii], zero_word, bo[0], bo[1], bo[CPL - 2],
+                                           bo[CPL - 1], bm[0], bm[1], bm[CPL - 2], bm[CPL - 1]);
+                    else          mac_row2(acc[i4 * 4 + ii][0], acc[i4 * 4 + ii][1], aw[ii], zero_word, bo[0], bo[1],
+                                           bm[0], bm[1]);
                 }
             }
         }
@@ -337,28 +376,36 @@ approx_gemm_lut_kernel(LutGemmArgs a)
 
 // Tile configurations and the host-side choice between them.
 struct LutTileCfg {
-    int warps, rpw, cpl;
+    int warps, rpw, cpl, kt, sidx;
     void (*kernel)(LutGemmArgs);
     int BM() const { return warps * rpw; }
     int BN() const { return 32 * cpl; }
-    size_t smem(int lut_bytes) const { return (size_t)lut_bytes + (size_t)LUT_STAGES * LUT_KT * (BM() + BN()) * 4; }
+    size_t smem(int lut_bytes) const { return (size_t)lut_bytes + (size_t)LUT_STAGES * kt * (BM() + BN()) * 4; }
 };
+#define LUT_TILE(W, R, C, KT, S) {W, R, C, KT, S, approx_gemm_lut_kernel<W, R, C, KT, (S) != 0>}
 static const LutTileCfg kLutTiles[] = {
-    {8, 16, 4, approx_gemm_lut_kernel<8, 16, 4>},     // 128 x 128
-    {8, 32, 2, approx_gemm_lut_kernel<8, 32, 2>},     // 256 x  64   (N <= 64)
-    {4, 16, 4, approx_gemm_lut_kernel<4, 16, 4>},     //  64 x 128   (few rows)
-    {4, 32, 2, approx_gemm_lut_kernel<4, 32, 2>},     // 128 x  64
-    {4, 16, 2, approx_gemm_lut_kernel<4, 16, 2>},     //  64 x  64
-    {16, 16, 4, approx_gemm_lut_kernel<16, 16, 4>},   // 256 x 128   (large tables: one CTA per SM)
+    LUT_TILE(8, 16, 4, 16, 0),    // 128 x 128
+    LUT_TILE(8, 32, 2, 16, 0),    // 256 x  64   (N <= 64)
+    LUT_TILE(4, 16, 4, 16, 0),    //  64 x 128   (few rows)
+    LUT_TILE(4, 32, 2, 16, 0),    // 128 x  64
+    LUT_TILE(4, 16, 2, 16, 0),    //  64 x  64
+    LUT_TILE(16, 16, 4, 16, 0),   // 256 x 128   (large tables: one CTA per SM)
+    // signed-index tables (three sign regions, up to 176 KB for E2M5)
+    LUT_TILE(16, 16, 4, 8, 1),    // 256 x 128, shallow k tile
+    LUT_TILE(8, 16, 4, 8, 1),     // 128 x 128
+    LUT_TILE(8, 16, 4, 16, 1),
+    LUT_TILE(4, 16, 4, 16, 1),
+    LUT_TILE(4, 16, 2, 16, 1),
 };
 
 // Cost model: an SM's table-lookup rate saturates with 8 resident warps; a CTA's work is BM*BN per
 // k; CTAs are dealt round-robin over the SMs, `r` resident at a time.
-static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int lut_bytes, int sms)
+static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int lut_bytes, int sidx, int sms)
 {
     const LutTileCfg* best = nullptr;
     double best_cost = 0;
     for (const LutTileCfg& c : kLutTiles) {
+        if (c.sidx != sidx) continue;
         const size_t sm = c.smem(lut_bytes) + 1024;
         if (sm > 227 * 1024) continue;
         int r = (int)((227 * 1024) / sm);
@@ -369,7 +416,7 @@ static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int lut_bytes
         const int64_t nc = ceil_div(Mrows, c.BM()) * ceil_div(N, c.BN());
         const int64_t full = nc / ((int64_t)sms * r), rem = nc - full * sms * r;
         const int rem_per_sm = (int)ceil_div(rem, sms);
-        const double T = (double)c.BM() * c.BN() * (c.cpl == 2 ? 1.06 : 1.0);
+        const double T = (double)c.BM() * c.BN() * (c.cpl == 2 ? 1.06 : 1.0) * (c.kt < 16 ? 1.05 : 1.0);
         auto rate = [&](int ctas) { return std::min(1.0, ctas * c.warps / 8.0); };
         double cost = full * r * T / rate(r);
         if (rem_per_sm > 0) cost += rem_per_sm * T / rate(rem_per_sm);
@@ -435,6 +482,23 @@ int device_table(const signed char* host, int M, const signed char** dev_out)
 }
 
 // Builds (once per configuration and device) the pair table of lut.cuh.  First use synchronises.
+static int build_lut(int E, int M, const signed char* dev_table, int with_approx, int clip_OF, bool sidx, LutEntry* e)
+{
+    e->geom = make_lut_geom(E, M, sidx);
+    e->lut_bytes = (int)round_up((int64_t)e->geom.total_entries * 2, 16);
+    LutFlags* d_flags = nullptr;
+    B200_CUDA_TRY(cudaMalloc(&e->d_lut, e->lut_bytes));
+    B200_CUDA_TRY(cudaMalloc(&d_flags, sizeof(LutFlags)));
+    B200_CUDA_TRY(cudaMemset(e->d_lut, 0, e->lut_bytes));
+    B200_CUDA_TRY(cudaMemset(d_flags, 0, sizeof(LutFlags)));
+    lut_build_kernel<<<(int)ceil_div(e->geom.total_entries, 256), 256>>>(e->geom, dev_table, dev_table != nullptr,
+                                                                        with_approx, clip_OF, e->d_lut, d_flags);
+    B200_LAUNCH_CHECK("lut_build_kernel");
+    B200_CUDA_TRY(cudaMemcpy(&e->flags, d_flags, sizeof(LutFlags), cudaMemcpyDeviceToHost));
+    cudaFree(d_flags);
+    return B200_OK;
+}
+
 static int get_lut(int E, int M, const signed char* host_table, const signed char* dev_table, int with_approx,
                    int clip_OF, const LutEntry** out)
 {
@@ -445,18 +509,13 @@ static int get_lut(int E, int M, const signed char* host_table, const signed cha
     auto it = g_luts.find(key);
     if (it == g_luts.end()) {
         LutEntry e;
-        e.geom = make_lut_geom(E, M);
-        e.lut_bytes = (int)round_up((int64_t)e.geom.total_entries * 2, 16);
-        LutFlags* d_flags = nullptr;
-        B200_CUDA_TRY(cudaMalloc(&e.d_lut, e.lut_bytes));
-        B200_CUDA_TRY(cudaMalloc(&d_flags, sizeof(LutFlags)));
-        B200_CUDA_TRY(cudaMemset(e.d_lut, 0, e.lut_bytes));
-        B200_CUDA_TRY(cudaMemset(d_flags, 0, sizeof(LutFlags)));
-        lut_build_kernel<<<(int)ceil_div(e.geom.total_entries, 256), 256>>>(e.geom, dev_table, dev_table != nullptr,
-                                                                           with_approx, clip_OF, e.d_lut, d_flags);
-        B200_LAUNCH_CHECK("lut_build_kernel");
-        B200_CUDA_TRY(cudaMemcpy(&e.flags, d_flags, sizeof(LutFlags), cudaMemcpyDeviceToHost));
-        cudaFree(d_flags);
+        if (int rc = build_lut(E, M, dev_table, with_approx, clip_OF, false, &e)) return rc;
+        if (e.flags.sign_quirk && !e.flags.unrepresentable) {
+            // not odd in the operand signs: rebuild with both signs in the index (lut.cuh)
+            cudaFree(e.d_lut);
+            e = LutEntry();
+            if (int rc = build_lut(E, M, dev_table, with_approx, clip_OF, true, &e)) return rc;
+        }
         it = g_luts.emplace(key, e).first;
     }
     *out = &it->second;
@@ -578,6 +637,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     la.Aw = Aw; la.Bw = Bw; la.lut = lut->d_lut; la.C = C; la.ldc = ldc; la.Mrows = Mrows; la.N = N;
     la.Mpad = Mpad; la.Npad = Npad; la.Kpad = (int)Kpad; la.lut_bytes = lut->lut_bytes;
     la.bias = bias; la.M = M;
+    la.zero_word = 2u * (uint32_t)lut->geom.zeroA_off;
     la.offgrid = flag;
     prof_record(true, st);
     static int sms = 0;
@@ -589,7 +649,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
         for (const LutTileCfg& c : kLutTiles)
             B200_CUDA_TRY(cudaFuncSetAttribute(c.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     }
-    const LutTileCfg* tc = choose_lut_tile(Mrows, N, lut->lut_bytes, sms);
+    const LutTileCfg* tc = choose_lut_tile(Mrows, N, lut->lut_bytes, lut->geom.sidx, sms);
     if (!tc) { set_error("b200_approx_gemm: pair table does not fit shared memory"); return B200_ERR_ARGUMENT; }
     tc->kernel<<<dim3((unsigned)ceil_div(Mrows, tc->BM()), (unsigned)ceil_div(N, tc->BN())), 32 * tc->warps,
                  tc->smem(lut->lut_bytes), st>>>(la);
@@ -598,7 +658,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     // runs only if the predecode found an off-grid operand
     pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<ApproxPairOp>(conditional)");
-    set_path("lut");
+    set_path(lut->geom.sidx ? "lut-signed" : "lut");
     return B200_OK;
 }
 

@@ -35,9 +35,17 @@ struct LutGeom {
     int a_stride;    // entries per (sa, mA) value: NT * row_entries
     int zeroA_off;   // entry offset of the all-zero region for a == 0
     int total_entries;
+    int sidx;        // 1: "signed index" layout for tables that are not odd in the operand signs
+    int s_stride;    // entries per sign region: a_stride * 2^M
 };
 
-__host__ __device__ inline LutGeom make_lut_geom(int E, int M)
+// Signed-index layout (sidx): the addend depends on the signs only through s = [a<0] xor [b<0], but for
+// a few cells at the round-to-zero edge of one table (E2M5, withComp, dnsmp 3) it is NOT odd in s: the
+// reference takes the sign from a golden product that already rounded to zero
+// (approx_matmul_whole_v9.py:68 after :36).  There the sign of b cannot ride on the FHFMA multiplier.
+// Both signs go into the index instead, additively: [a<0]*S + [b<0]*S selects one of THREE regions
+// (s = 0, s = 1, and a second copy of s = 0 for 1+1), each [mA][t][mB]; the multiplier is +1.0.
+__host__ __device__ inline LutGeom make_lut_geom(int E, int M, bool sidx = false)
 {
     LutGeom g;
     g.E = E;
@@ -48,7 +56,9 @@ __host__ __device__ inline LutGeom make_lut_geom(int E, int M)
     g.NT = g.RA + g.NTB;
     g.row_entries = 1 << M;
     g.a_stride = g.NT * g.row_entries;
-    g.zeroA_off = g.a_stride * (2 << M);
+    g.sidx = sidx ? 1 : 0;
+    g.s_stride = g.a_stride << M;
+    g.zeroA_off = g.s_stride * (sidx ? 3 : 2);
     g.total_entries = g.zeroA_off + g.NTB * g.row_entries;
     return g;
 }

@@ -114,8 +114,9 @@ def _grid_sample(rng, E, M, bias, shape, zero_frac, spread=None):
 
 # (E, M, dnsmp_factor, expected kernel path).  E2M5 / withComp / dnsmp 3 selects the one table whose
 # pair function is not odd in the operand signs (4 cells at the round-to-zero edge, v9 :68 after :36):
-# the library detects that when it builds the pair table and keeps the arithmetic kernel for it.
-@pytest.mark.parametrize("fmt", [(4, 3, 3, "lut"), (3, 4, 3, "lut"), (2, 5, 4, "lut"), (2, 5, 3, "generic")])
+# the library detects that when it builds the pair table and switches to the signed-index table
+# layout (both operand signs in the table index, csrc/lut.cuh).
+@pytest.mark.parametrize("fmt", [(4, 3, 3, "lut"), (3, 4, 3, "lut"), (2, 5, 4, "lut"), (2, 5, 3, "lut-signed")])
 @pytest.mark.parametrize("shape", [(300, 200, 130), (129, 1000, 257), (64, 4096, 40)])
 def test_gemm_vs_oracle(fq, fmt, shape):
     """Ragged shapes (not multiples of the tile), weight.t() views, per-column bias: table kernel vs

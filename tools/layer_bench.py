@@ -1,0 +1,93 @@
+#!/usr/bin/env python
+"""Per-shape timing of the approx GEMM over the GEMM shapes of a model.
+
+  python tools/layer_bench.py --model resnet18 --batch 32 [--zero-frac 0.5] [--mant-width 3]
+For every distinct (Mrows, K, N): whole call (predecode + table GEMM) and the table GEMM alone
+(CUDA events on the launching stream), in ms and T approx-MAC/s.  Operands are sampled on the FP8
+grid; `--zero-frac` of the activations are zero (post-ReLU tensors are about half zeros)."""
+import argparse
+import ctypes
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+# (count, Mrows per image, K, N)
+SHAPES = {
+    "resnet18": [(1, 12544, 147, 64), (4, 3136, 576, 64), (1, 784, 576, 128), (3, 784, 1152, 128),
+                 (1, 196, 1152, 256), (3, 196, 2304, 256), (1, 49, 2304, 512), (3, 49, 4608, 512),
+                 (1, 784, 64, 128), (1, 196, 128, 256), (1, 49, 256, 512)],
+    "vit_b16": [(48, 197, 768, 768), (12, 197, 768, 3072), (12, 197, 3072, 768)],
+    "mobilenetv2_pw": [(1, 12544, 32, 16), (1, 12544, 16, 96), (1, 3136, 96, 24), (2, 3136, 24, 144),
+                       (1, 3136, 144, 24), (1, 784, 144, 32), (3, 784, 32, 192), (2, 784, 192, 32),
+                       (1, 196, 192, 64), (4, 196, 64, 384), (3, 196, 384, 64), (1, 196, 384, 96),
+                       (3, 196, 96, 576), (2, 196, 576, 96), (1, 49, 576, 160), (3, 49, 160, 960),
+                       (2, 49, 960, 160), (1, 49, 960, 320), (1, 49, 320, 1280)],
+    "square": [(1, 4096, 4096, 4096)],
+}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="resnet18", choices=sorted(SHAPES))
+    ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--mant-width", type=int, default=3)
+    ap.add_argument("--zero-frac", type=float, default=0.5)
+    ap.add_argument("--steps", type=int, default=5)
+    a = ap.parse_args()
+    import torch
+    import fp8_quantization_b200 as pkg
+    from fp8_quantization_b200 import ops
+    lib = pkg._lib.load()
+    dev = torch.device("cuda", 0)
+    M = a.mant_width
+    E = 7 - M
+    params = ops.make_params(dict(expo_width=E, mant_width=M, dnsmp_factor=3, withComp=True, with_approx=True,
+                                  with_s2nn2s_opt=True, quant_btw_mult_accu=True))
+    g = torch.Generator(device="cpu").manual_seed(10)
+    mant = torch.tensor([float(M)])
+    tot_ms = tot_kern = tot_macs = 0.0
+    for cnt, mr, K, N in SHAPES[a.model]:
+        rows = mr * (a.batch if a.model != "square" else 1)
+        x = torch.randn(rows, K, generator=g).abs_() * 0.5
+        x[torch.rand(rows, K, generator=g) < a.zero_frac] = 0.0
+        w = torch.randn(N, K, generator=g) * 0.05
+        x, w = x.to(dev), w.to(dev)
+        xq, bA = ops.fp8_fakequant(x, 8, x.abs().max().reshape(1), mant, 1)
+        wq, bB = ops.fp8_fakequant(w, 8, w.abs().amax(dim=1), mant, 1)
+        ref = xq[:64] @ wq.t()
+        _, bR = ops.fp8_fakequant(ref, 8, (ref.abs().max() * 2).reshape(1), mant, 1)
+        out = torch.empty((rows, N), device=dev)
+        step = lambda: ops.approx_matmul(xq, wq.t(), bA, bB, bR, params, out=out)
+        for _ in range(2):
+            step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(a.steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / a.steps
+        lib.b200_profile_begin()
+        for _ in range(a.steps):
+            step()
+        t, c = ctypes.c_double(0), ctypes.c_int(0)
+        lib.b200_profile_end(ctypes.byref(t), ctypes.byref(c))
+        kms = t.value / max(c.value, 1)
+        macs = rows * K * N
+        print(json.dumps({"rows": rows, "K": K, "N": N, "count": cnt, "path": ops.last_path(), "ms": round(ms, 4),
+                          "gemm_ms": round(kms, 4), "tmacs": round(macs / ms / 1e9, 3),
+                          "gemm_tmacs": round(macs / kms / 1e9, 3) if kms else None}), flush=True)
+        tot_ms += cnt * ms
+        tot_kern += cnt * kms
+        tot_macs += cnt * macs
+    print(json.dumps({"model": a.model, "batch": a.batch, "format": f"E{E}M{M}", "zero_frac": a.zero_frac,
+                      "sum_ms": round(tot_ms, 3), "sum_gemm_ms": round(tot_kern, 3),
+                      "tmacs": round(tot_macs / tot_ms / 1e9, 3)}))
+
+
+if __name__ == "__main__":
+    main()
