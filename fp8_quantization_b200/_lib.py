@@ -65,6 +65,9 @@ SIGNATURES = {
                                        c_i64, c_vp, ctypes.POINTER(ApproxParams), c_vp, c_sz, c_vp]),
     "b200_qamaa_gemm": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_int, c_f32,
                                 c_int, c_vp]),
+    "b200_fq_gemm_tc_workspace_bytes": (c_sz, [c_i64, c_i64, c_i64]),
+    "b200_fq_gemm_tc": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_sz,
+                                c_vp]),
     "b200_conv_out_shape": (c_int, [ctypes.POINTER(ConvGeom), ctypes.POINTER(c_i64), ctypes.POINTER(ctypes.c_int32),
                                     ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32),
                                     ctypes.POINTER(ctypes.c_int32)]),

@@ -35,15 +35,16 @@ class _ApproxMixin:
             if self.quantize_after_mult_and_add:
                 q = self.res_quantizer.quantizer
                 return ops.qamaa_matmul(x, y, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits)
-            return x @ y
+            return ops.fq_matmul(x, y)               # `x @ y[:, i]` per column (:968-969): tcgen05
         # single output column (every depthwise group): int32-TENSOR biases in the reference
         # (:985-994) -> integer-pow numerics, no quantize_after_mult_and_add branch
         if self.approx_flag:
             return ops.approx_matmul(x, y, x_bias, y_bias, res_bias, self._params(True))
-        return x @ y
+        return ops.fq_matmul(x, y)
 
     def multiply(self, x, y):
-        return torch.matmul(x, y)
+        """`self.multiply` = torch.matmul in the reference (:704-705); 2-D operands go to the tensor cores."""
+        return ops.fq_matmul(x, y)
 
 
 class QCustomLinearTorch(_ApproxMixin, QuantizationHijacker, nn.Linear):

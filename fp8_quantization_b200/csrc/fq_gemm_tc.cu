@@ -1,0 +1,396 @@
+// fq_gemm_tc.cu -- K3: the NON-approx matmul of fake-quantized operands on the 5th-generation tensor
+// cores.
+//
+// Replaces `x @ y[:, i:i+1]` per column (approx/approx_calculation.py:968-969, :796-797, :996) and
+// `self.multiply` = torch.matmul (:704-705, conv without BN).
+//
+// Why tensor cores are legal here and only here: with approx_flag == False there is no per-product
+// bit manipulation and no re-quantisation between the multiply and the add -- the layer is a plain
+// contraction of fake-quantized operands.  Those operands carry <= 6 significant bits (mant_width <= 5
+// plus the hidden one) and an fp32-range exponent, so they convert to bf16 EXACTLY; bf16 x bf16
+// products are exact in fp32; only the fp32 accumulation order differs from the reference's
+// (cuBLAS/MKL sgemm, itself unspecified).  Stated tolerance: |C - ref| <= 1e-6 * sum_k |a_k b_k|.
+// Hardware FP8 (kind::f8f6f4) is NOT used: e4m3/e5m2 reserve exponent codes for NaN/Inf while the
+// reference's grid (fp8_quantizer.py:13-41) uses all of them and moves the bias per channel.
+//
+// Pipeline:  convert pass (fp32 -> bf16 planes, K padded to 64, raises a flag if ANY operand is not
+// exactly representable)  ->  fq_gemm_tc_kernel: TMA (128B swizzle) -> 4-stage shared-memory ring ->
+// tcgen05.mma kind::f16 issued by one thread, fp32 accumulator in TMEM -> tcgen05.ld epilogue
+// (+bias) -> fp32 stores.  If the flag is up (operands not fake-quantized), the tensor-core kernel
+// exits at once and an fp32 CUDA-core kernel computes the product instead: still no CPU path.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <mutex>
+
+#include "common.cuh"
+#include "pair_gemm.cuh"
+
+namespace b200 {
+
+constexpr int TC_BM = 128;      // UMMA M (cta_group::1): TMEM lane i <-> tile row i
+constexpr int TC_BK = 64;       // one 128-byte swizzle row of bf16
+constexpr int TC_UK = 16;       // K per tcgen05.mma kind::f16
+constexpr int TC_THREADS = 256; // warp 0: TMA, warp 1: MMA, warp 2: TMEM alloc, warps 4-7: epilogue
+
+// ---- PTX wrappers ----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "DONE:\n\t}" ::"r"(s32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(s32(dst)), "l"(map), "r"(s32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s32(bar)) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem], bf16 operands, fp32 accumulate
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (thread = TMEM lane = tile row)
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor of a K-major tile stored as TMA's 128-byte swizzle writes it:
+// row r at byte r*128, 16-byte chunks XOR-ed with (r & 7); 8-row groups are 1024 B apart (SBO).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3FFFu);          // start address, 16-byte units
+    d |= (uint64_t)0 << 16;                               // leading byte offset: unused for swizzled K-major
+    d |= (uint64_t)((1024u >> 4) & 0x3FFFu) << 32;        // stride byte offset: 8 rows * 128 B
+    d |= (uint64_t)1 << 46;                               // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                               // layout type: SWIZZLE_128B
+    return d;
+}
+// Instruction descriptor, kind::f16: D fp32, A/B bf16, both K-major, M x N tile.
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N)
+{
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---- the tensor-core kernel --------------------------------------------------------------------
+template <int BN, int ST>
+struct TcSmem {
+    static constexpr int A_BYTES = TC_BM * TC_BK * 2;        // 16 KB
+    static constexpr int B_BYTES = BN * TC_BK * 2;
+    static constexpr int STAGE = A_BYTES + B_BYTES;
+    static constexpr int BARS = ST * STAGE;                  // full[ST], empty[ST], tmem_full, then the TMEM base
+    static constexpr int TOTAL = BARS + (2 * ST + 1) * 8 + 16 + 1024;   // + slack for the 1024 B alignment
+};
+
+template <int BN, int ST>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+                  float* __restrict__ C, int64_t ldc, int64_t Mrows, int64_t N, int nkb,
+                  const float* __restrict__ bias, const int* __restrict__ inexact)
+{
+    if (*inexact != 0) return;   // an operand does not fit bf16 exactly: the fp32 kernel takes over
+    using L = TcSmem<BN, ST>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::BARS);
+    uint64_t* empty = full + ST;
+    uint64_t* tmem_full = empty + ST;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * BN;
+
+    if (threadIdx.x == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < ST; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        mbar_init(tmem_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {   // one warp allocates BN fp32 accumulator columns of tensor memory
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(tmem_slot)), "r"((uint32_t)BN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        // ===== TMA producer =====
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % ST;
+            mbar_wait(empty + s, ((kb / ST) & 1) ^ 1);
+            mbar_expect_tx(full + s, L::STAGE);
+            tma_load_2d(smem + s * L::STAGE, &mapA, full + s, kb * TC_BK, m0);
+            tma_load_2d(smem + s * L::STAGE + L::A_BYTES, &mapB, full + s, kb * TC_BK, n0);
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ===== MMA issuer: one thread drives the tensor core for the whole CTA =====
+        constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN);
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % ST;
+            mbar_wait(full + s, (kb / ST) & 1);
+            tc_fence_after();
+            const uint64_t adesc = umma_desc_sw128(s32(smem + s * L::STAGE));
+            const uint64_t bdesc = umma_desc_sw128(s32(smem + s * L::STAGE + L::A_BYTES));
+#pragma unroll
+            for (int k = 0; k < TC_BK / TC_UK; ++k)   // +32 B (= 2 sixteen-byte units) per K step inside the swizzle row
+                tc_mma_bf16(tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+            tc_commit(empty + s);      // frees the stage when these MMAs have read it
+        }
+        tc_commit(tmem_full);          // accumulator complete
+    } else if (warp >= 4) {
+        // ===== epilogue: TMEM -> registers -> (+bias) -> global fp32 =====
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+        const int w = warp - 4;                       // == warp % 4: the TMEM lane quarter this warp may read
+        const int64_t row = (int64_t)m0 + w * 32 + lane;
+        float* crow = C + row * ldc;
+        const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+            uint32_t v[32];
+            tc_ld32(tmem + ((uint32_t)(w * 32) << 16) + (uint32_t)(c * 32), v);
+            const int64_t n = (int64_t)n0 + c * 32;
+            if (row < Mrows && n < N) {
+                if (vec_ok && n + 32 <= N) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        float4 o = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                               __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+                        if (bias) {
+                            const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + n + j));
+                            o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+                        }
+                        *reinterpret_cast<float4*>(crow + n + j) = o;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (n + j < N) crow[n + j] = __uint_as_float(v[j]) + (bias ? __ldg(bias + n + j) : 0.0f);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)BN) : "memory");
+}
+
+// ---- convert pass: fp32 operand -> bf16 plane [rows][Kp], k contiguous, zero padded to Kp ---------
+// element (row, k) at src[row * s_row + k * s_k].  Raises *inexact if a value loses bits in bf16.
+template <bool SRC_K_CONTIG>
+__global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ src, int64_t s_row, int64_t s_k,
+                                                      __nv_bfloat16* __restrict__ dst, int64_t rows, int64_t K,
+                                                      int64_t Kp, int* __restrict__ inexact)
+{
+    int bad = 0;
+    if (SRC_K_CONTIG) {
+        // one thread: 4 consecutive k of one row (float4 when the source allows it)
+        const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+        const int64_t per_row = Kp / 4;
+        if (q < rows * per_row) {
+            const int64_t r = q / per_row, k = (q % per_row) * 4;
+            const float* p = src + r * s_row + k;
+            float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            if (k + 3 < K && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+                v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (k + j < K) v[j] = __ldg(p + j);
+            }
+            uint32_t h[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t b = __float_as_uint(v[j]);
+                bad |= (b & 0xFFFFu) != 0;
+                h[j] = b >> 16;
+            }
+            *reinterpret_cast<uint2*>(dst + r * Kp + k) = make_uint2(h[0] | (h[1] << 16), h[2] | (h[3] << 16));
+        }
+    } else {
+        // source contiguous along rows (a [K, N] row-major right operand): 32 x 32 transpose tile
+        __shared__ uint16_t tile[32][33];
+        const int64_t r0 = (int64_t)blockIdx.x * 32, k0 = (int64_t)blockIdx.y * 32;
+        const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int64_t k = k0 + ty + i * 8, r = r0 + tx;
+            uint32_t b = 0;
+            if (r < rows && k < K) b = __float_as_uint(__ldg(src + r * s_row + k * s_k));
+            bad |= (b & 0xFFFFu) != 0;
+            tile[ty + i * 8][tx] = (uint16_t)(b >> 16);   // [k][r]
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int64_t r = r0 + ty + i * 8, k = k0 + tx;
+            if (r < rows && k < Kp) reinterpret_cast<uint16_t*>(dst)[r * Kp + k] = tile[tx][ty + i * 8];
+        }
+    }
+    if (bad) *inexact = 1;
+}
+
+// fp32 CUDA-core product for operands that are not on a bf16-exact grid (and for K == 0)
+struct PlainOp {
+    struct Col { float bias; };
+    const float* bias;
+    __device__ __forceinline__ void begin() {}
+    __device__ __forceinline__ Col column(int64_t n) const { return Col{bias ? __ldg(bias + n) : 0.0f}; }
+    __device__ __forceinline__ float pair(float a, float b, const Col&) const { return a * b; }
+    __device__ __forceinline__ float finish(float acc, const Col& c) const { return acc + c.bias; }
+};
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int get_encode_fn(EncodeTiledFn* out)
+{
+    static std::mutex mu;
+    static EncodeTiledFn fn = nullptr;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        B200_CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (!p || q != cudaDriverEntryPointSuccess) { set_error("cuTensorMapEncodeTiled is not available in this driver"); return B200_ERR_CUDA; }
+        fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    *out = fn;
+    return B200_OK;
+}
+
+// bf16 plane [rows][Kp] -> 2-D tensor map, box {64 (k), box_rows}, 128-byte swizzle, OOB rows read as zero
+static int make_map(EncodeTiledFn enc, CUtensorMap* map, const void* base, int64_t rows, int64_t Kp, int box_rows)
+{
+    const cuuint64_t gdim[2] = {(cuuint64_t)Kp, (cuuint64_t)rows};
+    const cuuint64_t gstride[1] = {(cuuint64_t)Kp * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (code " + std::to_string((int)r) + ")"); return B200_ERR_CUDA; }
+    return B200_OK;
+}
+
+constexpr size_t kTcFlagBytes = 256;
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" size_t b200_fq_gemm_tc_workspace_bytes(int64_t Mrows, int64_t K, int64_t N)
+{
+    if (Mrows < 0 || K < 0 || N < 0) return 0;
+    const int64_t Kp = round_up(K > 0 ? K : 1, TC_BK);
+    return kTcFlagBytes + (size_t)round_up((Mrows + N) * Kp * 2, 256) + 256;
+}
+
+extern "C" int b200_fq_gemm_tc(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, float* C,
+                               int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float* bias_dev, void* workspace,
+                               size_t workspace_bytes, void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (Mrows < 0 || K < 0 || N < 0) { set_error("b200_fq_gemm_tc: bad argument"); return B200_ERR_ARGUMENT; }
+    if (Mrows == 0 || N == 0) return B200_OK;
+    if ((K > 0 && (!A || !B)) || !C) { set_error("b200_fq_gemm_tc: NULL operand"); return B200_ERR_ARGUMENT; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const ASrc asrc = make_gemm_asrc(A, lda);
+    const BSrc bsrc{B, sb_k, sb_n};
+    const PlainOp pop{bias_dev};
+    if (K == 0) {
+        pair_gemm_kernel<PlainOp><<<pair_gemm_grid(Mrows, N), 256, 0, st>>>(asrc, bsrc, C, ldc, Mrows, K, N, pop, nullptr, 0);
+        B200_LAUNCH_CHECK("pair_gemm_kernel<PlainOp>");
+        set_path("fp32");
+        return B200_OK;
+    }
+    if (workspace_bytes < b200_fq_gemm_tc_workspace_bytes(Mrows, K, N) || !workspace) {
+        set_error("b200_fq_gemm_tc: workspace too small (see b200_fq_gemm_tc_workspace_bytes)");
+        return B200_ERR_WORKSPACE;
+    }
+    EncodeTiledFn enc = nullptr;
+    if (int rc = get_encode_fn(&enc)) return rc;
+    const int64_t Kp = round_up(K, TC_BK);
+    int* flag = reinterpret_cast<int*>(workspace);
+    __nv_bfloat16* Ah = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(workspace) + kTcFlagBytes);
+    __nv_bfloat16* Bh = Ah + Mrows * Kp;
+    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
+    {
+        const int64_t n = Mrows * (Kp / 4);
+        to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(A, lda, 1, Ah, Mrows, K, Kp, flag);
+        B200_LAUNCH_CHECK("to_bf16_kernel<A>");
+    }
+    if (sb_k == 1) {
+        const int64_t n = N * (Kp / 4);
+        to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(B, sb_n, 1, Bh, N, K, Kp, flag);
+    } else {
+        to_bf16_kernel<false><<<dim3((unsigned)ceil_div(N, 32), (unsigned)(Kp / 32)), 256, 0, st>>>(B, sb_n, sb_k, Bh, N, K, Kp, flag);
+    }
+    B200_LAUNCH_CHECK("to_bf16_kernel<B>");
+
+    const int nkb = (int)(Kp / TC_BK);
+    CUtensorMap mapA, mapB;
+    if (int rc = make_map(enc, &mapA, Ah, Mrows, Kp, TC_BM)) return rc;
+    if (N > 128) {
+        constexpr int BN = 256, ST = 4;
+        if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
+        static bool attr = false;
+        if (!attr) { B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN, ST>::TOTAL)); attr = true; }
+        fq_gemm_tc_kernel<BN, ST><<<dim3((unsigned)ceil_div(Mrows, TC_BM), (unsigned)ceil_div(N, BN)), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
+            mapA, mapB, C, ldc, Mrows, N, nkb, bias_dev, flag);
+    } else {
+        constexpr int BN = 128, ST = 4;
+        if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
+        static bool attr = false;
+        if (!attr) { B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN, ST>::TOTAL)); attr = true; }
+        fq_gemm_tc_kernel<BN, ST><<<dim3((unsigned)ceil_div(Mrows, TC_BM), (unsigned)ceil_div(N, BN)), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
+            mapA, mapB, C, ldc, Mrows, N, nkb, bias_dev, flag);
+    }
+    B200_LAUNCH_CHECK("fq_gemm_tc_kernel");
+    // runs only if the convert pass found an operand that is not exact in bf16
+    pair_gemm_kernel<PlainOp><<<pair_gemm_grid(Mrows, N), 256, 0, st>>>(asrc, bsrc, C, ldc, Mrows, K, N, pop, flag, 1);
+    B200_LAUNCH_CHECK("pair_gemm_kernel<PlainOp>(conditional)");
+    set_path("tcgen05");
+    return B200_OK;
+}

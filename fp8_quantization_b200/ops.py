@@ -177,6 +177,33 @@ def qamaa_matmul(x, y, n_bits, maxval, mantissa_bits, sign_bits, out=None):
     return out
 
 
+def fq_matmul(x, y, bias=None, out=None):
+    """The non-approx `x @ y` of fake-quantized operands (approx/approx_calculation.py:968-969, :704-705) on the
+    tcgen05 tensor cores: bf16 operands (exact for FP8-grid values), fp32 accumulation in tensor memory.
+    Operands that are not exact in bf16 are detected on the device and computed in fp32 instead."""
+    lib = _lib.load()
+    _require_cuda(x, y)
+    assert x.dim() == 2 and y.dim() == 2 and x.shape[1] == y.shape[0]
+    x = x.float() if x.dtype != torch.float32 else x
+    y = y.float() if y.dtype != torch.float32 else y
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    Mrows, K = x.shape
+    N = y.shape[1]
+    if out is None:
+        out = torch.empty((Mrows, N), dtype=torch.float32, device=x.device)
+    b = None
+    if bias is not None:
+        b = bias.detach().to(device=x.device, dtype=torch.float32).reshape(-1).contiguous()
+        assert b.numel() == N
+    ws = _workspace(x.device, lib.b200_fq_gemm_tc_workspace_bytes(Mrows, K, N))
+    with torch.cuda.device(x.device):
+        rc = lib.b200_fq_gemm_tc(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out), out.stride(0),
+                                 Mrows, K, N, _ptr(b), _ptr(ws), ws.numel(), _stream())
+    _lib.check(rc)
+    return out
+
+
 def conv_geom(x_shape, w_shape, stride, padding, dilation, groups):
     g = _lib.ConvGeom()
     g.batch, g.C_in, g.H, g.W = (int(v) for v in x_shape)

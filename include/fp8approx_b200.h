@@ -129,6 +129,20 @@ int b200_qamaa_gemm(const float *A, int64_t lda, const float *B, int64_t sb_k, i
                     int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *maxval_dev, int n_bits,
                     float mantissa_bits, int sign_bits, void *stream);
 
+/* ---- K3: the non-approx matmul on the tensor cores (tcgen05) ---------------------------------- */
+/* C = A @ B (+ bias) for FAKE-QUANTIZED operands; replaces `x @ y[:, i:i+1]` per column
+ * (approx/approx_calculation.py:968-969 Linear, :796-797 BN-conv, :996 / :811 single column) and
+ * `self.multiply` = torch.matmul (:704-705, conv without BN).  Same operand layout as b200_approx_gemm.
+ * Operands are converted to bf16 on the device (exact for every FP8-grid value); tcgen05.mma kind::f16
+ * accumulates in fp32 in tensor memory.  If ANY operand is not exactly representable in bf16 the call
+ * computes the product with fp32 CUDA-core arithmetic instead (decided on the device, no host sync).
+ * bias_dev: device [N] fp32 added to every row, or NULL.
+ * Tolerance vs the reference's fp32 matmul: |C - ref| <= 1e-6 * sum_k |a_k * b_k| (summation order). */
+size_t b200_fq_gemm_tc_workspace_bytes(int64_t Mrows, int64_t K, int64_t N);
+int b200_fq_gemm_tc(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n, float *C,
+                    int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *bias_dev,
+                    void *workspace, size_t workspace_bytes, void *stream);
+
 /* ---- A9: conv form, QCustomBNConv2dTorch.run_forward, approx/approx_calculation.py:822-917 -------- */
 typedef struct b200_conv_geom {
     int64_t batch;
