@@ -58,6 +58,8 @@ SIGNATURES = {
     "b200_fpany_encode": (c_int, [c_vp, c_i64, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp]),
     "b200_fpany_decode": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     "b200_fpany_quant": (c_int, [c_vp, c_i64, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
+    "b200_approx_mult_v5": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_int, c_int, c_vp,
+                                    c_vp]),
     "b200_approx_gemm_workspace_bytes": (c_sz, [c_i64, c_i64, c_i64]),
     "b200_approx_gemm": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_vp,
                                  c_int, ctypes.POINTER(ApproxParams), c_vp, c_sz, c_vp]),

@@ -96,7 +96,7 @@ struct PredecodeArgs {
     int M;
     BiasSrc bias;
     int* offgrid;          // raised if any element cannot take the table path
-    unsigned long long* zero_count;   // A operand: number of zero elements (picks the GEMM's k loop), or null
+    unsigned long long* zero_count;   // A operand: number of zero elements (sampled; picks the GEMM's k loop), or null
 };
 
 __device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int bA, int& off)
@@ -184,9 +184,20 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
         }
     }
     if (off) *a.offgrid = 1;
-    if (!IS_B && a.zero_count) {
+    // zero statistics of the A operand, sampled: one block in 8 along the rows counts its zeros and its
+    // elements (one 64-bit atomic: zeros in the low half, elements in the high half)
+    if (!IS_B && a.zero_count && (blockIdx.x & 7) == 0) {
+        __shared__ int s_zeros;
+        if (threadIdx.x == 0) s_zeros = 0;
+        __syncthreads();
         zeros = __reduce_add_sync(0xFFFFFFFFu, zeros);
-        if (tx == 0 && zeros) atomicAdd(a.zero_count, (unsigned long long)zeros);
+        if (tx == 0 && zeros) atomicAdd(&s_zeros, zeros);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const int64_t nr = min((int64_t)32, a.rows - r0), nk = min((int64_t)32, a.K - k0);
+            if (nr > 0 && nk > 0)
+                atomicAdd(a.zero_count, (unsigned long long)s_zeros | ((unsigned long long)(nr * nk) << 32));
+        }
     }
 }
 
@@ -265,7 +276,6 @@ struct LutGemmArgs {
     uint32_t zero_word;   // the A word of a == 0
     int sparse_a;         // 1 / 0: force the branchy / predicated k loop; -1: decide from zero_count
     const unsigned long long* zero_count;   // zero activations counted by the predecode pass
-    unsigned long long sparse_min;          // branchy loop when *zero_count >= sparse_min
     const int* offgrid;
 };
 
@@ -374,7 +384,10 @@ approx_gemm_lut_kernel(LutGemmArgs a)
             }
         }
     };
-    const bool sparse = a.sparse_a >= 0 ? a.sparse_a != 0 : (CPL == 4 && *a.zero_count >= a.sparse_min);
+    // sampled zero statistics of the activations (predecode pass): low half zeros, high half elements
+    const unsigned long long zc = *a.zero_count;
+    const bool sparse = a.sparse_a >= 0 ? a.sparse_a != 0
+                                        : (CPL == 4 && 10ull * (zc & 0xFFFFFFFFull) >= 4ull * (zc >> 32));
     if (sparse) mainloop(std::true_type{});
     else            mainloop(std::false_type{});
     cp_async_wait<0>();
@@ -671,7 +684,6 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     // k-loop choice (measured, 4096^3 E4M3: branchy 5.2 / 7.3 T MAC/s at 0 % / 50 % zeros, predicated 6.4 / 6.9)
     { const char* e = getenv("B200_LUT_SPARSE"); la.sparse_a = e ? atoi(e) : -1; }
     la.zero_count = reinterpret_cast<const unsigned long long*>(flag + 2);
-    la.sparse_min = (unsigned long long)(0.4 * (double)Mrows * (double)K);
     la.offgrid = flag;
     prof_record(true, st);
     static int sms = 0;

@@ -132,9 +132,50 @@ __global__ void fpany_quant_kernel(const float* __restrict__ v, int64_t n, int E
         out[i] = fpany_quant(p, v[i], clip != 0);
 }
 
+// approx_mult_new (approx/approx_matmul_whole_v5.py:155-182): integer-add approximate multiply on the
+// code domain with the simulated hardware adder overflow / underflow.  x_int = (expo << M) + mant.
+__global__ void v5_ofuf_kernel(const int32_t* __restrict__ x_int, const int32_t* __restrict__ y_int,
+                               const int32_t* __restrict__ x_mant, const int32_t* __restrict__ y_mant,
+                               const signed char* __restrict__ table, int64_t n, int B_neg, int E, int M, int sim,
+                               int of_opt, int uf_opt, int32_t* __restrict__ out)
+{
+    const int32_t mod = 1 << (E + M), max_norm_int = mod - 1, mant_scale = 1 << M, tn = 1 << M;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        int mx = x_mant ? x_mant[i] : (x_int[i] & (mant_scale - 1));
+        int my = y_mant ? y_mant[i] : (y_int[i] & (mant_scale - 1));
+        if (mx < 0) mx += tn;                                    // Python negative indexing wraps once
+        if (my < 0) my += tn;
+        const int comp = (table && mx >= 0 && mx < tn && my >= 0 && my < tn) ? (int)table[mx * tn + my] : 0;
+        int32_t t = x_int[i] + y_int[i] + B_neg + comp;          // :160
+        if (sim) {
+            const bool of = t > max_norm_int, uf = t < 0;        // :166-167
+            t = ((t % mod) + mod) % mod;                         // torch `%` is a floor-mod, :170
+            if (of_opt && of) t = max_norm_int;                  // :172-173
+            if (uf_opt && uf) t = t % mant_scale;                // :175-176
+        }
+        out[i] = t;
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_approx_mult_v5(const int32_t* x_int, const int32_t* y_int, const int32_t* x_mant,
+                                   const int32_t* y_mant, const int8_t* table_dev, int64_t n, int B_neg, int E, int M,
+                                   int sim_hw_add_OFUF, int with_OF_opt, int with_UF_opt, int32_t* out, void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (E < 1 || M < 1 || E + M > 30) { set_error("Invalid combination of expo_width and mant_width"); return B200_ERR_INVALID_FORMAT; }
+    if (n <= 0) return B200_OK;
+    if (!x_int || !y_int || !out) { set_error("b200_approx_mult_v5: NULL operand"); return B200_ERR_ARGUMENT; }
+    v5_ofuf_kernel<<<elementwise_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(
+        x_int, y_int, x_mant, y_mant, reinterpret_cast<const signed char*>(table_dev), n, B_neg, E, M, sim_hw_add_OFUF,
+        with_OF_opt, with_UF_opt, out);
+    B200_LAUNCH_CHECK("v5_ofuf_kernel");
+    return B200_OK;
+}
 
 extern "C" int b200_fp8_fakequant(const float* x, float* y, int64_t n, const float* maxval, int64_t n_channels,
                                   int64_t inner, int n_bits, float mantissa_bits, int sign_bits, float* bias_out,

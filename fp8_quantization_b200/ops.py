@@ -353,6 +353,27 @@ def fpany_quant(values, expo_width, mant_width, bias, clip_OF=True, tensor_bias_
     return out
 
 
+def approx_mult_v5(x_int, y_int, B_neg, x_mant, y_mant, comp_table_NN, sim_hw_add_OFUF, with_OF_opt, with_UF_opt,
+                   expo_width, mant_width):
+    """approx_mult_new (approx/approx_matmul_whole_v5.py:155-182): the integer-add approximate multiply with
+    the simulated hardware-adder overflow / underflow -- the only live definition of sim_hw_add_OFUF,
+    with_OF_opt and with_UF_opt (approx_v9 ignores them).  int32 code tensors in, int32 codes out."""
+    lib = _lib.load()
+    _require_cuda(x_int, y_int)
+    shape = torch.broadcast_shapes(x_int.shape, y_int.shape)
+    xi = x_int.to(torch.int32).expand(shape).contiguous()
+    yi = y_int.to(torch.int32).expand(shape).contiguous()
+    xm = x_mant.to(torch.int32).expand(shape).contiguous() if x_mant is not None else None
+    ym = y_mant.to(torch.int32).expand(shape).contiguous() if y_mant is not None else None
+    t = comp_table_NN.to(device=xi.device, dtype=torch.int8).contiguous() if comp_table_NN is not None else None
+    out = torch.empty(shape, dtype=torch.int32, device=xi.device)
+    with torch.cuda.device(xi.device):
+        _lib.check(lib.b200_approx_mult_v5(_ptr(xi), _ptr(yi), _ptr(xm), _ptr(ym), _ptr(t), xi.numel(), int(B_neg),
+                                           int(expo_width), int(mant_width), int(bool(sim_hw_add_OFUF)),
+                                           int(bool(with_OF_opt)), int(bool(with_UF_opt)), _ptr(out), _stream()))
+    return out
+
+
 def kernel_launches():
     return int(_lib.load().b200_kernel_launches())
 

@@ -96,6 +96,21 @@ int b200_fpany_decode(const int32_t *expo, const int32_t *mant, const float *sig
 int b200_fpany_quant(const float *v, int64_t n, int expo_width, int mant_width, int bias,
                      int tensor_bias_quirk, int clip_OF, float *out, void *stream);
 
+/* ---- A7: hardware adder overflow / underflow clipping (only live in v5) ------------------------ */
+/* approx_mult_new, approx/approx_matmul_whole_v5.py:155-182, elementwise on the integer code domain:
+ *   t = x_int + y_int + B_neg + table[x_mant, y_mant];
+ *   sim_hw_add_OFUF: of = t > 2^(E+M)-1, uf = t < 0; t = t mod 2^(E+M) (floor-mod);
+ *   with_OF_opt: t = of ? 2^(E+M)-1 : t;   with_UF_opt: t = uf ? t mod 2^M : t.
+ * approx_v9 accepts these three flags and never reads them (approx_matmul_whole_v9.py:15 vs :20-169), so
+ * b200_approx_gemm ignores them too; this entry point is the opt-in v5 semantics.  x_mant / y_mant may
+ * be NULL (-> x_int mod 2^M); table_dev: DEVICE int8 [2^M, 2^M] or NULL (zeros).  (The with_OF_opt line of
+ * the reference names an undefined tensor, :173; its evident meaning is implemented -- see
+ * tests/golden/make_v5_ofuf.py.) */
+int b200_approx_mult_v5(const int32_t *x_int, const int32_t *y_int, const int32_t *x_mant,
+                        const int32_t *y_mant, const int8_t *table_dev, int64_t n, int B_neg, int expo_width,
+                        int mant_width, int sim_hw_add_OFUF, int with_OF_opt, int with_UF_opt, int32_t *out,
+                        void *stream);
+
 /* ---- A1/A6: approx_multiply -> custom_matmul_vectorize ---------------------------------------- */
 /* Replaces the whole per-column Python loop of approx_multiply
  * (approx/approx_calculation.py:946-971 Linear, :774-799 BN-conv; one column =

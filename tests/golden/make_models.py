@@ -69,6 +69,15 @@ def main():
                 taps[f"{name}_{lname}_x{phase[0]}"] = inp[0].detach().contiguous().numpy().copy()
                 taps[f"{name}_{lname}_y{phase[0]}"] = outp.detach().contiguous().numpy().copy()
             mods[lname].register_forward_hook(hook)
+        # probes: for EVERY hot-path layer a fixed pseudo-random sample of its output (end-to-end pass, no
+        # teacher forcing) -- locates the first layer at which two implementations part ways
+        if name in mc.PROBED_CASES:
+            for li, (lname, mod) in enumerate((n, m) for n, m in mods.items() if hasattr(m, "run_forward")):
+                def probe(mod, inp, outp, lname=lname, li=li):
+                    flat = outp.detach().contiguous().reshape(-1)
+                    idx = mc.probe_indices(flat.numel(), li)
+                    taps[f"{name}_{lname}_p{phase[0]}"] = flat[idx].numpy().copy()
+                mod.register_forward_hook(probe)
         with torch.inference_mode(), contextlib.redirect_stdout(io.StringIO()):
             model.quantized()
             model.estimate_ranges()

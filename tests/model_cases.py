@@ -62,7 +62,17 @@ MODEL_CASES = [
 TAPPED_LAYERS = {
     "resnet18_64": ["features.0", "features.2.0.features.0", "features.3.0.downsample.0", "features.4.1.features.1",
                     "features.5.1.features.1", "fc"],
-    "resnet18_224_b8": [],
+    "resnet18_224_b8": ["features.5.1.features.1", "fc"],
     "mobilenetv2_64": ["features.0.0", "features.1.conv.0", "features.2.conv.0", "features.2.conv.1",
                        "features.4.conv.2", "features.17.conv.1", "features.18.0", "classifier.1"],
 }
+
+# cases for which the golden file also holds, for EVERY hot-path layer, a fixed sample of the layer output
+# in the end-to-end pass (keys f"{case}_{layer}_p{cal|eval}")
+PROBED_CASES = ["resnet18_224_b8"]
+PROBE_N = 4096
+
+
+def probe_indices(numel, layer_index):
+    g = torch.Generator().manual_seed(1000 + layer_index)
+    return torch.randint(0, numel, (min(PROBE_N, numel),), generator=g)

@@ -246,3 +246,17 @@ def test_codec_fixture(fq):
         # decode(encode(v)) == quant(v) for the sub-normal aware codec
         d = fq.ops.fpany_decode(e, m, E, M, bias, sign=torch.where(x < 0, -1.0, 1.0))
         assert same_bits(d.cpu().numpy(), z[f"q{i}"])
+
+
+def test_v5_ofuf_fixture(fq):
+    """Row A7 on the GPU: b200_approx_mult_v5 against the unmodified reference's approx_mult_new
+    (integer codes: bit exact), with explicit mantissa tensors and with them derived on the device."""
+    z = np.load(os.path.join(GOLD, "v5_ofuf.npz"))
+    for i, (E, M, wc, dn, B_neg, sim, of, uf, g) in enumerate(z["cfgs"]):
+        E, M = int(E), int(M)
+        x, y, T = dev(z[f"x{g}"]), dev(z[f"y{g}"]), dev(z[f"t{g}"])
+        got = fq.ops.approx_mult_v5(x, y, int(B_neg), x % (2 ** M), y % (2 ** M), T, sim, of, uf, E, M)
+        assert np.array_equal(got.cpu().numpy(), z[f"r{i}"]), (i, E, M, sim, of, uf)
+        if i % 8 == 7:
+            got = fq.ops.approx_mult_v5(x, y, int(B_neg), None, None, T, sim, of, uf, E, M)
+            assert np.array_equal(got.cpu().numpy(), z[f"r{i}"])

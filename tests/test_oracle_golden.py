@@ -117,3 +117,15 @@ def test_grid_fixed_points():
             y, b = orc.fp8_fakequant(v, [maxval], 8, float(M), 1)
             assert b[0] == bias
             assert same_bits(y, v)
+
+
+def test_v5_ofuf_fixture():
+    """Row A7: the oracle's overflow / underflow clipping against the unmodified reference's
+    approx_mult_new (approx/approx_matmul_whole_v5.py:155-182), all 8 flag combinations."""
+    z = np.load(os.path.join(GOLD, "v5_ofuf.npz"))
+    assert int(z["of_opt_raises_nameerror"]) == 1     # the reference line :173 as shipped
+    for i, (E, M, wc, dn, B_neg, sim, of, uf, g) in enumerate(z["cfgs"]):
+        x, y, T = z[f"x{g}"], z[f"y{g}"], z[f"t{g}"].astype(np.int32)
+        comp = T[x % (2 ** M), y % (2 ** M)]
+        got = orc.v5_ofuf(x, y, comp, int(B_neg), int(E), int(M), int(sim), int(of), int(uf))
+        assert np.array_equal(got, z[f"r{i}"]), (i, E, M, sim, of, uf)

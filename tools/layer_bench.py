@@ -36,6 +36,7 @@ def main():
     ap.add_argument("--mant-width", type=int, default=3)
     ap.add_argument("--zero-frac", type=float, default=0.5)
     ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--check", action="store_true", help="compare with the arithmetic kernel, bit for bit")
     a = ap.parse_args()
     import torch
     import fp8_quantization_b200 as pkg
@@ -78,6 +79,12 @@ def main():
         lib.b200_profile_end(ctypes.byref(t), ctypes.byref(c))
         kms = t.value / max(c.value, 1)
         macs = rows * K * N
+        if a.check:
+            pg = ops.make_params(dict(expo_width=E, mant_width=M, dnsmp_factor=3, withComp=True, with_approx=True,
+                                      with_s2nn2s_opt=True, quant_btw_mult_accu=True), force_generic=True)
+            want = ops.approx_matmul(xq, wq.t(), bA, bB, bR, pg)
+            nbad = int((want.view(torch.int32) != out.view(torch.int32)).sum())
+            print("check", rows, K, N, "mismatching elements:", nbad, "max abs diff", float((want - out).abs().max()))
         print(json.dumps({"rows": rows, "K": K, "N": N, "count": cnt, "path": ops.last_path(), "ms": round(ms, 4),
                           "gemm_ms": round(kms, 4), "tmacs": round(macs / ms / 1e9, 3),
                           "gemm_tmacs": round(macs / kms / 1e9, 3) if kms else None}), flush=True)
