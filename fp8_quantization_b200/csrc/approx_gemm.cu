@@ -201,6 +201,62 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
     }
 }
 
+// Conv form (implicit im2col, approx/approx_calculation.py:724-747): one thread owns one output pixel
+// (row) and walks 32 consecutive k = (c, ky, kx) with incremental counters -- the row is decomposed
+// into (b, ho, wo) ONCE, nothing in the loop divides.  Adjacent threads are adjacent output pixels:
+// loads are coalesced for stride-1 convs (and hit L1/L2 for the kh*kw re-reads), stores are 512-byte
+// coalesced rows of the k-major plane.  The K-times inflated im2col matrix exists only as this plane.
+constexpr int PC_ROWS = 128, PC_KCH = 32;
+__global__ void __launch_bounds__(PC_ROWS) predecode_conv_kernel(PredecodeArgs a, LutGeom g)
+{
+    const ASrc& s = a.asrc;
+    const int64_t r = (int64_t)blockIdx.x * PC_ROWS + threadIdx.x;
+    const int k0 = blockIdx.y * PC_KCH;
+    int off = 0, zeros = 0;
+    const int bA = a.bias.A(), bR = a.bias.R();
+    if (bA <= -64 || bA >= 64 || bR <= -64 || bR >= 64) off = 1;
+    const bool valid_r = r < a.rows;
+    const int wo = (int)(r % s.Wo);
+    const int64_t t2 = r / s.Wo;
+    const int ho = (int)(t2 % s.Ho);
+    const int64_t b = t2 / s.Ho;
+    const int h0 = ho * s.sh - s.ph, w0 = wo * s.sw - s.pw;
+    const float* base = s.p + (b * s.C + s.c0) * (int64_t)s.H * s.W;
+    int kx = k0 % s.kw, tk = k0 / s.kw;
+    int ky = tk % s.kh, c = tk / s.kh;
+    const uint32_t zero_word = 2u * (uint32_t)g.zeroA_off;
+    uint32_t* dst = a.dst + (int64_t)k0 * a.Rpad + r;
+    const int kend = (int)min((int64_t)PC_KCH, a.Kpad - k0);
+#pragma unroll 4
+    for (int kk = 0; kk < kend; ++kk) {
+        uint32_t w = zero_word;
+        if (valid_r && k0 + kk < a.K) {
+            const int h = h0 + ky * s.dh, wi = w0 + kx * s.dw;
+            float v = 0.0f;                                              // F.pad zeros (:727)
+            if (h >= 0 && h < s.H && wi >= 0 && wi < s.W) v = __ldg(base + ((int64_t)c * s.H + h) * s.W + wi);
+            w = predecode_a(g, v, bA, off);
+            zeros += (v == 0.0f);
+        }
+        dst[(int64_t)kk * a.Rpad] = w;
+        if (++kx == s.kw) { kx = 0; if (++ky == s.kh) { ky = 0; ++c; } }
+    }
+    if (off) *a.offgrid = 1;
+    if (a.zero_count && (blockIdx.x & 7) == 0) {   // sampled zero statistics, as in predecode_kernel
+        __shared__ int s_zeros;
+        if (threadIdx.x == 0) s_zeros = 0;
+        __syncthreads();
+        zeros = __reduce_add_sync(0xFFFFFFFFu, zeros);
+        if ((threadIdx.x & 31) == 0 && zeros) atomicAdd(&s_zeros, zeros);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const int64_t nr = min((int64_t)PC_ROWS, a.rows - (int64_t)blockIdx.x * PC_ROWS);
+            const int64_t nk = min((int64_t)PC_KCH, a.K - k0);
+            if (nr > 0 && nk > 0)
+                atomicAdd(a.zero_count, (unsigned long long)s_zeros | ((unsigned long long)(nr * nk) << 32));
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // Table-driven GEMM.  Template <WARPS, RPW, CPL>: CTA tile (RPW*WARPS) x (32*CPL); one warp =
 // RPW rows x 32*CPL columns; one lane = RPW rows x CPL consecutive columns (RPW*CPL = 64 or 32 fp32
@@ -665,7 +721,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     pa.zero_count = reinterpret_cast<unsigned long long*>(flag + 2);
     // GEMM rows are k-contiguous (transpose through shared memory); an im2col view is contiguous along
     // the output pixel, i.e. along rows: read and write row-fastest
-    if (A.conv) predecode_kernel<false, false><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, lut->geom);
+    if (A.conv) predecode_conv_kernel<<<dim3((unsigned)(Mpad / PC_ROWS), (unsigned)ceil_div(Kpad, PC_KCH)), PC_ROWS, 0, st>>>(pa, lut->geom);
     else        predecode_kernel<false, true><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, lut->geom);
     B200_LAUNCH_CHECK("predecode_kernel<A>");
     PredecodeArgs pb = pa;
