@@ -42,8 +42,12 @@ struct LutFlags {
     int unrepresentable;   // cells whose value does not fit bf16 exactly
 };
 
+// quirk = 1: the single-column (int32-tensor-bias) numerics of approx_calculation.py:800-809 for biases >= 2:
+// integer pow makes min_norm 0 in every format (approx_matmul_whole_v9.py:202), so nothing is treated
+// as sub-normal, no product rounds to zero (all rows are live) and an exponent code of exactly 0 is
+// DECODED as a sub-normal (:321-323).
 __global__ void lut_build_kernel(LutGeom g, const signed char* __restrict__ T, int has_table, int with_approx,
-                                 int clip_OF, uint16_t* __restrict__ lut, LutFlags* __restrict__ flags)
+                                 int clip_OF, int quirk, uint16_t* __restrict__ lut, LutFlags* __restrict__ flags)
 {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= g.total_entries) return;
@@ -57,8 +61,9 @@ __global__ void lut_build_kernel(LutGeom g, const signed char* __restrict__ T, i
         const int mA = q & ((1 << M) - 1);
         const int s0 = (q >> M) & 1;   // plain layout: [a<0]; signed-index layout: region & 1 = [a<0] xor [b<0]
         const int t = idx_t - g.RA - M - 2;
-        if (idx_t > g.RA) {
-            const FmtParam pR = make_param(g.E, M, 1 - M, false);   // unit space: u = 2^(1-bias-M) = 1
+        if (idx_t > g.RA || quirk) {
+            FmtParam pR = make_param(g.E, M, 1 - M, false);   // unit space: u = 2^(1-bias-M) = 1
+            if (quirk) pR.min_norm = 0.0f;
             const float s = ldexpf(1.0f, -M);
             const float pex = (1.0f + (float)mA * s) * (1.0f + (float)mB * s);
             const float p = has_table ? mult_mant(M, mA, mB, T, with_approx != 0)
@@ -579,7 +584,8 @@ int device_table(const signed char* host, int M, const signed char** dev_out)
 }
 
 // Builds (once per configuration and device) the pair table of lut.cuh.  First use synchronises.
-static int build_lut(int E, int M, const signed char* dev_table, int with_approx, int clip_OF, bool sidx, LutEntry* e)
+static int build_lut(int E, int M, const signed char* dev_table, int with_approx, int clip_OF, bool sidx, bool quirk,
+                     LutEntry* e)
 {
     e->geom = make_lut_geom(E, M, sidx);
     e->lut_bytes = (int)round_up((int64_t)e->geom.total_entries * 2, 16);
@@ -589,7 +595,8 @@ static int build_lut(int E, int M, const signed char* dev_table, int with_approx
     B200_CUDA_TRY(cudaMemset(e->d_lut, 0, e->lut_bytes));
     B200_CUDA_TRY(cudaMemset(d_flags, 0, sizeof(LutFlags)));
     lut_build_kernel<<<(int)ceil_div(e->geom.total_entries, 256), 256>>>(e->geom, dev_table, dev_table != nullptr,
-                                                                        with_approx, clip_OF, e->d_lut, d_flags);
+                                                                        with_approx, clip_OF, quirk ? 1 : 0, e->d_lut,
+                                                                        d_flags);
     B200_LAUNCH_CHECK("lut_build_kernel");
     B200_CUDA_TRY(cudaMemcpy(&e->flags, d_flags, sizeof(LutFlags), cudaMemcpyDeviceToHost));
     cudaFree(d_flags);
@@ -597,21 +604,21 @@ static int build_lut(int E, int M, const signed char* dev_table, int with_approx
 }
 
 static int get_lut(int E, int M, const signed char* host_table, const signed char* dev_table, int with_approx,
-                   int clip_OF, const LutEntry** out)
+                   int clip_OF, const LutEntry** out, bool quirk = false)
 {
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lk(g_cache_mu);
-    auto key = std::make_tuple(dev, E, M, (const void*)host_table, with_approx, clip_OF);
+    auto key = std::make_tuple(dev, E, M, (const void*)host_table, with_approx, clip_OF + (quirk ? 2 : 0));
     auto it = g_luts.find(key);
     if (it == g_luts.end()) {
         LutEntry e;
-        if (int rc = build_lut(E, M, dev_table, with_approx, clip_OF, false, &e)) return rc;
-        if (e.flags.sign_quirk && !e.flags.unrepresentable) {
+        if (int rc = build_lut(E, M, dev_table, with_approx, clip_OF, quirk, quirk, &e)) return rc;
+        if (!quirk && e.flags.sign_quirk && !e.flags.unrepresentable) {
             // not odd in the operand signs: rebuild with both signs in the index (lut.cuh)
             cudaFree(e.d_lut);
             e = LutEntry();
-            if (int rc = build_lut(E, M, dev_table, with_approx, clip_OF, true, &e)) return rc;
+            if (int rc = build_lut(E, M, dev_table, with_approx, clip_OF, true, false, &e)) return rc;
         }
         it = g_luts.emplace(key, e).first;
     }
@@ -619,6 +626,19 @@ static int get_lut(int E, int M, const signed char* host_table, const signed cha
     return B200_OK;
 }
 
+
+// The single-column table (signed-index layout, quirk numerics) for conv.cu's depthwise kernel.
+int get_quirk_lut(int E, int M, const signed char* host_table, const signed char* dev_table, int with_approx,
+                  LutGeom* geom, const uint16_t** d_lut, int* lut_bytes, int* usable)
+{
+    const LutEntry* e = nullptr;
+    if (int rc = get_lut(E, M, host_table, dev_table, with_approx, 0, &e, true)) return rc;
+    *geom = e->geom;
+    *d_lut = e->d_lut;
+    *lut_bytes = e->lut_bytes;
+    *usable = e->flags.unrepresentable == 0;
+    return B200_OK;
+}
 
 // Optional per-launch timing of the dominant kernel (bench.py's roofline leg): CUDA events recorded
 // on the launching stream right around the table GEMM.

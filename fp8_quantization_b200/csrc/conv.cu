@@ -9,6 +9,8 @@
 //     single-column numerics (int32-tensor biases -> integer pow in param_prepare,
 //     approx_calculation.py:800-809);
 //   * b200_im2col: the explicit matrix, for the exact (non-approx) conv and for tests.
+#include <algorithm>
+
 #include "common.cuh"
 #include "conv_geom.cuh"
 #include "gemm_impl.cuh"
@@ -43,8 +45,9 @@ struct DwArgs {
     const signed char* T;
 };
 
-__global__ void __launch_bounds__(256) approx_dw_kernel(DwArgs d)
+__global__ void __launch_bounds__(256) approx_dw_kernel(DwArgs d, const int* __restrict__ gate, int gate_run_if_nonzero)
 {
+    if (gate && ((*gate != 0) != (gate_run_if_nonzero != 0))) return;
     __shared__ float tile[32][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int64_t m = (int64_t)blockIdx.x * 32 + tx;
@@ -77,6 +80,105 @@ __global__ void __launch_bounds__(256) approx_dw_kernel(DwArgs d)
         const int g = blockIdx.y * 32 + tx;
         if (mm < d.rows && g < d.groups) d.out[mm * d.groups + g] = tile[tx][ml];
     }
+}
+
+// ---- single-column groups, table driven -----------------------------------------------------------
+// Same function as approx_dw_kernel for the main mode (with_s2nn2s_opt && quant_btw_mult_accu, no
+// golden_clip_OF), operands on the FP8 grid and all three exponent biases >= 2 (where the integer pow of
+// the tensor-bias branch makes min_norm 0): the addend is u * F(s, t, mA, mB) with the quirk table of
+// approx_gemm.cu (signed-index layout, lut.cuh).  Per MAC: field extraction of `a` (the weight word is
+// warp-uniform), one 16-bit shared-memory lookup, one fp32 add, k ascending like the arithmetic kernel.
+// Anything outside those conditions raises *flag; approx_dw_kernel then recomputes the whole output.
+struct DwLutArgs {
+    ASrc a;
+    const float* w;
+    float* out;
+    int64_t rows, n_row_tiles;
+    int groups, Kg, Cg, n_grp_tiles;
+    BiasSrc bias;
+    LutGeom g;
+    const uint16_t* lut;
+    int lut_bytes;
+    int* flag;
+};
+
+__global__ void __launch_bounds__(256) approx_dw_lut_kernel(DwLutArgs d)
+{
+    extern __shared__ __align__(16) unsigned char dw_smem[];
+    float (*tile)[33] = reinterpret_cast<float (*)[33]>(dw_smem + d.lut_bytes);
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(d.lut);
+        uint4* dst = reinterpret_cast<uint4*>(dw_smem);
+        for (int i = threadIdx.x; i < d.lut_bytes / 16; i += 256) dst[i] = __ldg(src + i);
+    }
+    const uint16_t* lut_s = reinterpret_cast<const uint16_t*>(dw_smem);
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const LutGeom& g = d.g;
+    const int M = g.M;
+    const int bA = d.bias.A(), bR = d.bias.R();
+    int off = (bA < 2 || bR < 2 || bA >= 64 || bR >= 64) ? 1 : 0;
+    const float unit = pow2f_i(1 - bR - M);
+    const uint32_t frac_mask = (1u << (23 - M)) - 1u;
+    const ASrc& s = d.a;
+    __syncthreads();
+    for (int64_t t = blockIdx.x; t < d.n_row_tiles * d.n_grp_tiles; t += gridDim.x) {
+        const int64_t rt = t / d.n_grp_tiles;
+        const int gt = (int)(t - rt * d.n_grp_tiles);
+        const int64_t m = rt * 32 + tx;
+        const int wo = (int)(m % s.Wo);
+        const int64_t t2 = m / s.Wo;
+        const int ho = (int)(t2 % s.Ho);
+        const int64_t b = t2 / s.Ho;
+        const int h0 = ho * s.sh - s.ph, w0 = wo * s.sw - s.pw;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int gl = ty + 8 * i;
+            const int grp = gt * 32 + gl;
+            float acc = 0.0f;
+            if (grp < d.groups && m < d.rows) {
+                const int bB = d.bias.B(grp);
+                if (bB < 2 || bB >= 64) off = 1;
+                const float* wg = d.w + (int64_t)grp * d.Kg;
+                const float* base = s.p + (b * s.C + (int64_t)grp * d.Cg) * (int64_t)s.H * s.W;
+                int kx = 0, ky = 0, c = 0;
+                for (int k = 0; k < d.Kg; ++k) {
+                    const uint32_t wb = __float_as_uint(__ldg(wg + k));      // warp-uniform
+                    const int h = h0 + ky * s.dh, wi = w0 + kx * s.dw;
+                    float av = 0.0f;
+                    if (h >= 0 && h < s.H && wi >= 0 && wi < s.W) av = __ldg(base + ((int64_t)c * s.H + h) * s.W + wi);
+                    if (++kx == s.kw) { kx = 0; if (++ky == s.kh) { ky = 0; ++c; } }
+                    const uint32_t ab = __float_as_uint(av);
+                    const uint32_t wmag = wb & 0x7FFFFFFFu, amag = ab & 0x7FFFFFFFu;
+                    if (wmag == 0u || amag == 0u) continue;                   // zero product: addend 0 (v9 :81)
+                    const int LB = (int)(wmag >> 23) - 127, LA = (int)(amag >> 23) - 127;
+                    const int tA = LA - (1 - bA - M);
+                    const int tB = LB + bR - bA + 3 + g.RA;                   // no clamp: every row is live here
+                    if ((wmag & frac_mask) || (amag & frac_mask) || tA < 0 || tA > g.RA || tB < 0 || tB > g.NTB - 1 ||
+                        LB < 1 - bB - M || (wmag >> 23) == 0 || (wmag >> 23) == 255 || (amag >> 23) == 0 ||
+                        (amag >> 23) == 255) {
+                        off = 1;
+                        continue;
+                    }
+                    const uint32_t mA = (amag & 0x7FFFFFu) >> (23 - M), mB = (wmag & 0x7FFFFFu) >> (23 - M);
+                    const uint32_t sreg = (ab >> 31) + (wb >> 31);             // 0, 1 or 2: region s = sreg & 1
+                    const uint32_t idx = (uint32_t)g.s_stride * sreg + (uint32_t)g.a_stride * mA +
+                                         (uint32_t)g.row_entries * (uint32_t)(tA + tB) + mB;
+                    acc += __uint_as_float((uint32_t)lut_s[idx] << 16);
+                }
+            }
+            tile[gl][tx] = acc * unit;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int ml = ty + 8 * i;
+            const int64_t mm = rt * 32 + ml;
+            const int grp = gt * 32 + tx;
+            if (mm < d.rows && grp < d.groups) d.out[mm * d.groups + grp] = tile[tx][ml];
+        }
+        __syncthreads();
+    }
+    if (off) *d.flag = 1;
 }
 
 }  // namespace b200
@@ -122,7 +224,7 @@ extern "C" size_t b200_approx_conv2d_workspace_bytes(const b200_conv_geom* g)
 {
     ConvDims d;
     if (conv_dims(g, &d) != B200_OK) return 0;
-    if (d.Ng == 1) return 0;
+    if (d.Ng == 1) return 256;   // device-side fallback flag of the single-column table kernel
     return b200_approx_gemm_workspace_bytes(d.rows, d.Kg, d.Ng);
 }
 
@@ -174,7 +276,43 @@ extern "C" int b200_approx_conv2d_fbias(const float* x, const float* w, float* o
     a.cfg.quirk = true;
     a.T = a.cfg.with_approx ? dev_table : nullptr;
     const dim3 grid((unsigned)ceil_div(d.rows, 32), (unsigned)ceil_div(g->groups, 32));
-    approx_dw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    cudaStream_t st = (cudaStream_t)stream;
+    // table path: main mode only; needs 256 B of workspace for the device-side fallback flag
+    const bool lut_mode = !p->force_generic && p->with_s2nn2s_opt && p->quant_btw_mult_accu && !p->golden_clip_OF &&
+                          workspace && workspace_bytes >= 256;
+    if (lut_mode) {
+        DwLutArgs la;
+        int usable = 0;
+        if (int rc = get_quirk_lut(E, M, a.cfg.with_approx ? host_table : nullptr, a.T, a.cfg.with_approx, &la.g, &la.lut,
+                                   &la.lut_bytes, &usable))
+            return rc;
+        const size_t smem = (size_t)la.lut_bytes + 32 * 33 * sizeof(float);
+        if (usable && smem <= 227 * 1024) {
+            static int sms = 0;
+            if (sms == 0) {
+                int dev = 0;
+                cudaGetDevice(&dev);
+                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+                if (sms <= 0) sms = 148;
+                B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_lut_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            }
+            la.a = a.a; la.w = w; la.out = out; la.rows = d.rows; la.groups = g->groups; la.Kg = d.Kg; la.Cg = d.Cg;
+            la.n_row_tiles = ceil_div(d.rows, 32); la.n_grp_tiles = (int)ceil_div(g->groups, 32);
+            la.bias = a.bias; la.flag = reinterpret_cast<int*>(workspace);
+            B200_CUDA_TRY(cudaMemsetAsync(la.flag, 0, 4, st));
+            const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (227 * 1024) / (smem + 1024)));
+            const int64_t tiles = la.n_row_tiles * la.n_grp_tiles;
+            const unsigned blocks = (unsigned)std::min<int64_t>(tiles, (int64_t)sms * per_sm);
+            approx_dw_lut_kernel<<<blocks, 256, smem, st>>>(la);
+            B200_LAUNCH_CHECK("approx_dw_lut_kernel");
+            // runs only if the table kernel met an operand / bias outside its domain
+            approx_dw_kernel<<<grid, 256, 0, st>>>(a, la.flag, 1);
+            B200_LAUNCH_CHECK("approx_dw_kernel(conditional)");
+            set_path("single-column-lut");
+            return B200_OK;
+        }
+    }
+    approx_dw_kernel<<<grid, 256, 0, st>>>(a, nullptr, 0);
     B200_LAUNCH_CHECK("approx_dw_kernel");
     set_path("single-column");
     return B200_OK;

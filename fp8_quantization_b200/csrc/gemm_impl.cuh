@@ -1,6 +1,7 @@
 // gemm_impl.cuh -- internal interface between the C-ABI entry points (approx_gemm.cu, conv.cu).
 #pragma once
 #include "common.cuh"
+#include "lut.cuh"
 #include "pair_gemm.cuh"
 
 namespace b200 {
@@ -22,6 +23,10 @@ struct BiasSrc {
 
 // (device, host table) -> cached device copy of a 4^M int8 table; nullptr stays nullptr (zero table)
 int device_table(const signed char* host, int M, const signed char** dev_out);
+
+// pair table with the single-column ("tensor bias") numerics, signed-index layout (approx_gemm.cu)
+int get_quirk_lut(int E, int M, const signed char* host_table, const signed char* dev_table, int with_approx,
+                  LutGeom* geom, const uint16_t** d_lut, int* lut_bytes, int* usable);
 
 int approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc,
                      int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const b200_approx_params* p,

@@ -260,3 +260,41 @@ def test_v5_ofuf_fixture(fq):
         if i % 8 == 7:
             got = fq.ops.approx_mult_v5(x, y, int(B_neg), None, None, T, sim, of, uf, E, M)
             assert np.array_equal(got.cpu().numpy(), z[f"r{i}"])
+
+
+@pytest.mark.parametrize("fmt", [(4, 3, 3), (3, 4, 3), (2, 5, 3), (2, 5, 5)])
+@pytest.mark.parametrize("geom", [(3, 40, 17, 19, 3, 1, 1), (2, 33, 16, 16, 3, 2, 1), (1, 8, 9, 9, 5, 1, 2)])
+def test_depthwise_table_kernel_vs_arithmetic(fq, fmt, geom):
+    """Single-column groups (every depthwise conv): the table kernel against the arithmetic kernel that the
+    layer fixtures pin to the reference's tensor-bias branch (approx_calculation.py:800-809): bit exact.
+    Also: biases < 2 and off-grid operands must fall back on the device."""
+    E, M, dnsmp = fmt
+    B, C, H, W, k, stride, pad = geom
+    rng = np.random.default_rng(100 * E + C)
+    half = 2 ** (E - 1)
+    bA, bR = half + 1, half + 2
+    bW = rng.integers(max(2, half), half + 4, size=C).astype(np.float32)
+    x = _grid_sample(rng, E, M, bA, (B, C, H, W), 0.4)
+    w = np.stack([_grid_sample(rng, E, M, int(bW[c]), (1, k, k), 0.05) for c in range(C)], axis=0)
+    kw = dict(expo_width=E, mant_width=M, withComp=True, dnsmp_factor=dnsmp, with_approx=True, with_s2nn2s_opt=True,
+              quant_btw_mult_accu=True)
+    args = (dev(x), dev(w), torch.tensor([float(bA)]).cuda(), dev(bW), torch.tensor([float(bR)]).cuda())
+    conv = ((stride, stride), (pad, pad), (1, 1), C)
+    got = fq.ops.approx_conv2d(*args, fq.ops.make_params(kw, single_column_quirk=True), *conv)
+    assert fq.ops.last_path() == "single-column-lut"
+    want = fq.ops.approx_conv2d(*args, fq.ops.make_params(kw, single_column_quirk=True, force_generic=True), *conv)
+    assert fq.ops.last_path() == "single-column"
+    assert same_bits(got.cpu().numpy(), want.cpu().numpy())
+    assert float(want.abs().max()) > 0
+    # a result bias of 1 leaves the table's domain (integer pow gives min_norm = 1, not 0)
+    args1 = args[:4] + (torch.tensor([1.0]).cuda(),)
+    got = fq.ops.approx_conv2d(*args1, fq.ops.make_params(kw, single_column_quirk=True), *conv)
+    want = fq.ops.approx_conv2d(*args1, fq.ops.make_params(kw, single_column_quirk=True, force_generic=True), *conv)
+    assert same_bits(got.cpu().numpy(), want.cpu().numpy())
+    # an off-grid activation
+    x2 = x.copy()
+    x2[0, 0, 1, 1] = np.float32(0.3337)
+    args2 = (dev(x2),) + args[1:]
+    got = fq.ops.approx_conv2d(*args2, fq.ops.make_params(kw, single_column_quirk=True), *conv)
+    want = fq.ops.approx_conv2d(*args2, fq.ops.make_params(kw, single_column_quirk=True, force_generic=True), *conv)
+    assert same_bits(got.cpu().numpy(), want.cpu().numpy())
