@@ -111,6 +111,16 @@ def cpu_port_rate(rows, M, target_s, x_q, w_q, bA, bB, bR):
     return rows * K_DIM * ncols / dt, ncols, dt, orc.num_threads()
 
 
+def measured_traffic(M, rows):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the table GEMM, per launch, from the committed ncu
+    --set full capture of this same workload (profiles/traffic.json); None for other configurations."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return t.get(f"approx_gemm_lut_kernel E{7 - M}M{M} {rows}x{K_DIM}x{N_DIM}")
+    except Exception:
+        return None
+
+
 def build_layer(M, device, w, b):
     """The reference-facing plugin: QCustomLinearTorch with the flags of scripts/image_net.sh
     (--fp8-set-maxval --per-channel --quantize-input, act allminmax / weight current_minmax)."""
@@ -254,6 +264,16 @@ def run_ours(args):
                      "kernel_gmacs": round(macs / (kern_ms * 1e-3) / 1e9, 1) if kern_ms > 0 else None},
         "clocks": clocks,
     }
+    # the bound that actually binds the table kernel: one 16-bit shared-memory lookup per MAC, 32 lookups per
+    # clock per SM; clock = median SM clock sampled during the timed region
+    if kern_ms > 0 and clocks and clocks.get("sm_mhz"):
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        lds_peak = 32.0 * sms * clocks["sm_mhz"] * 1e6
+        line["roofline"]["lds"] = {"achieved": round(macs / (kern_ms * 1e-3) / 1e12, 3), "peak": round(lds_peak / 1e12, 3),
+                                   "unit": "T lookups/s", "frac": round(macs / (kern_ms * 1e-3) / lds_peak, 4),
+                                   "note": "ncu: l1tex__data_pipe_lsu_wavefronts_mem_shared at 96.7 % of peak "
+                                           "(profiles/r1b_approx_gemm_lut_full.txt)"}
+    line["roofline"]["traffic"] = measured_traffic(M, rows)
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             rate, ncols, dt, thr = cpu_port_rate(rows, M, 12.0, xq.cpu().numpy(), wq.cpu().numpy(),

@@ -506,6 +506,12 @@ static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int lut_bytes
 {
     const LutTileCfg* best = nullptr;
     double best_cost = 0;
+    if (const char* e = getenv("B200_LUT_TILE")) {   // experiments: force a tile configuration by index
+        const int i = atoi(e);
+        if (i >= 0 && i < (int)(sizeof(kLutTiles) / sizeof(kLutTiles[0])) && kLutTiles[i].sidx == sidx &&
+            kLutTiles[i].smem(lut_bytes) + 1024 <= 227 * 1024)
+            return &kLutTiles[i];
+    }
     for (const LutTileCfg& c : kLutTiles) {
         if (c.sidx != sidx) continue;
         const size_t sm = c.smem(lut_bytes) + 1024;

@@ -23,10 +23,21 @@ import torch
 from torch import nn
 from torch.nn.modules.pooling import _AdaptiveAvgPoolNd, _AvgPoolNd
 
-from .approx_calculation import QCustomBNConv2dTorch, QCustomConv2dTorch, QCustomLinearTorch
-from .quantization import (ACTIVATIONS, QuantizationManager, QuantizedActivation, QuantizedModule)
+import torch.nn.functional as F
 
-non_bn_module_map = {nn.Conv2d: QCustomConv2dTorch, nn.Linear: QCustomLinearTorch}
+from .approx_calculation import QCustomBNConv2dTorch, QCustomConv2dTorch, QCustomLinearTorch
+from .quantization import (ACTIVATIONS, QuantizationHijacker, QuantizationManager, QuantizedActivation,
+                           QuantizedModule)
+
+
+class QuantLayerNorm(QuantizationHijacker, nn.LayerNorm):
+    """approx/replace_operations_with_approx_ops.py:160-168: LayerNorm whose weight is fake-quantized."""
+
+    def run_forward(self, x, weight, bias, offsets=None):
+        return F.layer_norm(x.contiguous(), self.normalized_shape, weight.contiguous(), bias.contiguous(), self.eps)
+
+
+non_bn_module_map = {nn.Conv2d: QCustomConv2dTorch, nn.Linear: QCustomLinearTorch, nn.LayerNorm: QuantLayerNorm}
 bn_module_map = {nn.Conv2d: QCustomBNConv2dTorch}
 non_param_modules = (_AdaptiveAvgPoolNd, _AvgPoolNd)
 
@@ -82,6 +93,8 @@ def _ctor_args(mod, act):
                   bias=mod.bias is not None)
     elif isinstance(mod, nn.Linear):
         kw = dict(in_features=mod.in_features, out_features=mod.out_features, bias=mod.bias is not None)
+    elif isinstance(mod, nn.LayerNorm):
+        kw = dict(normalized_shape=mod.normalized_shape, eps=mod.eps, elementwise_affine=mod.elementwise_affine)
     else:
         raise ValueError(type(mod))
     kw["activation"] = act

@@ -78,3 +78,33 @@ def test_model_against_reference(case):
         scale = float(np.abs(want).max())
         print(f"{name} {tag}: end-to-end max |dlogit| = {err:.3e} (logit scale {scale:.3e})")
         assert err <= END_TO_END_TOL * scale, (name, tag, err, scale)
+
+
+def test_vit_tiny_table_vs_arithmetic():
+    """ViT wrappers (models/vit_quantized_approx.py mirror) on a 2-layer toy config: the reference cannot run
+    this model with approx_flag (it asserts on 3-D activations), so parity is operator
+    level; here the whole forward through the table kernel must equal the forward through the arithmetic
+    kernel (the definition the operator fixtures pin to the reference), calibration and eval pass."""
+    from fp8_quantization_b200 import ops, vit
+    cfg = vit.ViTConfig(hidden_size=64, num_hidden_layers=2, num_attention_heads=4, intermediate_size=128,
+                        image_size=32, patch_size=16, num_labels=10)
+    outs = []
+    orig = ops.make_params
+    for force in (False, True):
+        torch.manual_seed(3)
+        model = vit.vit_quantized_approx(vit.VisionTransformerForImageClassification(cfg), **qparams(3, 4)).cuda().eval()
+        ops.make_params = (lambda *a, **k: orig(*a, **{**k, "force_generic": True})) if force else orig
+        try:
+            with torch.inference_mode():
+                model.quantized()
+                model.estimate_ranges()
+                y_cal = model(mc.images(4, 32, 1).cuda())
+                model.fix_ranges()
+                y_eval = model(mc.images(4, 32, 2).cuda())
+                path = ops.last_path()
+        finally:
+            ops.make_params = orig
+        outs.append((y_cal, y_eval, path))
+    assert outs[0][2] == "lut" and outs[1][2] == "generic"
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert float(outs[0][1].abs().max()) > 0

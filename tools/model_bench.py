@@ -13,10 +13,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-MACS_PER_IMAGE = {"resnet18": 1.814e9, "mobilenetv2": 0.301e9}
+MACS_PER_IMAGE = {"resnet18": 1.814e9, "mobilenetv2": 0.301e9, "vit_b16": 16.73e9, "bert_base": 10.87e9}   # bert_base: per sequence of 128 tokens, NON-approx (tcgen05)
 
 
 def build(model_name, E, M, device):
+    import torch
     import model_cases as mc
     from fp8_quantization_b200 import model_wrap as mw
     qp = dict(method="fp_quantizer", act_method="fp_quantizer", n_bits=8, n_bits_act=8, per_channel_weights=True,
@@ -25,6 +26,15 @@ def build(model_name, E, M, device):
               run_method=dict(mc.RUN_APPROX))
     if model_name == "resnet18":
         model = mw.QuantizedResNet(mc.fp_resnet18(), **qp)
+    elif model_name == "bert_base":
+        from fp8_quantization_b200 import bert
+        torch.manual_seed(mc.SEED)
+        qp["run_method"] = dict(bert.RUN_PLAIN)
+        model = bert.bert_quantized(**qp)
+    elif model_name == "vit_b16":
+        from fp8_quantization_b200 import vit
+        torch.manual_seed(mc.SEED)
+        model = vit.vit_quantized_approx(**qp)
     else:
         model = mw.QuantizedMobileNetV2(mc.fp_mobilenetv2(mw.MobileNetV2, 224), **qp)
     return model.to(device).eval()
@@ -37,8 +47,12 @@ def images_per_s(model_name="resnet18", batch=8, steps=10, warmup=3, E=4, M=3, g
     from fp8_quantization_b200 import eval_harness as eh, ops
     device = device or torch.device("cuda", torch.cuda.current_device())
     model = build(model_name, E, M, device)
-    x_cal = mc.images(calib_batch or batch, 224, 1).to(device)
-    x = mc.images(batch, 224, 2).to(device)
+    if model_name == "bert_base":
+        ids = lambda n, seed: torch.randint(0, 30522, (n, 128), generator=torch.Generator().manual_seed(seed))
+        x_cal, x = ids(calib_batch or batch, 1).to(device), ids(batch, 2).to(device)
+    else:
+        x_cal = mc.images(calib_batch or batch, 224, 1).to(device)
+        x = mc.images(batch, 224, 2).to(device)
     eh.calibrate(model, x_cal)
     with torch.inference_mode():
         for _ in range(warmup):
