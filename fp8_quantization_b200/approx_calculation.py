@@ -34,7 +34,8 @@ class _ApproxMixin:
                 return ops.approx_matmul(x, y, x_bias, y_bias, res_bias, self._params(False))
             if self.quantize_after_mult_and_add:
                 q = self.res_quantizer.quantizer
-                return ops.qamaa_matmul(x, y, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits)
+                return ops.qamaa_matmul(x, y, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits, x_bias=x_bias,
+                                        y_bias=y_bias)
             return ops.fq_matmul(x, y)               # `x @ y[:, i]` per column (:968-969): tcgen05
         # single output column (every depthwise group): int32-TENSOR biases in the reference
         # (:985-994) -> integer-pow numerics, no quantize_after_mult_and_add branch
@@ -93,7 +94,8 @@ class _ConvMixin(_ApproxMixin):
         elif use_approx and self.quantize_after_mult_and_add and Ng != 1:
             q = self.res_quantizer.quantizer
             out = ops.qamaa_conv2d(x, weight, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits, self.stride,
-                                   self.padding, self.dilation, self.groups)
+                                   self.padding, self.dilation, self.groups, x_bias=self.get_acts_fp_bias(),
+                                   w_bias=self.get_weights_fp_bias())
         else:
             col = self.im2col(x, kh, kw, self.stride, self.padding, self.dilation)
             Kg = Cg * kh * kw

@@ -28,6 +28,7 @@
 #include "lut.cuh"
 #include "pair_gemm.cuh"
 #include "pair_math.cuh"
+#include "qamaa_op.cuh"
 #include "tables.h"
 #include "gemm_impl.cuh"
 
@@ -82,6 +83,46 @@ __global__ void lut_build_kernel(LutGeom g, const signed char* __restrict__ T, i
             if (!g.sidx && val[1] != -val[0]) atomicAdd(&flags->sign_quirk, 1);   // not odd in the sign of b
             const uint32_t bits = __float_as_uint(val[0]);
             if (bits & 0xFFFFu) atomicAdd(&flags->unrepresentable, 1);
+            out = (uint16_t)(bits >> 16);
+        }
+    }
+    lut[idx] = out;
+}
+
+// Pair table of the quantize_after_mult_and_add mode (approx_calculation.py:959-967): the addend is
+// Q(a * b) with Q = quantize_to_fp8_ste_MM(., n_bits, maxval, mantissa_bits, sign_bits); for operands on
+// the FP8 grid that is sb * u * F(sa, t, mA, mB) with the SAME index geometry as the approx table
+// (t = LA + LB + bias_R, u = 2^(1 - bias_R - M)), where bias_R follows from the result quantizer's maxval.
+// maxval lives on the device and moves during calibration, so the table is rebuilt per call (<= 60 K cells,
+// a few microseconds) into the caller's workspace; the kernel also publishes bias_R (as fp32) for the
+// operand predecode, and raises *flag when the table path does not apply (unsigned grid, exotic widths).
+__global__ void lut_build_qamaa_kernel(LutGeom g, QamaaOp op, uint16_t* __restrict__ lut, float* __restrict__ bias_out,
+                                       int* __restrict__ flag)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    op.begin();
+    if (idx == 0) {
+        *bias_out = op.bias;
+        if (!op.fast || op.M_i != g.M || op.sign_bits != 1) *flag = 1;
+    }
+    if (idx >= g.total_entries) return;
+    uint16_t out = 0;
+    if (idx < g.zeroA_off && op.fast) {
+        const int M = g.M;
+        const int mB = idx & ((1 << M) - 1);
+        const int row = idx >> M;
+        const int idx_t = row % g.NT;
+        const int q = row / g.NT;
+        const int mA = q & ((1 << M) - 1);
+        const int sa = (q >> M) & 1;
+        const int t = idx_t - g.RA - M - 2;                  // LA + LB + bias_R
+        if (idx_t > g.RA) {
+            const float s = ldexpf(1.0f, -M);
+            const float p = (1.0f + (float)mA * s) * (1.0f + (float)mB * s);     // exact
+            const float x = p * pow2f_i(t - op.bias_i) * (sa ? -1.0f : 1.0f);   // a * b for b > 0
+            const float v = op.quant(x) * pow2f_i(M + op.bias_i - 1);           // in units of u
+            const uint32_t bits = __float_as_uint(v);
+            if ((bits & 0xFFFFu) || op.quant(-x) != -op.quant(x)) *flag = 1;    // not bf16-exact / not odd in b
             out = (uint16_t)(bits >> 16);
         }
     }
@@ -338,6 +379,8 @@ struct LutGemmArgs {
     int sparse_a;         // 1 / 0: force the branchy / predicated k loop; -1: decide from zero_count
     const unsigned long long* zero_count;   // zero activations counted by the predecode pass
     const int* offgrid;
+    int qamaa;            // 1: epilogue applies the result quantizer to the sum (quantize_after_mult_and_add)
+    QamaaOp qop;
 };
 
 // KT: k-tile depth (8 where a large table leaves little shared memory for the operand ring).
@@ -453,8 +496,16 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     else            mainloop(std::false_type{});
     cp_async_wait<0>();
 
-    // epilogue: C = acc * u (exact power-of-two scaling)
+    // epilogue: C = acc * u (exact power-of-two scaling); quantize_after_mult_and_add: C = Q(acc * u)
     const float unit = pow2f_i(1 - a.bias.R() - a.M);
+    if (a.qamaa) {
+        QamaaOp q = a.qop;
+        q.begin();
+#pragma unroll
+        for (int i = 0; i < RPW; ++i)
+#pragma unroll
+            for (int j = 0; j < CPL; ++j) acc[i][j] = q.quant(acc[i][j] * unit) / unit;   // stored below as acc * unit
+    }
     const int64_t n = n0 + lane * CPL;
     const bool vec = ((a.ldc & (CPL - 1)) == 0) && ((reinterpret_cast<uintptr_t>(a.C) & (4 * CPL - 1)) == 0) &&
                      (n + CPL - 1 < a.N);
@@ -670,6 +721,62 @@ static void prof_record(bool start, cudaStream_t st)
 constexpr int64_t kPadM = 256, kPadN = 128, kPadK = 32;
 constexpr size_t kFlagBytes = 256;
 
+// Predecode of both operands + the table GEMM launch, shared by the approx path and the
+// quantize_after_mult_and_add path (whose table and result bias live in the workspace).
+static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc,
+                        int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const LutGeom& geom,
+                        const uint16_t* d_lut, int lut_bytes, int* flag, uint32_t* Aw, uint32_t* Bw, int64_t Mpad,
+                        int64_t Npad, int64_t Kpad, const QamaaOp* qop, cudaStream_t st)
+{
+    const int M = geom.M;
+    PredecodeArgs pa;
+    pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
+    pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
+    pa.zero_count = reinterpret_cast<unsigned long long*>(flag + 2);
+    // GEMM rows are k-contiguous (transpose through shared memory); an im2col view is contiguous along
+    // the output pixel, i.e. along rows: read and write row-fastest
+    if (A.conv) predecode_conv_kernel<<<dim3((unsigned)(Mpad / PC_ROWS), (unsigned)ceil_div(Kpad, PC_KCH)), PC_ROWS, 0, st>>>(pa, geom);
+    else        predecode_kernel<false, true><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, geom);
+    B200_LAUNCH_CHECK("predecode_kernel<A>");
+    PredecodeArgs pb = pa;
+    pb.zero_count = nullptr;
+    pb.src = B; pb.s_row = sb_n; pb.s_k = sb_k; pb.dst = Bw; pb.rows = N; pb.Rpad = Npad;
+    const dim3 pgrid((unsigned)(Npad / 32), (unsigned)(Kpad / 32));
+    if (sb_k == 1 && sb_n != 1) predecode_kernel<true, true><<<pgrid, 256, 0, st>>>(pb, geom);
+    else                        predecode_kernel<true, false><<<pgrid, 256, 0, st>>>(pb, geom);
+    B200_LAUNCH_CHECK("predecode_kernel<B>");
+
+    LutGemmArgs la;
+    la.Aw = Aw; la.Bw = Bw; la.lut = d_lut; la.C = C; la.ldc = ldc; la.Mrows = Mrows; la.N = N;
+    la.Mpad = Mpad; la.Npad = Npad; la.Kpad = (int)Kpad; la.lut_bytes = lut_bytes;
+    la.bias = bias; la.M = M;
+    la.zero_word = 2u * (uint32_t)geom.zeroA_off;
+    // k-loop choice (measured, 4096^3 E4M3: branchy 5.2 / 7.3 T MAC/s at 0 % / 50 % zeros, predicated 6.4 / 6.9)
+    { const char* e = getenv("B200_LUT_SPARSE"); la.sparse_a = e ? atoi(e) : -1; }
+    la.zero_count = reinterpret_cast<const unsigned long long*>(flag + 2);
+    la.offgrid = flag;
+    la.qamaa = qop ? 1 : 0;
+    if (qop) la.qop = *qop; else la.qop = QamaaOp{};
+    prof_record(true, st);
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+        for (const LutTileCfg& c : kLutTiles)
+            B200_CUDA_TRY(cudaFuncSetAttribute(c.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    }
+    const LutTileCfg* tc = choose_lut_tile(Mrows, N, lut_bytes, geom.sidx, sms);
+    if (!tc) { set_error("b200_approx_gemm: pair table does not fit shared memory"); return B200_ERR_ARGUMENT; }
+    tc->kernel<<<dim3((unsigned)ceil_div(Mrows, tc->BM()), (unsigned)ceil_div(N, tc->BN())), 32 * tc->warps,
+                 tc->smem(lut_bytes), st>>>(la);
+    prof_record(false, st);
+    B200_LAUNCH_CHECK("approx_gemm_lut_kernel");
+    return B200_OK;
+}
+
+
 }  // namespace b200
 
 using namespace b200;
@@ -741,52 +848,69 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     uint32_t* Bw = Aw + (size_t)Kpad * Mpad;
     B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 16, st));
 
-    PredecodeArgs pa;
-    pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
-    pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
-    pa.zero_count = reinterpret_cast<unsigned long long*>(flag + 2);
-    // GEMM rows are k-contiguous (transpose through shared memory); an im2col view is contiguous along
-    // the output pixel, i.e. along rows: read and write row-fastest
-    if (A.conv) predecode_conv_kernel<<<dim3((unsigned)(Mpad / PC_ROWS), (unsigned)ceil_div(Kpad, PC_KCH)), PC_ROWS, 0, st>>>(pa, lut->geom);
-    else        predecode_kernel<false, true><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, lut->geom);
-    B200_LAUNCH_CHECK("predecode_kernel<A>");
-    PredecodeArgs pb = pa;
-    pb.zero_count = nullptr;
-    pb.src = B; pb.s_row = sb_n; pb.s_k = sb_k; pb.dst = Bw; pb.rows = N; pb.Rpad = Npad;
-    const dim3 pgrid((unsigned)(Npad / 32), (unsigned)(Kpad / 32));
-    if (sb_k == 1 && sb_n != 1) predecode_kernel<true, true><<<pgrid, 256, 0, st>>>(pb, lut->geom);
-    else                        predecode_kernel<true, false><<<pgrid, 256, 0, st>>>(pb, lut->geom);
-    B200_LAUNCH_CHECK("predecode_kernel<B>");
-
-    LutGemmArgs la;
-    la.Aw = Aw; la.Bw = Bw; la.lut = lut->d_lut; la.C = C; la.ldc = ldc; la.Mrows = Mrows; la.N = N;
-    la.Mpad = Mpad; la.Npad = Npad; la.Kpad = (int)Kpad; la.lut_bytes = lut->lut_bytes;
-    la.bias = bias; la.M = M;
-    la.zero_word = 2u * (uint32_t)lut->geom.zeroA_off;
-    // k-loop choice (measured, 4096^3 E4M3: branchy 5.2 / 7.3 T MAC/s at 0 % / 50 % zeros, predicated 6.4 / 6.9)
-    { const char* e = getenv("B200_LUT_SPARSE"); la.sparse_a = e ? atoi(e) : -1; }
-    la.zero_count = reinterpret_cast<const unsigned long long*>(flag + 2);
-    la.offgrid = flag;
-    prof_record(true, st);
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (sms <= 0) sms = 148;
-        for (const LutTileCfg& c : kLutTiles)
-            B200_CUDA_TRY(cudaFuncSetAttribute(c.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    }
-    const LutTileCfg* tc = choose_lut_tile(Mrows, N, lut->lut_bytes, lut->geom.sidx, sms);
-    if (!tc) { set_error("b200_approx_gemm: pair table does not fit shared memory"); return B200_ERR_ARGUMENT; }
-    tc->kernel<<<dim3((unsigned)ceil_div(Mrows, tc->BM()), (unsigned)ceil_div(N, tc->BN())), 32 * tc->warps,
-                 tc->smem(lut->lut_bytes), st>>>(la);
-    prof_record(false, st);
-    B200_LAUNCH_CHECK("approx_gemm_lut_kernel");
+    if (int rc = run_lut_gemm(A, B, sb_k, sb_n, C, ldc, Mrows, K, N, bias, lut->geom, lut->d_lut, lut->lut_bytes, flag,
+                              Aw, Bw, Mpad, Npad, Kpad, nullptr, st))
+        return rc;
     // runs only if the predecode found an off-grid operand
     pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<ApproxPairOp>(conditional)");
     set_path(lut->geom.sidx ? "lut-signed" : "lut");
+    return B200_OK;
+}
+
+// quantize_after_mult_and_add on the table kernel.  `hint` carries the operand exponent biases (the
+// fake-quantizers' custom_bias tensors): they only fix the table's index range -- an operand outside the
+// grid they describe raises the device flag and the arithmetic kernel recomputes the output.
+constexpr size_t kQamaaTableBytes = 128 * 1024;
+
+extern "C" size_t b200_qamaa_gemm_workspace_bytes(int64_t Mrows, int64_t K, int64_t N)
+{
+    const size_t base = b200_approx_gemm_workspace_bytes(Mrows, K, N);
+    return base ? base + kQamaaTableBytes : 0;
+}
+
+int b200::qamaa_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc,
+                          int64_t Mrows, int64_t K, int64_t N, const float* maxval_dev, int n_bits,
+                          float mantissa_bits, int sign_bits, const BiasSrc* hint, void* workspace,
+                          size_t workspace_bytes, void* stream)
+{
+    cudaStream_t st = (cudaStream_t)stream;
+    QamaaOp op;
+    op.maxval_dev = maxval_dev;
+    op.n_bits = n_bits;
+    op.sign_bits = sign_bits;
+    op.mantissa_bits = mantissa_bits;
+    const BSrc bsrc{B, sb_k, sb_n};
+    const dim3 ggrid = pair_gemm_grid(Mrows, N);
+    const int M = (int)rintf(mantissa_bits), E = n_bits - sign_bits - M;
+    const bool lut_mode = hint && n_bits == 8 && sign_bits == 1 && M >= 2 && M <= 5 && E >= 2 && K > 0 && workspace &&
+                          workspace_bytes >= b200_qamaa_gemm_workspace_bytes(Mrows, K, N) && !getenv("B200_QAMAA_GENERIC");
+    if (!lut_mode) {
+        pair_gemm_kernel<QamaaOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, nullptr, 0);
+        B200_LAUNCH_CHECK("pair_gemm_kernel<QamaaOp>");
+        set_path("qamaa-generic");
+        return B200_OK;
+    }
+    const LutGeom geom = make_lut_geom(E, M);
+    const int lut_bytes = (int)round_up((int64_t)geom.total_entries * 2, 16);
+    if ((size_t)lut_bytes > kQamaaTableBytes) { set_error("b200_qamaa_gemm: table does not fit"); return B200_ERR_ARGUMENT; }
+    const int64_t Mpad = round_up(Mrows, kPadM), Npad = round_up(N, kPadN), Kpad = round_up(K, kPadK);
+    int* flag = reinterpret_cast<int*>(workspace);
+    float* bias_R = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 64);
+    uint32_t* Aw = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(workspace) + kFlagBytes);
+    uint32_t* Bw = Aw + (size_t)Kpad * Mpad;
+    uint16_t* d_lut = reinterpret_cast<uint16_t*>(Bw + (size_t)Kpad * Npad);
+    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 16, st));
+    lut_build_qamaa_kernel<<<(int)ceil_div(lut_bytes / 2, 256), 256, 0, st>>>(geom, op, d_lut, bias_R, flag);
+    B200_LAUNCH_CHECK("lut_build_qamaa_kernel");
+    BiasSrc bias = *hint;
+    bias.fR = bias_R;                                   // result bias = the quantizer's, computed on the device
+    if (int rc = run_lut_gemm(A, B, sb_k, sb_n, C, ldc, Mrows, K, N, bias, geom, d_lut, lut_bytes, flag, Aw, Bw, Mpad,
+                              Npad, Kpad, &op, st))
+        return rc;
+    pair_gemm_kernel<QamaaOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
+    B200_LAUNCH_CHECK("pair_gemm_kernel<QamaaOp>(conditional)");
+    set_path("qamaa-lut");
     return B200_OK;
 }
 

@@ -32,4 +32,10 @@ int approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, 
                      int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const b200_approx_params* p,
                      void* workspace, size_t workspace_bytes, void* stream);
 
+// quantize_after_mult_and_add GEMM: table kernel when `hint` (operand exponent biases) is given and the
+// format allows it, arithmetic kernel otherwise (approx_gemm.cu)
+int qamaa_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc, int64_t Mrows,
+                    int64_t K, int64_t N, const float* maxval_dev, int n_bits, float mantissa_bits, int sign_bits,
+                    const BiasSrc* hint, void* workspace, size_t workspace_bytes, void* stream);
+
 }  // namespace b200

@@ -15,45 +15,8 @@
 #include "conv_geom.cuh"
 #include "pair_gemm.cuh"
 #include "pair_math.cuh"
-
-namespace b200 {
-
-struct QamaaOp {
-    struct Col {};
-    const float* maxval_dev;
-    int n_bits, sign_bits;
-    float mantissa_bits;
-    // derived per thread
-    float mx, mn, bias, Mf;
-    int bias_i, M_i, fast;
-    __device__ __forceinline__ void begin()
-    {
-        mx = __ldg(maxval_dev);
-        mn = (sign_bits == 1) ? -mx : 0.0f;
-        bias = fp8_ste_bias(mx, n_bits, mantissa_bits, sign_bits, &Mf);
-        bias_i = (int)bias;
-        M_i = (int)Mf;
-        // exponent-field path needs an integral, moderate bias (always true for a finite positive maxval)
-        fast = (bias == (float)bias_i) && bias_i > -90 && bias_i < 90;
-    }
-    __device__ __forceinline__ Col column(int64_t) const { return Col{}; }
-    __device__ __forceinline__ float quant(float x) const
-    {
-        if (!fast) return fp8_ste_quant(x, mx, bias, Mf, sign_bits);
-        const float xc = fminf(fmaxf(x, mn), mx);                          // :119-120
-        const int ef = (int)((__float_as_uint(xc) >> 23) & 0xFFu);          // floor(log2|xc|) + 127 (0: zero / denormal)
-        int ls = ef - 127 + bias_i;                                         // :144
-        if (ls < 1) ls = 1;                                                 // clamp(min=1)
-        const int se = ls - M_i - bias_i;                                   // log2(scale), :151
-        // round-half-even to a multiple of 2^se: add and subtract 1.5 * 2^(23+se) (exact; |xc| < 2^(22+se))
-        const float magic = __uint_as_float(((uint32_t)(se + 23 + 127) << 23) | 0x00400000u);
-        return (xc + magic) - magic;                                        // == rint(xc / scale) * scale, :154
-    }
-    __device__ __forceinline__ float pair(float a, float b, const Col&) const { return quant(a * b); }
-    __device__ __forceinline__ float finish(float acc, const Col&) const { return quant(acc); }
-};
-
-}  // namespace b200
+#include "qamaa_op.cuh"
+#include "gemm_impl.cuh"
 
 using namespace b200;
 
@@ -65,23 +28,34 @@ extern "C" int b200_qamaa_gemm(const float* A, int64_t lda, const float* B, int6
     if (Mrows < 0 || K < 0 || N < 0 || !maxval_dev) { set_error("b200_qamaa_gemm: bad argument"); return B200_ERR_ARGUMENT; }
     if (Mrows == 0 || N == 0) return B200_OK;
     if (!A || !B || !C) { set_error("b200_qamaa_gemm: NULL operand"); return B200_ERR_ARGUMENT; }
-    QamaaOp op;
-    op.maxval_dev = maxval_dev;
-    op.n_bits = n_bits;
-    op.sign_bits = sign_bits;
-    op.mantissa_bits = mantissa_bits;
-    pair_gemm_kernel<QamaaOp><<<pair_gemm_grid(Mrows, N), 256, 0, (cudaStream_t)stream>>>(
-        make_gemm_asrc(A, lda), BSrc{B, sb_k, sb_n}, C, ldc, Mrows, K, N, op, nullptr, 0);
-    B200_LAUNCH_CHECK("pair_gemm_kernel<QamaaOp>");
-    return B200_OK;
+    return qamaa_gemm_impl(make_gemm_asrc(A, lda), B, sb_k, sb_n, C, ldc, Mrows, K, N, maxval_dev, n_bits, mantissa_bits,
+                           sign_bits, nullptr, nullptr, 0, stream);
+}
+
+extern "C" int b200_qamaa_gemm_fbias(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, float* C,
+                                     int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float* maxval_dev,
+                                     int n_bits, float mantissa_bits, int sign_bits, const float* bA_dev,
+                                     const float* bB_dev, int64_t bB_stride, void* workspace, size_t workspace_bytes,
+                                     void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (Mrows < 0 || K < 0 || N < 0 || !maxval_dev) { set_error("b200_qamaa_gemm_fbias: bad argument"); return B200_ERR_ARGUMENT; }
+    if (Mrows == 0 || N == 0) return B200_OK;
+    if (!A || !B || !C) { set_error("b200_qamaa_gemm_fbias: NULL operand"); return B200_ERR_ARGUMENT; }
+    const int E = n_bits - sign_bits - (int)rintf(mantissa_bits);
+    const int dflt = 1 << (E > 0 ? E - 1 : 0);
+    BiasSrc hint{dflt, dflt, bA_dev, nullptr, nullptr, bB_dev, bB_stride};
+    return qamaa_gemm_impl(make_gemm_asrc(A, lda), B, sb_k, sb_n, C, ldc, Mrows, K, N, maxval_dev, n_bits, mantissa_bits,
+                           sign_bits, bB_dev ? &hint : nullptr, workspace, workspace_bytes, stream);
 }
 
 // Conv form (BN-conv variant, approx/approx_calculation.py:787-795 inside the group loop :858-906):
 // implicit im2col over the NCHW input, one launch per group.  out is [B*Ho*Wo, C_out] row-major.
 // Groups with a single output channel take the reference's N == 1 branch, which has NO
 // quantize_after_mult_and_add mode (:800-811): the caller must use the exact matmul for them.
-extern "C" int b200_qamaa_conv2d(const float* x, const float* w, float* out, const b200_conv_geom* g,
-                                 const float* maxval_dev, int n_bits, float mantissa_bits, int sign_bits, void* stream)
+static int qamaa_conv2d_impl(const float* x, const float* w, float* out, const b200_conv_geom* g, const float* maxval_dev,
+                            int n_bits, float mantissa_bits, int sign_bits, const float* bA_dev, const float* bB_dev,
+                            int64_t bB_stride, void* workspace, size_t workspace_bytes, void* stream)
 {
     if (int rc = check_device()) return rc;
     ConvDims d;
@@ -93,17 +67,39 @@ extern "C" int b200_qamaa_conv2d(const float* x, const float* w, float* out, con
     }
     if (d.rows == 0) return B200_OK;
     if (!x || !w || !out) { set_error("b200_qamaa_conv2d: NULL operand"); return B200_ERR_ARGUMENT; }
-    QamaaOp op;
-    op.maxval_dev = maxval_dev;
-    op.n_bits = n_bits;
-    op.sign_bits = sign_bits;
-    op.mantissa_bits = mantissa_bits;
+    const int E = n_bits - sign_bits - (int)rintf(mantissa_bits);
+    const int dflt = 1 << (E > 0 ? E - 1 : 0);
     for (int grp = 0; grp < g->groups; ++grp) {
         const float* wg = w + (int64_t)grp * d.Ng * d.Kg;     // weight_col[g*Ng:(g+1)*Ng, :] ([N,K] rows, k contiguous)
-        pair_gemm_kernel<QamaaOp><<<pair_gemm_grid(d.rows, d.Ng), 256, 0, (cudaStream_t)stream>>>(
-            make_conv_asrc(x, g, d, grp), BSrc{wg, 1, d.Kg}, out + (int64_t)grp * d.Ng, g->C_out, d.rows, d.Kg, d.Ng,
-            op, nullptr, 0);
-        B200_LAUNCH_CHECK("pair_gemm_kernel<QamaaOp>(conv)");
+        BiasSrc hint{dflt, dflt, bA_dev, nullptr, nullptr, bB_dev ? bB_dev + (int64_t)grp * d.Ng * bB_stride : nullptr,
+                     bB_stride};
+        if (int rc = qamaa_gemm_impl(make_conv_asrc(x, g, d, grp), wg, 1, d.Kg, out + (int64_t)grp * d.Ng, g->C_out,
+                                     d.rows, d.Kg, d.Ng, maxval_dev, n_bits, mantissa_bits, sign_bits,
+                                     bB_dev ? &hint : nullptr, workspace, workspace_bytes, stream))
+            return rc;
     }
     return B200_OK;
+}
+
+extern "C" int b200_qamaa_conv2d(const float* x, const float* w, float* out, const b200_conv_geom* g,
+                                 const float* maxval_dev, int n_bits, float mantissa_bits, int sign_bits, void* stream)
+{
+    return qamaa_conv2d_impl(x, w, out, g, maxval_dev, n_bits, mantissa_bits, sign_bits, nullptr, nullptr, 0, nullptr, 0,
+                             stream);
+}
+
+extern "C" size_t b200_qamaa_conv2d_workspace_bytes(const b200_conv_geom* g)
+{
+    ConvDims d;
+    if (conv_dims(g, &d) != B200_OK) return 0;
+    return b200_qamaa_gemm_workspace_bytes(d.rows, d.Kg, d.Ng);
+}
+
+extern "C" int b200_qamaa_conv2d_fbias(const float* x, const float* w, float* out, const b200_conv_geom* g,
+                                       const float* maxval_dev, int n_bits, float mantissa_bits, int sign_bits,
+                                       const float* bA_dev, const float* bB_dev, int64_t bB_stride, void* workspace,
+                                       size_t workspace_bytes, void* stream)
+{
+    return qamaa_conv2d_impl(x, w, out, g, maxval_dev, n_bits, mantissa_bits, sign_bits, bA_dev, bB_dev, bB_stride,
+                             workspace, workspace_bytes, stream);
 }

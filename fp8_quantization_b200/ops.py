@@ -151,7 +151,18 @@ def _dev_scalar(b, device):
     return b.reshape(-1)[:1].to(device=device, dtype=torch.float32)
 
 
-def qamaa_matmul(x, y, n_bits, maxval, mantissa_bits, sign_bits, out=None):
+def _bias_vec(b, n, device, what):
+    """Per-column exponent-bias hint as (device fp32 vector, stride) -- stride 0 broadcasts one value."""
+    fb = b if torch.is_tensor(b) else torch.tensor([float(b)])
+    fb = fb.reshape(-1).to(device=device, dtype=torch.float32)
+    if fb.numel() == 1:
+        return fb, 0
+    if fb.numel() < n:
+        raise IndexError(f"index out of range: {what} has fewer entries than output columns")
+    return fb, fb.stride(0)
+
+
+def qamaa_matmul(x, y, n_bits, maxval, mantissa_bits, sign_bits, out=None, x_bias=None, y_bias=None):
     """quantize_after_mult_and_add column loop (approx/approx_calculation.py:959-967) in ONE launch:
     C = Q(sum_k Q(x[:,k] * y[k,:])) with Q = quantize_to_fp8_ste_MM(., n_bits, maxval, mantissa_bits,
     sign_bits)[0]; `maxval` is the result quantizer's per-tensor range (read on the device)."""
@@ -171,8 +182,17 @@ def qamaa_matmul(x, y, n_bits, maxval, mantissa_bits, sign_bits, out=None):
     if out is None:
         out = torch.empty((Mrows, N), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
-        rc = lib.b200_qamaa_gemm(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out), out.stride(0),
-                                 Mrows, K, N, _ptr(mv), int(n_bits), mbits, int(sign_bits), _stream())
+        if y_bias is not None:
+            # operand exponent biases known (the fake-quantizers' custom_bias): table kernel
+            fb, sB = _bias_vec(y_bias, N, x.device, "y_bias")
+            fa = _dev_scalar(x_bias, x.device)
+            ws = _workspace(x.device, lib.b200_qamaa_gemm_workspace_bytes(Mrows, K, N))
+            rc = lib.b200_qamaa_gemm_fbias(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out),
+                                           out.stride(0), Mrows, K, N, _ptr(mv), int(n_bits), mbits, int(sign_bits),
+                                           _ptr(fa), _ptr(fb), sB, _ptr(ws), ws.numel(), _stream())
+        else:
+            rc = lib.b200_qamaa_gemm(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out), out.stride(0),
+                                     Mrows, K, N, _ptr(mv), int(n_bits), mbits, int(sign_bits), _stream())
     _lib.check(rc)
     return out
 
@@ -268,7 +288,8 @@ def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, 
     return out
 
 
-def qamaa_conv2d(x, weight, n_bits, maxval, mantissa_bits, sign_bits, stride, padding, dilation, groups):
+def qamaa_conv2d(x, weight, n_bits, maxval, mantissa_bits, sign_bits, stride, padding, dilation, groups,
+                 x_bias=None, w_bias=None):
     """quantize_after_mult_and_add conv (approx/approx_calculation.py:787-795 in the group loop)."""
     lib = _lib.load()
     _require_cuda(x, weight)
@@ -282,8 +303,16 @@ def qamaa_conv2d(x, weight, n_bits, maxval, mantissa_bits, sign_bits, stride, pa
         raise ValueError("quantize_after_mult_and_add needs a per-tensor result range")
     mbits = float(mantissa_bits.item()) if torch.is_tensor(mantissa_bits) else float(mantissa_bits)
     with torch.cuda.device(x.device):
-        rc = lib.b200_qamaa_conv2d(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(mv), int(n_bits), mbits,
-                                   int(sign_bits), _stream())
+        if w_bias is not None:
+            fb, sB = _bias_vec(w_bias, g.C_out, x.device, "weight fp bias")
+            fa = _dev_scalar(x_bias, x.device)
+            ws = _workspace(x.device, lib.b200_qamaa_conv2d_workspace_bytes(ctypes.byref(g)))
+            rc = lib.b200_qamaa_conv2d_fbias(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(mv), int(n_bits),
+                                             mbits, int(sign_bits), _ptr(fa), _ptr(fb), sB, _ptr(ws), ws.numel(),
+                                             _stream())
+        else:
+            rc = lib.b200_qamaa_conv2d(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(mv), int(n_bits), mbits,
+                                       int(sign_bits), _stream())
     _lib.check(rc)
     return out
 

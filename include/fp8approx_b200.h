@@ -144,6 +144,17 @@ int b200_qamaa_gemm(const float *A, int64_t lda, const float *B, int64_t sb_k, i
                     int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *maxval_dev, int n_bits,
                     float mantissa_bits, int sign_bits, void *stream);
 
+/* Same function on the TABLE kernel: the operand exponent biases (the fake-quantizers' custom_bias
+ * tensors, as in b200_approx_gemm_fbias; bA_dev may be NULL -> 2^(E-1)) fix the index range of a pair
+ * table that is rebuilt on the device from `maxval` at every call (maxval moves during calibration).
+ * Operands off that grid, an unsigned grid or n_bits != 8 -> the arithmetic kernel computes the result
+ * (decided on the device / from the arguments; never on the host CPU). */
+size_t b200_qamaa_gemm_workspace_bytes(int64_t Mrows, int64_t K, int64_t N);
+int b200_qamaa_gemm_fbias(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n, float *C,
+                          int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *maxval_dev, int n_bits,
+                          float mantissa_bits, int sign_bits, const float *bA_dev, const float *bB_dev,
+                          int64_t bB_stride, void *workspace, size_t workspace_bytes, void *stream);
+
 /* ---- K3: the non-approx matmul on the tensor cores (tcgen05) ---------------------------------- */
 /* C = A @ B (+ bias) for FAKE-QUANTIZED operands; replaces `x @ y[:, i:i+1]` per column
  * (approx/approx_calculation.py:968-969 Linear, :796-797 BN-conv, :996 / :811 single column) and
@@ -185,6 +196,12 @@ int b200_approx_conv2d_fbias(const float *x, const float *w, float *out, const b
  * (B200_ERR_ARGUMENT): the reference computes those exactly (:810-811). */
 int b200_qamaa_conv2d(const float *x, const float *w, float *out, const b200_conv_geom *g,
                       const float *maxval_dev, int n_bits, float mantissa_bits, int sign_bits, void *stream);
+/* table-kernel variant (see b200_qamaa_gemm_fbias); bB_dev: per-output-channel weight bias */
+size_t b200_qamaa_conv2d_workspace_bytes(const b200_conv_geom *g);
+int b200_qamaa_conv2d_fbias(const float *x, const float *w, float *out, const b200_conv_geom *g,
+                            const float *maxval_dev, int n_bits, float mantissa_bits, int sign_bits,
+                            const float *bA_dev, const float *bB_dev, int64_t bB_stride, void *workspace,
+                            size_t workspace_bytes, void *stream);
 
 /* ---- measurement tool: CUDA-core integer issue peak (roofline denominator) ------ */
 /* Synchronous.  tiops_out: IADD3/LOP3 lane-ops per second in Tiop/s over all SMs; ms_out may be NULL. */

@@ -36,6 +36,7 @@ def main():
     ap.add_argument("--mant-width", type=int, default=3)
     ap.add_argument("--zero-frac", type=float, default=0.5)
     ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--mode", default="approx", choices=["approx", "qamaa"])
     ap.add_argument("--check", action="store_true", help="compare with the arithmetic kernel, bit for bit")
     a = ap.parse_args()
     import torch
@@ -62,6 +63,9 @@ def main():
         _, bR = ops.fp8_fakequant(ref, 8, (ref.abs().max() * 2).reshape(1), mant, 1)
         out = torch.empty((rows, N), device=dev)
         step = lambda: ops.approx_matmul(xq, wq.t(), bA, bB, bR, params, out=out)
+        if a.mode == "qamaa":
+            mv = (ref.abs().max() * 2).reshape(1)
+            step = lambda: ops.qamaa_matmul(xq, wq.t(), 8, mv, mant, 1, out=out, x_bias=bA, y_bias=bB)
         for _ in range(2):
             step()
         torch.cuda.synchronize()
