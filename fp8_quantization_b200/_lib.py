@@ -84,6 +84,8 @@ SIGNATURES = {
     "b200_approx_conv2d_fbias": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_vp, c_i64, c_vp,
                                          ctypes.POINTER(ApproxParams), c_vp, c_sz, c_vp]),
     "b200_qamaa_conv2d": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_int, c_f32, c_int, c_vp]),
+    "b200_bn_act": (c_int, [c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_int, c_i64, c_vp, c_vp, c_vp, c_vp, c_f32, c_int,
+                            c_vp]),
     "b200_int_peak_probe": (c_int, [c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
     "b200_profile_begin": (c_int, []),
     "b200_profile_end": (c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_int)]),

@@ -158,9 +158,105 @@ __global__ void v5_ofuf_kernel(const int32_t* __restrict__ x_int, const int32_t*
     }
 }
 
+// ---- eval-mode BatchNorm + activation epilogue (quantization/quantized_folded_bn.py:66-78) -----------
+// y = act(fma(x, alpha, beta)),  invstd = 1 / sqrt(var + eps),  alpha = gamma * invstd,
+// beta' = fma(-mean, alpha, beta): op for op what ATen's CPU batch_norm evaluates in inference mode
+// (checked bit for bit against torch 2.11 on this container's CPU, tests/golden/make_bn.py), so that a
+// model forward stays bit-identical to the reference run on CPU tensors; cuDNN's kernel rounds
+// differently in ~15 % of the elements.  Input: any 4-D strided view (the hot path produces channels-last
+// [B*Ho*Wo, C] tensors viewed as NCHW); output: contiguous NCHW -- the layout change that the next
+// layer would otherwise pay for with a copy is done here, through a 32 x 32 shared-memory tile.
+struct BnArgs {
+    const float* x;
+    int64_t sb, sc, sp;     // element strides of x: batch, channel, pixel (h*W + w must be linear: sh == W * sw)
+    float* y;               // [B, C, HW] contiguous
+    int64_t B;
+    int C;
+    int64_t HW;
+    const float *mean, *var, *gamma, *beta;
+    float eps;
+    int act;                // 0: none, 1: ReLU, 2: ReLU6
+};
+
+__device__ __forceinline__ float bn_act_apply(float v, float alpha, float beta, int act)
+{
+    float r = fmaf(v, alpha, beta);
+    if (act >= 1) r = fmaxf(r, 0.0f);
+    if (act == 2) r = fminf(r, 6.0f);
+    return r;
+}
+
+// grid: (ceil(HW/32), ceil(C/32), B); block 256 = 32 x 8.  TRANSPOSE: x is channel-fastest.
+template <bool TRANSPOSE>
+__global__ void __launch_bounds__(256) bn_act_kernel(BnArgs a)
+{
+    __shared__ float tile[32][33];
+    __shared__ float s_alpha[32], s_beta[32];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int64_t p0 = (int64_t)blockIdx.x * 32;
+    const int c0 = blockIdx.y * 32;
+    const int64_t b = blockIdx.z;
+    if (threadIdx.x < 32) {
+        const int c = c0 + threadIdx.x;
+        float alpha = 0.0f, beta = 0.0f;
+        if (c < a.C) {
+            const float invstd = 1.0f / sqrtf(__ldg(a.var + c) + a.eps);
+            alpha = (a.gamma ? __ldg(a.gamma + c) : 1.0f) * invstd;
+            beta = fmaf(-__ldg(a.mean + c), alpha, a.beta ? __ldg(a.beta + c) : 0.0f);
+        }
+        s_alpha[threadIdx.x] = alpha;
+        s_beta[threadIdx.x] = beta;
+    }
+    __syncthreads();
+    const float* xb = a.x + b * a.sb;
+    float* yb = a.y + b * (int64_t)a.C * a.HW;
+    if (TRANSPOSE) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {            // read: lanes along channels
+            const int64_t p = p0 + ty + i * 8;
+            const int c = c0 + tx;
+            float v = 0.0f;
+            if (p < a.HW && c < a.C) v = bn_act_apply(__ldg(xb + c * a.sc + p * a.sp), s_alpha[tx], s_beta[tx], a.act);
+            tile[ty + i * 8][tx] = v;            // [pixel][channel]
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {            // write: lanes along pixels
+            const int c = c0 + ty + i * 8;
+            const int64_t p = p0 + tx;
+            if (p < a.HW && c < a.C) yb[(int64_t)c * a.HW + p] = tile[tx][ty + i * 8];
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {            // pixel-fastest input: lanes along pixels for both
+            const int cl = ty + i * 8, c = c0 + cl;
+            const int64_t p = p0 + tx;
+            if (p < a.HW && c < a.C)
+                yb[(int64_t)c * a.HW + p] = bn_act_apply(__ldg(xb + c * a.sc + p * a.sp), s_alpha[cl], s_beta[cl], a.act);
+        }
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_bn_act(const float* x, int64_t sb, int64_t sc, int64_t sp, float* y, int64_t B, int C, int64_t HW,
+                           const float* mean, const float* var, const float* gamma, const float* beta, float eps, int act,
+                           void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (B < 0 || C < 1 || HW < 0 || act < 0 || act > 2) { set_error("b200_bn_act: bad argument"); return B200_ERR_ARGUMENT; }
+    if (B == 0 || HW == 0) return B200_OK;
+    if (!x || !y || !mean || !var) { set_error("b200_bn_act: NULL operand"); return B200_ERR_ARGUMENT; }
+    if (B > 65535) { set_error("b200_bn_act: batch too large for one launch"); return B200_ERR_ARGUMENT; }
+    BnArgs a{x, sb, sc, sp, y, B, C, HW, mean, var, gamma, beta, eps, act};
+    const dim3 grid((unsigned)ceil_div(HW, 32), (unsigned)ceil_div(C, 32), (unsigned)B);
+    if (sc == 1 && sp != 1) bn_act_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    else                    bn_act_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    B200_LAUNCH_CHECK("bn_act_kernel");
+    return B200_OK;
+}
 
 extern "C" int b200_approx_mult_v5(const int32_t* x_int, const int32_t* y_int, const int32_t* x_mant,
                                    const int32_t* y_mant, const int8_t* table_dev, int64_t n, int B_neg, int E, int M,

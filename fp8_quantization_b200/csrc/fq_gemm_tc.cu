@@ -21,6 +21,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <algorithm>
 #include <mutex>
 
 #include "common.cuh"
@@ -112,14 +113,23 @@ struct TcSmem {
     static constexpr int A_BYTES = TC_BM * TC_BK * 2;        // 16 KB
     static constexpr int B_BYTES = BN * TC_BK * 2;
     static constexpr int STAGE = A_BYTES + B_BYTES;
-    static constexpr int BARS = ST * STAGE;                  // full[ST], empty[ST], tmem_full, then the TMEM base
-    static constexpr int TOTAL = BARS + (2 * ST + 1) * 8 + 16 + 1024;   // + slack for the 1024 B alignment
+    static constexpr int BARS = ST * STAGE;                  // full[ST], empty[ST], tmem_full[2], tmem_empty[2], TMEM base
+    static constexpr int TOTAL = BARS + (2 * ST + 4) * 8 + 16 + 1024;   // + slack for the 1024 B alignment
 };
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(bar)) : "memory");
+}
+
+// Persistent: one CTA per SM walks the output tiles (m fastest, so that concurrently running CTAs share
+// the B tile in L2).  Three pipelines run concurrently: TMA -> shared-memory ring (full/empty), MMA ->
+// one of TWO accumulator stages in tensor memory (tmem_full/tmem_empty), epilogue warps draining the
+// other stage -- the epilogue of tile i overlaps the main loop of tile i+1.
 template <int BN, int ST>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
-                  float* __restrict__ C, int64_t ldc, int64_t Mrows, int64_t N, int nkb,
+                  float* __restrict__ C, int64_t ldc, int64_t Mrows, int64_t N, int nkb, int m_blocks, int n_tiles,
                   const float* __restrict__ bias, const int* __restrict__ inexact)
 {
     if (*inexact != 0) return;   // an operand does not fit bf16 exactly: the fp32 kernel takes over
@@ -128,10 +138,10 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     uint8_t* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::BARS);
     uint64_t* empty = full + ST;
-    uint64_t* tmem_full = empty + ST;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+    uint64_t* tmem_full = empty + ST;      // [2]
+    uint64_t* tmem_empty = tmem_full + 2;  // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * BN;
 
     if (threadIdx.x == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
@@ -139,11 +149,11 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < ST; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
-        mbar_init(tmem_full, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 2) {   // one warp allocates BN fp32 accumulator columns of tensor memory
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(tmem_slot)), "r"((uint32_t)BN) : "memory");
+    if (warp == 2) {   // one warp allocates two accumulator stages of BN fp32 columns each
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(tmem_slot)), "r"((uint32_t)(2 * BN)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
@@ -153,65 +163,84 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 
     if (warp == 0 && lane == 0) {
         // ===== TMA producer =====
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % ST;
-            mbar_wait(empty + s, ((kb / ST) & 1) ^ 1);
-            mbar_expect_tx(full + s, L::STAGE);
-            tma_load_2d(smem + s * L::STAGE, &mapA, full + s, kb * TC_BK, m0);
-            tma_load_2d(smem + s * L::STAGE + L::A_BYTES, &mapB, full + s, kb * TC_BK, n0);
+        int it = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const int m0 = (tile % m_blocks) * TC_BM, n0 = (tile / m_blocks) * BN;
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+                const int s = it % ST;
+                mbar_wait(empty + s, ((it / ST) & 1) ^ 1);
+                mbar_expect_tx(full + s, L::STAGE);
+                tma_load_2d(smem + s * L::STAGE, &mapA, full + s, kb * TC_BK, m0);
+                tma_load_2d(smem + s * L::STAGE + L::A_BYTES, &mapB, full + s, kb * TC_BK, n0);
+            }
         }
     } else if (warp == 1 && lane == 0) {
         // ===== MMA issuer: one thread drives the tensor core for the whole CTA =====
         constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN);
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % ST;
-            mbar_wait(full + s, (kb / ST) & 1);
+        int it = 0, ti = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++ti) {
+            const int as = ti & 1;
+            mbar_wait(tmem_empty + as, ((ti >> 1) & 1) ^ 1);     // the epilogue has drained this accumulator stage
             tc_fence_after();
-            const uint64_t adesc = umma_desc_sw128(s32(smem + s * L::STAGE));
-            const uint64_t bdesc = umma_desc_sw128(s32(smem + s * L::STAGE + L::A_BYTES));
+            const uint32_t d_tmem = tmem + (uint32_t)(as * BN);
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+                const int s = it % ST;
+                mbar_wait(full + s, (it / ST) & 1);
+                tc_fence_after();
+                const uint64_t adesc = umma_desc_sw128(s32(smem + s * L::STAGE));
+                const uint64_t bdesc = umma_desc_sw128(s32(smem + s * L::STAGE + L::A_BYTES));
 #pragma unroll
-            for (int k = 0; k < TC_BK / TC_UK; ++k)   // +32 B (= 2 sixteen-byte units) per K step inside the swizzle row
-                tc_mma_bf16(tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
-            tc_commit(empty + s);      // frees the stage when these MMAs have read it
+                for (int k = 0; k < TC_BK / TC_UK; ++k)   // +32 B (= 2 sixteen-byte units) per K step inside the swizzle row
+                    tc_mma_bf16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+                tc_commit(empty + s);      // frees the stage when these MMAs have read it
+            }
+            tc_commit(tmem_full + as);     // accumulator complete
         }
-        tc_commit(tmem_full);          // accumulator complete
     } else if (warp >= 4) {
         // ===== epilogue: TMEM -> registers -> (+bias) -> global fp32 =====
-        mbar_wait(tmem_full, 0);
-        tc_fence_after();
         const int w = warp - 4;                       // == warp % 4: the TMEM lane quarter this warp may read
-        const int64_t row = (int64_t)m0 + w * 32 + lane;
-        float* crow = C + row * ldc;
         const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+        int ti = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++ti) {
+            const int m0 = (tile % m_blocks) * TC_BM, n0 = (tile / m_blocks) * BN;
+            const int as = ti & 1;
+            mbar_wait(tmem_full + as, (ti >> 1) & 1);
+            tc_fence_after();
+            const int64_t row = (int64_t)m0 + w * 32 + lane;
+            float* crow = C + row * ldc;
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-            uint32_t v[32];
-            tc_ld32(tmem + ((uint32_t)(w * 32) << 16) + (uint32_t)(c * 32), v);
-            const int64_t n = (int64_t)n0 + c * 32;
-            if (row < Mrows && n < N) {
-                if (vec_ok && n + 32 <= N) {
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t v[32];
+                tc_ld32(tmem + ((uint32_t)(w * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
+                const int64_t n = (int64_t)n0 + c * 32;
+                if (row < Mrows && n < N) {
+                    if (vec_ok && n + 32 <= N) {
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        float4 o = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
-                                               __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
-                        if (bias) {
-                            const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + n + j));
-                            o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+                        for (int j = 0; j < 32; j += 4) {
+                            float4 o = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                                   __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+                            if (bias) {
+                                const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + n + j));
+                                o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+                            }
+                            *reinterpret_cast<float4*>(crow + n + j) = o;
                         }
-                        *reinterpret_cast<float4*>(crow + n + j) = o;
-                    }
-                } else {
+                    } else {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (n + j < N) crow[n + j] = __uint_as_float(v[j]) + (bias ? __ldg(bias + n + j) : 0.0f);
+                        for (int j = 0; j < 32; ++j)
+                            if (n + j < N) crow[n + j] = __uint_as_float(v[j]) + (bias ? __ldg(bias + n + j) : 0.0f);
+                    }
                 }
             }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty + as);    // this warp's quarter of the stage is drained
         }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 2)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)BN) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)(2 * BN)) : "memory");
 }
 
 // ---- convert pass: fp32 operand -> bf16 plane [rows][Kp], k contiguous, zero padded to Kp ---------
@@ -223,29 +252,32 @@ __global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ 
 {
     int bad = 0;
     if (SRC_K_CONTIG) {
-        // one thread: 4 consecutive k of one row (float4 when the source allows it)
+        // one thread: 8 consecutive k of one row (two float4 loads when the source allows it, one 16-byte store)
         const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-        const int64_t per_row = Kp / 4;
+        const int64_t per_row = Kp / 8;
         if (q < rows * per_row) {
-            const int64_t r = q / per_row, k = (q % per_row) * 4;
+            const int64_t r = q / per_row, k = (q % per_row) * 8;
             const float* p = src + r * s_row + k;
-            float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-            if (k + 3 < K && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
-                const float4 t = __ldg(reinterpret_cast<const float4*>(p));
-                v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+            float v[8] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+            if (k + 7 < K && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
+                const float4 t0 = __ldg(reinterpret_cast<const float4*>(p));
+                const float4 t1 = __ldg(reinterpret_cast<const float4*>(p) + 1);
+                v[0] = t0.x; v[1] = t0.y; v[2] = t0.z; v[3] = t0.w;
+                v[4] = t1.x; v[5] = t1.y; v[6] = t1.z; v[7] = t1.w;
             } else {
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
+                for (int j = 0; j < 8; ++j)
                     if (k + j < K) v[j] = __ldg(p + j);
             }
-            uint32_t h[4];
+            uint32_t h[8];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < 8; ++j) {
                 const uint32_t b = __float_as_uint(v[j]);
                 bad |= (b & 0xFFFFu) != 0;
                 h[j] = b >> 16;
             }
-            *reinterpret_cast<uint2*>(dst + r * Kp + k) = make_uint2(h[0] | (h[1] << 16), h[2] | (h[3] << 16));
+            *reinterpret_cast<uint4*>(dst + r * Kp + k) =
+                make_uint4(h[0] | (h[1] << 16), h[2] | (h[3] << 16), h[4] | (h[5] << 16), h[6] | (h[7] << 16));
         }
     } else {
         // source contiguous along rows (a [K, N] row-major right operand): 32 x 32 transpose tile
@@ -357,12 +389,12 @@ extern "C" int b200_fq_gemm_tc(const float* A, int64_t lda, const float* B, int6
     __nv_bfloat16* Bh = Ah + Mrows * Kp;
     B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
     {
-        const int64_t n = Mrows * (Kp / 4);
+        const int64_t n = Mrows * (Kp / 8);
         to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(A, lda, 1, Ah, Mrows, K, Kp, flag);
         B200_LAUNCH_CHECK("to_bf16_kernel<A>");
     }
     if (sb_k == 1) {
-        const int64_t n = N * (Kp / 4);
+        const int64_t n = N * (Kp / 8);
         to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(B, sb_n, 1, Bh, N, K, Kp, flag);
     } else {
         to_bf16_kernel<false><<<dim3((unsigned)ceil_div(N, 32), (unsigned)(Kp / 32)), 256, 0, st>>>(B, sb_n, sb_k, Bh, N, K, Kp, flag);
@@ -370,6 +402,13 @@ extern "C" int b200_fq_gemm_tc(const float* A, int64_t lda, const float* B, int6
     B200_LAUNCH_CHECK("to_bf16_kernel<B>");
 
     const int nkb = (int)(Kp / TC_BK);
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
     CUtensorMap mapA, mapB;
     if (int rc = make_map(enc, &mapA, Ah, Mrows, Kp, TC_BM)) return rc;
     if (N > 128) {
@@ -377,15 +416,17 @@ extern "C" int b200_fq_gemm_tc(const float* A, int64_t lda, const float* B, int6
         if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
         static bool attr = false;
         if (!attr) { B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN, ST>::TOTAL)); attr = true; }
-        fq_gemm_tc_kernel<BN, ST><<<dim3((unsigned)ceil_div(Mrows, TC_BM), (unsigned)ceil_div(N, BN)), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
-            mapA, mapB, C, ldc, Mrows, N, nkb, bias_dev, flag);
+        const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
+        fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
+            mapA, mapB, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
     } else {
         constexpr int BN = 128, ST = 4;
         if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
         static bool attr = false;
         if (!attr) { B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN, ST>::TOTAL)); attr = true; }
-        fq_gemm_tc_kernel<BN, ST><<<dim3((unsigned)ceil_div(Mrows, TC_BM), (unsigned)ceil_div(N, BN)), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
-            mapA, mapB, C, ldc, Mrows, N, nkb, bias_dev, flag);
+        const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
+        fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
+            mapA, mapB, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
     }
     B200_LAUNCH_CHECK("fq_gemm_tc_kernel");
     // runs only if the convert pass found an operand that is not exact in bf16

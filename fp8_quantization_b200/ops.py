@@ -403,6 +403,28 @@ def approx_mult_v5(x_int, y_int, B_neg, x_mant, y_mant, comp_table_NN, sim_hw_ad
     return out
 
 
+def bn_act(x, running_mean, running_var, gamma, beta, eps, act=0):
+    """Eval-mode BatchNorm + activation (quantization/quantized_folded_bn.py:66-78) with ATen's CPU op sequence
+    (bit-identical to the reference on CPU tensors).  x: [B,C,H,W] in any layout whose (h,w) plane is linear
+    (contiguous or channels-last); returns a contiguous NCHW tensor.  act: 0 none, 1 ReLU, 2 ReLU6."""
+    lib = _lib.load()
+    _require_cuda(x)
+    assert x.dim() == 4
+    if x.dtype != torch.float32:
+        x = x.float()
+    B, C, H, W = x.shape
+    if W > 1 and H > 1 and x.stride(2) != W * x.stride(3):
+        x = x.contiguous()
+    sp = x.stride(3) if W > 1 else (x.stride(2) if H > 1 else 1)
+    y = torch.empty((B, C, H, W), dtype=torch.float32, device=x.device)
+    f = lambda t: None if t is None else t.detach().to(device=x.device, dtype=torch.float32).contiguous()
+    m, v, g, b = f(running_mean), f(running_var), f(gamma), f(beta)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.b200_bn_act(_ptr(x), x.stride(0), x.stride(1), sp, _ptr(y), B, C, H * W, _ptr(m), _ptr(v),
+                                   _ptr(g), _ptr(b), float(eps), int(act), _stream()))
+    return y
+
+
 def kernel_launches():
     return int(_lib.load().b200_kernel_launches())
 

@@ -409,6 +409,27 @@ class QuantizationHijacker(QuantizedModule):
 
 
 # ---- BNFusedHijacker (quantized_folded_bn.py:12-95) ---------------------------------------------
+FUSED_BN_EPILOGUE = True   # False: torch's F.batch_norm (cuDNN) + activation, as separate launches
+
+
+def _act_code(fn):
+    """0 none, 1 ReLU, 2 ReLU6; -1 for anything the fused epilogue does not evaluate itself."""
+    if fn is None:
+        return 0
+    if isinstance(fn, nn.ReLU6):
+        return 2
+    if isinstance(fn, nn.ReLU):
+        return 1
+    return -1
+
+
+def _fusable_act(fn):
+    """Activation code the kernel applies: the layer's own if it is ReLU / ReLU6 / none, else 0 (BN only; the
+    activation then runs afterwards as in the reference)."""
+    code = _act_code(fn)
+    return code if code >= 0 else 0
+
+
 class BNFusedHijacker(QuantizationHijacker):
     def __init__(self, *args, **kwargs):
         kwargs.pop("bias", None)
@@ -431,10 +452,19 @@ class BNFusedHijacker(QuantizationHijacker):
 
     def forward(self, x):
         res = self._core(x)
-        res = F.batch_norm(res, self.running_mean, self.running_var, self.gamma, self.beta, self.training,
-                           self.momentum, self.epsilon)
-        if self.activation_function is not None:
-            res = self.activation_function(res)
+        fused = FUSED_BN_EPILOGUE and not self.training and res.dim() == 4 and res.is_cuda
+        act = _fusable_act(self.activation_function) if fused else None
+        if fused and act is not None:
+            # F.batch_norm + activation (quantized_folded_bn.py:66-78) as ONE kernel that evaluates ATen's CPU op
+            # sequence (bit-identical to the reference on CPU tensors) and writes contiguous NCHW
+            from . import ops
+            res = ops.bn_act(res, self.running_mean, self.running_var, self.gamma, self.beta, self.epsilon, act)
+            res = res if act == _act_code(self.activation_function) else self.activation_function(res)
+        else:
+            res = F.batch_norm(res, self.running_mean, self.running_var, self.gamma, self.beta, self.training,
+                               self.momentum, self.epsilon)
+            if self.activation_function is not None:
+                res = self.activation_function(res)
         if not self.quantize_input and self._quant_a:
             res = self.activation_quantizer(res)
         return res

@@ -203,6 +203,16 @@ int b200_qamaa_conv2d_fbias(const float *x, const float *w, float *out, const b2
                             const float *bA_dev, const float *bB_dev, int64_t bB_stride, void *workspace,
                             size_t workspace_bytes, void *stream);
 
+/* ---- N2: eval-mode BatchNorm + activation epilogue, quantization/quantized_folded_bn.py:66-78 ------- */
+/* y = act(fma(x, alpha, beta')) with invstd = 1/sqrt(var+eps), alpha = gamma*invstd,
+ * beta' = fma(-mean, alpha, beta): the op sequence of ATen's CPU batch_norm in inference mode (bit-identical
+ * to the reference run on CPU tensors).  x: 4-D tensor given by element strides (batch sb, channel sc,
+ * pixel sp with pixel = h*W + w, i.e. stride(h) == W*stride(w)); y: contiguous NCHW.  gamma / beta may be
+ * NULL (1 / 0).  act: 0 none, 1 ReLU, 2 ReLU6. */
+int b200_bn_act(const float *x, int64_t sb, int64_t sc, int64_t sp, float *y, int64_t B, int C, int64_t HW,
+                const float *mean, const float *var, const float *gamma, const float *beta, float eps, int act,
+                void *stream);
+
 /* ---- measurement tool: CUDA-core integer issue peak (roofline denominator) ------ */
 /* Synchronous.  tiops_out: IADD3/LOP3 lane-ops per second in Tiop/s over all SMs; ms_out may be NULL. */
 int b200_int_peak_probe(int iters, double *tiops_out, double *ms_out);

@@ -46,8 +46,9 @@ def main():
     dev = torch.device("cuda", 0)
     M = a.mant_width
     E = 7 - M
+    # mant_width 2 (E5M2) has no reference answer (approx_v9 raises for it): all-zero table, "parity unpinned"
     params = ops.make_params(dict(expo_width=E, mant_width=M, dnsmp_factor=3, withComp=True, with_approx=True,
-                                  with_s2nn2s_opt=True, quant_btw_mult_accu=True))
+                                  with_s2nn2s_opt=True, quant_btw_mult_accu=True), allow_unpinned_format=(M == 2))
     g = torch.Generator(device="cpu").manual_seed(10)
     mant = torch.tensor([float(M)])
     tot_ms = tot_kern = tot_macs = 0.0
