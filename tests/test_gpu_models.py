@@ -67,11 +67,27 @@ def test_model_against_reference(case):
                 if got.shape != want.shape or err > tol:
                     bad.append((lname, tag, err, tol))
         assert not bad, bad
-        # end to end (fresh calibration of the whole network)
+        # end to end (fresh calibration of the whole network); where the golden file holds probes, a fixed
+        # sample of EVERY hot-path layer's output is compared bit for bit on the way (no teacher forcing)
+        phase, probe_bad, hooks = ["cal"], [], []
+        if name in mc.PROBED_CASES:
+            for li, (lname, mod) in enumerate((n, m) for n, m in mods.items() if hasattr(m, "run_forward")):
+                def probe(mod, inp, outp, lname=lname, li=li):
+                    flat = outp.detach().contiguous().reshape(-1)
+                    got = flat[mc.probe_indices(flat.numel(), li).to(flat.device)].cpu().numpy()
+                    want = z[f"{name}_{lname}_p{phase[0]}"]
+                    n_bad = int(((got.view(np.uint32) != want.view(np.uint32)) & ~((got == 0) & (want == 0))).sum())
+                    if n_bad:
+                        probe_bad.append((phase[0], lname, n_bad, float(np.abs(got - want).max())))
+                hooks.append(mod.register_forward_hook(probe))
         model.estimate_ranges()
         y_cal = model(mc.images(batch, size, 1).cuda())
         model.fix_ranges()
+        phase[0] = "eval"
         y_eval = model(mc.images(batch, size, 2).cuda())
+        for h in hooks:
+            h.remove()
+        assert not probe_bad, probe_bad[:5]
     for tag, got in (("cal", y_cal), ("eval", y_eval)):
         want = z[f"{name}_y{tag}"]
         err = float(np.abs(got.cpu().numpy().astype(np.float64) - want).max())
