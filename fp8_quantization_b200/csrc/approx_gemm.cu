@@ -143,9 +143,10 @@ struct PredecodeArgs {
     BiasSrc bias;
     int* offgrid;          // raised if any element cannot take the table path
     unsigned long long* zero_count;   // A operand: number of zero elements (sampled; picks the GEMM's k loop), or null
+    int* tmax;                        // split-K only: atomicMax of the operand's table row index (bounds the addends)
 };
 
-__device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int bA, int& off)
+__device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int bA, int& off, int& tmax)
 {
     const uint32_t bits = __float_as_uint(v);
     const uint32_t mag = bits & 0x7FFFFFFFu;
@@ -162,10 +163,11 @@ __device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int b
     }
     const uint32_t mA = frac >> (23 - M);
     const uint32_t sa = bits >> 31;
+    tmax = max(tmax, tA);
     return 2u * (uint32_t)(g.row_entries * (tA + g.NT * (int)(mA + (sa << M))));
 }
 
-__device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int bA, int bB, int bR, int& off)
+__device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int bA, int bB, int bR, int& off, int& tmax)
 {
     const uint32_t bits = __float_as_uint(v);
     const uint32_t mag = bits & 0x7FFFFFFFu;
@@ -181,6 +183,7 @@ __device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int b
         return zero_b;
     }
     if (tB < -g.RA) tB = -g.RA;
+    tmax = max(tmax, tB + g.RA);
     const uint32_t mB = frac >> (23 - M);
     const uint32_t boff = 2u * (mB + (uint32_t)(g.row_entries * (tB + g.RA)));
     if (g.sidx) return boff + ((bits >> 31) ? 2u * (uint32_t)g.s_stride : 0u);   // sign of b selects a region
@@ -195,7 +198,7 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
     __shared__ uint32_t tile[32][33];
     const int64_t r0 = (int64_t)blockIdx.x * 32, k0 = (int64_t)blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
-    int off = 0, zeros = 0;
+    int off = 0, zeros = 0, tmax = 0;
     const int bA = a.bias.A(), bR = a.bias.R();
     if (bA <= -64 || bA >= 64 || bR <= -64 || bR >= 64) off = 1;
     if (SRC_K_CONTIG) {
@@ -205,7 +208,7 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
             uint32_t w = IS_B ? (g.sidx ? 0u : (kBf16One << 16)) : 2u * (uint32_t)g.zeroA_off;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
-                w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off) : predecode_a(g, v, bA, off);
+                w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax) : predecode_a(g, v, bA, off, tmax);
                 if (!IS_B) zeros += (v == 0.0f);
             }
             tile[tx][ty + i * 8] = w;   // [k][r]
@@ -223,13 +226,17 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
             uint32_t w = IS_B ? (g.sidx ? 0u : (kBf16One << 16)) : 2u * (uint32_t)g.zeroA_off;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
-                w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off) : predecode_a(g, v, bA, off);
+                w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax) : predecode_a(g, v, bA, off, tmax);
                 if (!IS_B) zeros += (v == 0.0f);
             }
             if (k < a.Kpad && r < a.Rpad) a.dst[k * a.Rpad + r] = w;
         }
     }
     if (off) *a.offgrid = 1;
+    if (a.tmax) {
+        tmax = __reduce_max_sync(0xFFFFFFFFu, tmax);
+        if ((threadIdx.x & 31) == 0 && tmax > *(volatile int*)a.tmax) atomicMax(a.tmax, tmax);
+    }
     // zero statistics of the A operand, sampled: one block in 8 along the rows counts its zeros and its
     // elements (one 64-bit atomic: zeros in the low half, elements in the high half)
     if (!IS_B && a.zero_count && (blockIdx.x & 7) == 0) {
@@ -258,7 +265,7 @@ __global__ void __launch_bounds__(PC_ROWS) predecode_conv_kernel(PredecodeArgs a
     const ASrc& s = a.asrc;
     const int64_t r = (int64_t)blockIdx.x * PC_ROWS + threadIdx.x;
     const int k0 = blockIdx.y * PC_KCH;
-    int off = 0, zeros = 0;
+    int off = 0, zeros = 0, tmax = 0;
     const int bA = a.bias.A(), bR = a.bias.R();
     if (bA <= -64 || bA >= 64 || bR <= -64 || bR >= 64) off = 1;
     const bool valid_r = r < a.rows;
@@ -280,13 +287,17 @@ __global__ void __launch_bounds__(PC_ROWS) predecode_conv_kernel(PredecodeArgs a
             const int h = h0 + ky * s.dh, wi = w0 + kx * s.dw;
             float v = 0.0f;                                              // F.pad zeros (:727)
             if (h >= 0 && h < s.H && wi >= 0 && wi < s.W) v = __ldg(base + ((int64_t)c * s.H + h) * s.W + wi);
-            w = predecode_a(g, v, bA, off);
+            w = predecode_a(g, v, bA, off, tmax);
             zeros += (v == 0.0f);
         }
         dst[(int64_t)kk * a.Rpad] = w;
         if (++kx == s.kw) { kx = 0; if (++ky == s.kh) { ky = 0; ++c; } }
     }
     if (off) *a.offgrid = 1;
+    if (a.tmax) {
+        tmax = __reduce_max_sync(0xFFFFFFFFu, tmax);
+        if ((threadIdx.x & 31) == 0 && tmax > *(volatile int*)a.tmax) atomicMax(a.tmax, tmax);
+    }
     if (a.zero_count && (blockIdx.x & 7) == 0) {   // sampled zero statistics, as in predecode_kernel
         __shared__ int s_zeros;
         if (threadIdx.x == 0) s_zeros = 0;
@@ -381,6 +392,16 @@ struct LutGemmArgs {
     const int* offgrid;
     int qamaa;            // 1: epilogue applies the result quantizer to the sum (quantize_after_mult_and_add)
     QamaaOp qop;
+    // split-K (grids that cannot fill the SMs): blockIdx.z owns a slice of the k tiles and stores its partial
+    // sums, in units of u, to `partial`; splitk_reduce_kernel adds the slices in order.  That changes the
+    // summation order, so it is only USED when every sum involved is provably exact in fp32 (see below);
+    // otherwise *inexact is raised and the unsplit kernel (gate != null) recomputes the output.
+    int splits;
+    float* partial;       // [splits][Mrows][N]
+    int* inexact;
+    const int* tmax;      // [2]: largest table row index of A / of B seen by the predecode pass
+    int t_bias;           // t = tA_idx + tB_idx - t_bias
+    const int* gate;      // non-null: run only if *gate != 0
 };
 
 // KT: k-tile depth (8 where a large table leaves little shared memory for the operand ring).
@@ -393,6 +414,7 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     static_assert(CPL == 4 || CPL == 2, "a lane owns 2 or 4 consecutive columns");
     static_assert(RPW % 4 == 0, "A words are read 4 at a time");
     if (*a.offgrid != 0) return;   // some operand is off the FP8 grid: the generic kernel takes over
+    if (a.gate && *a.gate == 0) return;
     extern __shared__ __align__(16) unsigned char smem[];
     uint32_t* As = reinterpret_cast<uint32_t*>(smem + a.lut_bytes);   // [ST][KT][BM]
     uint32_t* Bs = As + ST * KT * BM;                                 // [ST][KT][BN]
@@ -429,11 +451,14 @@ approx_gemm_lut_kernel(LutGemmArgs a)
 #pragma unroll
         for (int j = 0; j < CPL; ++j) acc[i][j] = 0.0f;
 
-    const int nk = a.Kpad / KT;
+    const int nk_all = a.Kpad / KT;
+    const int kt0 = (a.splits > 1) ? (int)((int64_t)blockIdx.z * nk_all / a.splits) : 0;
+    const int nk = ((a.splits > 1) ? (int)((int64_t)(blockIdx.z + 1) * nk_all / a.splits) : nk_all) - kt0;
+    float macc = 0.0f;   // split-K: largest |partial sum| seen at a k-tile boundary
     const uint32_t zero_word = a.zero_word;
 #pragma unroll
     for (int s = 0; s < ST - 1; ++s) {
-        if (s < nk) load_tile(s, s);
+        if (s < nk) load_tile(kt0 + s, s);
         cp_async_commit();
     }
     // The k loop exists twice: dense activations use the predicated row (no branches, full ILP across
@@ -443,7 +468,7 @@ approx_gemm_lut_kernel(LutGemmArgs a)
         for (int kt = 0; kt < nk; ++kt) {
             cp_async_wait<ST - 2>();
             __syncthreads();
-            if (kt + ST - 1 < nk) load_tile(kt + ST - 1, (kt + ST - 1) % ST);
+            if (kt + ST - 1 < nk) load_tile(kt0 + kt + ST - 1, (kt + ST - 1) % ST);
             cp_async_commit();
             const uint32_t* Asm = As + (kt % ST) * KT * BM + warp * RPW;
             const uint32_t* Bsm = Bs + (kt % ST) * KT * BN + lane * CPL;
@@ -486,6 +511,12 @@ approx_gemm_lut_kernel(LutGemmArgs a)
                     }
                 }
             }
+            if (a.splits > 1) {
+#pragma unroll
+                for (int i = 0; i < RPW; ++i)
+#pragma unroll
+                    for (int j = 0; j < CPL; ++j) macc = fmaxf(macc, fabsf(acc[i][j]));
+            }
         }
     };
     // sampled zero statistics of the activations (predecode pass): low half zeros, high half elements
@@ -496,6 +527,30 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     else            mainloop(std::false_type{});
     cp_async_wait<0>();
 
+    if (a.splits > 1) {
+        // Exactness certificate.  Table entries are integers (units of u) of magnitude <= 2^(t + M + 1), so one
+        // k tile moves a running sum by at most D = KT * 2^(t_max + M + 1).  If every slice's running sum stayed
+        // within (2^24 - D) / splits at all of its k-tile boundaries, then every intermediate sum of every slice,
+        // of the ordered combination of the slices AND of the unsplit k-ascending order is an integer of
+        // magnitude <= 2^24: all of them are exact in fp32, hence the result is bit-identical to the unsplit
+        // kernel's.
+        const int t_max = a.tmax[0] + a.tmax[1] - a.t_bias;
+        int lg = 0;
+        while ((1 << lg) < KT) ++lg;
+        const int dl = t_max + a.M + 1 + lg;   // log2 of D, the most one k tile can move a sum
+        if (dl > 23 || !(macc * (float)a.splits <= 16777216.0f - (float)(1 << (dl > 0 ? dl : 0)))) *a.inexact = 1;
+        float* P = a.partial + (int64_t)blockIdx.z * a.Mrows * a.N;
+        const int64_t n = n0 + lane * CPL;
+#pragma unroll
+        for (int i = 0; i < RPW; ++i) {
+            const int64_t m = m0 + warp * RPW + i;
+            if (m >= a.Mrows) break;
+#pragma unroll
+            for (int j = 0; j < CPL; ++j)
+                if (n + j < a.N) P[m * a.N + n + j] = acc[i][j];
+        }
+        return;
+    }
     // epilogue: C = acc * u (exact power-of-two scaling); quantize_after_mult_and_add: C = Q(acc * u)
     const float unit = pow2f_i(1 - a.bias.R() - a.M);
     if (a.qamaa) {
@@ -527,6 +582,26 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     }
 }
 
+// Ordered sum of the split-K slices; does nothing when the exactness certificate failed.
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ P, int splits, float* __restrict__ C,
+                                                            int64_t ldc, int64_t Mrows, int64_t N, BiasSrc bias, int M,
+                                                            int qamaa, QamaaOp qop, const int* __restrict__ inexact,
+                                                            const int* __restrict__ offgrid)
+{
+    if (*inexact != 0 || *offgrid != 0) return;
+    const float unit = pow2f_i(1 - bias.R() - M);
+    if (qamaa) qop.begin();
+    const int64_t total = Mrows * N, stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        float s = P[i];
+        for (int z = 1; z < splits; ++z) s += P[(int64_t)z * total + i];
+        s *= unit;
+        if (qamaa) s = qop.quant(s);
+        const int64_t m = i / N;
+        C[m * ldc + (i - m * N)] = s;
+    }
+}
+
 // Tile configurations and the host-side choice between them.
 struct LutTileCfg {
     int warps, rpw, cpl, kt, sidx;
@@ -551,18 +626,40 @@ static const LutTileCfg kLutTiles[] = {
     LUT_TILE(4, 16, 2, 16, 1),
 };
 
-// Cost model: an SM's table-lookup rate saturates with 8 resident warps; a CTA's work is BM*BN per
-// k; CTAs are dealt round-robin over the SMs, `r` resident at a time.
-static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int lut_bytes, int sidx, int sms)
+// Largest split-K factor the workspace reserves partial-sum room for (32 MB at most).
+static int max_splits(int64_t Mrows, int64_t N)
+{
+    const int64_t el = Mrows * N;
+    if (el <= 0 || el > ((int64_t)1 << 21)) return 1;
+    return (int)std::min<int64_t>(8, ((int64_t)8 << 20) / el);
+}
+static size_t splitk_partial_bytes(int64_t Mrows, int64_t N)
+{
+    const int s = max_splits(Mrows, N);
+    return s > 1 ? round_up((size_t)s * Mrows * N * 4, 256) : 0;
+}
+
+// Cost model (in table lookups per SM): an SM's lookup rate saturates with 8 resident warps; a CTA does
+// BM*BN lookups per k; CTAs are dealt round-robin over the SMs, `r` resident at a time.  Splitting k by S
+// multiplies the CTA count and divides each CTA's k range; it costs a pipeline prologue/epilogue per CTA
+// and two more launches (the ordered reduction and the gated unsplit fallback).
+static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int64_t Kpad, int lut_bytes, int sidx, int sms,
+                                         int max_s, int* splits)
 {
     const LutTileCfg* best = nullptr;
     double best_cost = 0;
+    *splits = 1;
+    int forced_s = 0;
+    if (const char* e = getenv("B200_LUT_SPLITK")) forced_s = std::max(1, std::min(atoi(e), max_s));   // experiments / tests
     if (const char* e = getenv("B200_LUT_TILE")) {   // experiments: force a tile configuration by index
         const int i = atoi(e);
         if (i >= 0 && i < (int)(sizeof(kLutTiles) / sizeof(kLutTiles[0])) && kLutTiles[i].sidx == sidx &&
-            kLutTiles[i].smem(lut_bytes) + 1024 <= 227 * 1024)
+            kLutTiles[i].smem(lut_bytes) + 1024 <= 227 * 1024) {
+            if (forced_s && Kpad / kLutTiles[i].kt >= forced_s) *splits = forced_s;
             return &kLutTiles[i];
+        }
     }
+    for (int pass = 0; pass < 2 && !best; ++pass, forced_s = 0)
     for (const LutTileCfg& c : kLutTiles) {
         if (c.sidx != sidx) continue;
         const size_t sm = c.smem(lut_bytes) + 1024;
@@ -572,14 +669,21 @@ static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int lut_bytes
         r = std::min(r, 65536 / (acc_regs * 32 * c.warps));
         r = std::min(r, 64 / c.warps);
         if (r < 1) continue;
-        const int64_t nc = ceil_div(Mrows, c.BM()) * ceil_div(N, c.BN());
-        const int64_t full = nc / ((int64_t)sms * r), rem = nc - full * sms * r;
-        const int rem_per_sm = (int)ceil_div(rem, sms);
-        const double T = (double)c.BM() * c.BN() * (c.cpl == 2 ? 1.06 : 1.0) * (c.kt < 16 ? 1.05 : 1.0);
+        const int64_t nk = Kpad / c.kt;
+        const double T = (double)c.BM() * c.BN() * c.kt * (c.cpl == 2 ? 1.06 : 1.0) * (c.kt < 16 ? 1.05 : 1.0);
         auto rate = [&](int ctas) { return std::min(1.0, ctas * c.warps / 8.0); };
-        double cost = full * r * T / rate(r);
-        if (rem_per_sm > 0) cost += rem_per_sm * T / rate(rem_per_sm);
-        if (!best || cost < best_cost) { best = &c; best_cost = cost; }
+        for (int S = 1; S <= max_s; ++S) {
+            if (forced_s && S != forced_s) continue;
+            if (S > 1 && nk / S < 4) break;
+            const int64_t nc = ceil_div(Mrows, c.BM()) * ceil_div(N, c.BN()) * S;
+            const int64_t full = nc / ((int64_t)sms * r), rem = nc - full * sms * r;
+            const int rem_per_sm = (int)ceil_div(rem, sms);
+            const double Tc = T * ((double)ceil_div(nk, S) + 2.0);
+            double cost = full * r * Tc / rate(r);
+            if (rem_per_sm > 0) cost += rem_per_sm * Tc / rate(rem_per_sm);
+            if (S > 1) cost += 3.0e5 + 4.0 * (double)S * Mrows * N / sms;
+            if (!best || cost < best_cost) { best = &c; best_cost = cost; *splits = S; }
+        }
     }
     return best;
 }
@@ -719,17 +823,31 @@ static void prof_record(bool start, cudaStream_t st)
 }
 
 constexpr int64_t kPadM = 256, kPadN = 128, kPadK = 32;
-constexpr size_t kFlagBytes = 256;
+constexpr size_t kFlagBytes = 256;   // ints: [0] off-grid, [2..3] zero statistics, [4..5] row maxima, [6] split-K inexact
+static thread_local int g_last_splits = 1;
 
 // Predecode of both operands + the table GEMM launch, shared by the approx path and the
 // quantize_after_mult_and_add path (whose table and result bias live in the workspace).
 static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc,
                         int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const LutGeom& geom,
                         const uint16_t* d_lut, int lut_bytes, int* flag, uint32_t* Aw, uint32_t* Bw, int64_t Mpad,
-                        int64_t Npad, int64_t Kpad, const QamaaOp* qop, cudaStream_t st)
+                        int64_t Npad, int64_t Kpad, const QamaaOp* qop, float* partial, cudaStream_t st)
 {
     const int M = geom.M;
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+        for (const LutTileCfg& c : kLutTiles)
+            B200_CUDA_TRY(cudaFuncSetAttribute(c.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    }
+    int S = 1;
+    const LutTileCfg* tc = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, partial ? max_splits(Mrows, N) : 1, &S);
+    if (!tc) { set_error("b200_approx_gemm: pair table does not fit shared memory"); return B200_ERR_ARGUMENT; }
     PredecodeArgs pa;
+    pa.tmax = S > 1 ? flag + 4 : nullptr;
     pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
     pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
     pa.zero_count = reinterpret_cast<unsigned long long*>(flag + 2);
@@ -740,6 +858,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     B200_LAUNCH_CHECK("predecode_kernel<A>");
     PredecodeArgs pb = pa;
     pb.zero_count = nullptr;
+    pb.tmax = S > 1 ? flag + 5 : nullptr;
     pb.src = B; pb.s_row = sb_n; pb.s_k = sb_k; pb.dst = Bw; pb.rows = N; pb.Rpad = Npad;
     const dim3 pgrid((unsigned)(Npad / 32), (unsigned)(Kpad / 32));
     if (sb_k == 1 && sb_n != 1) predecode_kernel<true, true><<<pgrid, 256, 0, st>>>(pb, geom);
@@ -758,19 +877,23 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     la.qamaa = qop ? 1 : 0;
     if (qop) la.qop = *qop; else la.qop = QamaaOp{};
     prof_record(true, st);
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (sms <= 0) sms = 148;
-        for (const LutTileCfg& c : kLutTiles)
-            B200_CUDA_TRY(cudaFuncSetAttribute(c.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    }
-    const LutTileCfg* tc = choose_lut_tile(Mrows, N, lut_bytes, geom.sidx, sms);
-    if (!tc) { set_error("b200_approx_gemm: pair table does not fit shared memory"); return B200_ERR_ARGUMENT; }
-    tc->kernel<<<dim3((unsigned)ceil_div(Mrows, tc->BM()), (unsigned)ceil_div(N, tc->BN())), 32 * tc->warps,
+    la.splits = S; la.partial = partial; la.inexact = flag + 6; la.tmax = flag + 4; la.t_bias = geom.RA + M + 2;
+    la.gate = nullptr;
+    tc->kernel<<<dim3((unsigned)ceil_div(Mrows, tc->BM()), (unsigned)ceil_div(N, tc->BN()), (unsigned)S), 32 * tc->warps,
                  tc->smem(lut_bytes), st>>>(la);
+    if (S > 1) {
+        B200_LAUNCH_CHECK("approx_gemm_lut_kernel(split-K)");
+        splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(Mrows * N, 256), 4 * sms), 256, 0, st>>>(
+            partial, S, C, ldc, Mrows, N, bias, M, la.qamaa, la.qop, flag + 6, flag);
+        B200_LAUNCH_CHECK("splitk_reduce_kernel");
+        // runs only if the exactness certificate failed
+        int S1 = 1;
+        const LutTileCfg* t1 = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, 1, &S1);
+        la.splits = 1; la.gate = flag + 6;
+        t1->kernel<<<dim3((unsigned)ceil_div(Mrows, t1->BM()), (unsigned)ceil_div(N, t1->BN())), 32 * t1->warps,
+                     t1->smem(lut_bytes), st>>>(la);
+    }
+    g_last_splits = S;
     prof_record(false, st);
     B200_LAUNCH_CHECK("approx_gemm_lut_kernel");
     return B200_OK;
@@ -786,7 +909,7 @@ extern "C" size_t b200_approx_gemm_workspace_bytes(int64_t Mrows, int64_t K, int
     if (Mrows < 0 || K < 0 || N < 0) return 0;
     const int64_t Mpad = round_up(Mrows > 0 ? Mrows : 1, kPadM), Npad = round_up(N > 0 ? N : 1, kPadN);
     const int64_t Kpad = round_up(K > 0 ? K : 1, kPadK);
-    return kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4;
+    return kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4 + splitk_partial_bytes(Mrows, N);
 }
 
 // Shared by the GEMM and conv entry points (conv.cu): `A` is either a row-major matrix or an
@@ -838,7 +961,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     }
 
     const int64_t Mpad = round_up(Mrows, kPadM), Npad = round_up(N, kPadN), Kpad = round_up(K, kPadK);
-    const size_t need = kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4;
+    const size_t words = kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4, need = words;
     if (!workspace || workspace_bytes < need) {
         set_error("b200_approx_gemm: workspace too small (see b200_approx_gemm_workspace_bytes)");
         return B200_ERR_WORKSPACE;
@@ -846,15 +969,18 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     int* flag = reinterpret_cast<int*>(workspace);
     uint32_t* Aw = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(workspace) + kFlagBytes);
     uint32_t* Bw = Aw + (size_t)Kpad * Mpad;
-    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 16, st));
+    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 32, st));
 
+    // split-K partial sums: only if the caller's workspace has the room b200_approx_gemm_workspace_bytes asks for
+    float* partial = (splitk_partial_bytes(Mrows, N) && workspace_bytes >= words + splitk_partial_bytes(Mrows, N))
+                         ? reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + words) : nullptr;
     if (int rc = run_lut_gemm(A, B, sb_k, sb_n, C, ldc, Mrows, K, N, bias, lut->geom, lut->d_lut, lut->lut_bytes, flag,
-                              Aw, Bw, Mpad, Npad, Kpad, nullptr, st))
+                              Aw, Bw, Mpad, Npad, Kpad, nullptr, partial, st))
         return rc;
     // runs only if the predecode found an off-grid operand
     pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<ApproxPairOp>(conditional)");
-    set_path(lut->geom.sidx ? "lut-signed" : "lut");
+    set_path(lut->geom.sidx ? "lut-signed" : (g_last_splits > 1 ? "lut-splitk" : "lut"));
     return B200_OK;
 }
 
@@ -900,17 +1026,19 @@ int b200::qamaa_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t s
     uint32_t* Aw = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(workspace) + kFlagBytes);
     uint32_t* Bw = Aw + (size_t)Kpad * Mpad;
     uint16_t* d_lut = reinterpret_cast<uint16_t*>(Bw + (size_t)Kpad * Npad);
-    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 16, st));
+    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 32, st));
     lut_build_qamaa_kernel<<<(int)ceil_div(lut_bytes / 2, 256), 256, 0, st>>>(geom, op, d_lut, bias_R, flag);
     B200_LAUNCH_CHECK("lut_build_qamaa_kernel");
     BiasSrc bias = *hint;
     bias.fR = bias_R;                                   // result bias = the quantizer's, computed on the device
+    float* partial = splitk_partial_bytes(Mrows, N)
+                         ? reinterpret_cast<float*>(reinterpret_cast<char*>(d_lut) + kQamaaTableBytes) : nullptr;
     if (int rc = run_lut_gemm(A, B, sb_k, sb_n, C, ldc, Mrows, K, N, bias, geom, d_lut, lut_bytes, flag, Aw, Bw, Mpad,
-                              Npad, Kpad, &op, st))
+                              Npad, Kpad, &op, partial, st))
         return rc;
     pair_gemm_kernel<QamaaOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<QamaaOp>(conditional)");
-    set_path("qamaa-lut");
+    set_path(g_last_splits > 1 ? "qamaa-lut-splitk" : "qamaa-lut");
     return B200_OK;
 }
 
