@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--mant-width", type=int, default=3)
     ap.add_argument("--check", action="store_true", help="rank 0 re-runs the whole batch alone and compares")
+    ap.add_argument("--graph", action="store_true", help="replay the forward as a CUDA graph (eval_harness.GraphedForward)")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -55,15 +56,16 @@ def main():
     x_cal = mk(a.per_gpu_batch, 1).to(dev)          # replicated calibration batch
     x = mk(n, 2).to(dev)                            # every rank holds the batch, evaluates its slice
     eh.calibrate(model, x_cal)
+    fwd = eh.GraphedForward(model) if a.graph else None
     for _ in range(max(a.warmup, 3)):
-        logits, _ = eh.evaluate(model, x)
+        logits, _ = eh.evaluate(model, x, forward=fwd)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(a.steps):
-        logits, _ = eh.evaluate(model, x)
+        logits, _ = eh.evaluate(model, x, forward=fwd)
     e1.record()
     torch.cuda.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -79,7 +81,7 @@ def main():
     if rank == 0:
         print(json.dumps({"metric": f"{a.model}_approx_sim_images_per_s", "value": round(n / ms_step * 1e3, 1),
                           "unit": "images/s", "n_gpus": world, "steps": a.steps, "ms_per_step": round(ms_step, 3),
-                          "scaling": "weak", "per_gpu_batch": a.per_gpu_batch, "global_batch": n,
+                          "scaling": "weak", "cuda_graph": bool(a.graph), "per_gpu_batch": a.per_gpu_batch, "global_batch": n,
                           "format": f"E{7 - M}M{M}", "approx_gmacs": round(n * mb.MACS_PER_IMAGE[a.model] / ms_step / 1e6, 1),
                           "collective": "one all_gather of logits per step" if world > 1 else None,
                           "sharded_equals_single_gpu": same, "logits_checksum": float(logits.double().sum())}),
