@@ -650,6 +650,8 @@ static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int64_t Kpad,
     double best_cost = 0;
     *splits = 1;
     int forced_s = 0;
+    double rate8 = 0.7;
+    if (const char* e = getenv("B200_LUT_RATE8")) rate8 = atof(e);   // experiments
     if (const char* e = getenv("B200_LUT_SPLITK")) forced_s = std::max(1, std::min(atoi(e), max_s));   // experiments / tests
     if (const char* e = getenv("B200_LUT_TILE")) {   // experiments: force a tile configuration by index
         const int i = atoi(e);
@@ -671,7 +673,12 @@ static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int64_t Kpad,
         if (r < 1) continue;
         const int64_t nk = Kpad / c.kt;
         const double T = (double)c.BM() * c.BN() * c.kt * (c.cpl == 2 ? 1.06 : 1.0) * (c.kt < 16 ? 1.05 : 1.0);
-        auto rate = [&](int ctas) { return std::min(1.0, ctas * c.warps / 8.0); };
+        // lookup rate of an SM against resident warps (latency hiding): measured ~0.7 of the peak rate with 8
+        // warps (one 128x128 CTA per SM), ~1.0 from 16 warps on
+        auto rate = [&](int ctas) {
+            const double w = ctas * c.warps;
+            return w <= 8.0 ? rate8 * w / 8.0 : std::min(1.0, rate8 + (1.0 - rate8) * (w - 8.0) / 8.0);
+        };
         for (int S = 1; S <= max_s; ++S) {
             if (forced_s && S != forced_s) continue;
             if (S > 1 && nk / S < 4) break;
