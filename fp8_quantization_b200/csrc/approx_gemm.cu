@@ -314,6 +314,71 @@ __global__ void __launch_bounds__(PC_ROWS) predecode_conv_kernel(PredecodeArgs a
     }
 }
 
+// Conv form, second variant: the group's input channels are decoded ONCE, in place of the kh*kw-times
+// inflated plane above, into words Pw[b][c][h][w]; the GEMM's A-tile loader then does the im2col gather
+// itself (4-byte cp.async from this L2-resident plane).  kinfo[k] = {word offset of tap k = (c, ky, kx)
+// relative to the pixel's top-left tap, ky*dh | kx*dw << 16}; k >= K gets an always-out-of-range row offset.
+struct ConvPlane {
+    const uint32_t* Pw;       // [B][Cg][H][W] words
+    const int2* kinfo;        // [Kpad]
+    const uint32_t* zero_src; // one word: the A word of a == 0 (padding, rows / k beyond the matrix)
+    int64_t img_words;        // Cg * H * W
+    int H, W, Ho, Wo, sh, sw, ph, pw;
+};
+
+__global__ void __launch_bounds__(256) predecode_plane_kernel(PredecodeArgs a, LutGeom g, uint32_t* __restrict__ Pw,
+                                                              int2* __restrict__ kinfo, uint32_t* __restrict__ zero_dst,
+                                                              int64_t nB, int64_t Cg)
+{
+    const ASrc& s = a.asrc;
+    const int64_t img = Cg * s.H * s.W, total = nB * img;
+    const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int off = 0, zeros = 0, tmax = 0;
+    const int bA = a.bias.A(), bR = a.bias.R();
+    if (bA <= -64 || bA >= 64 || bR <= -64 || bR >= 64) off = 1;
+    if (gid == 0) *zero_dst = 2u * (uint32_t)g.zeroA_off;
+    if (gid < a.Kpad) {
+        int2 ki = make_int2(0, -30000 & 0xFFFF);   // dy far outside: never in range
+        if (gid < a.K) {
+            const int kx = (int)(gid % s.kw), t = (int)(gid / s.kw);
+            const int ky = t % s.kh, c = t / s.kh;
+            ki.x = (c * s.H + ky * s.dh) * s.W + kx * s.dw;
+            ki.y = (ky * s.dh) | ((kx * s.dw) << 16);
+        }
+        kinfo[gid] = ki;
+    }
+    const int64_t i4 = gid * 4;
+    if (i4 < total) {
+        // img % 4 == 0 (checked by the host): the four elements are in one image and 16-byte aligned
+        const int64_t b = i4 / img, j = i4 - b * img;
+        const float4 v = __ldg(reinterpret_cast<const float4*>(s.p + (b * s.C + s.c0) * (int64_t)s.H * s.W + j));
+        uint4 w;
+        w.x = predecode_a(g, v.x, bA, off, tmax);
+        w.y = predecode_a(g, v.y, bA, off, tmax);
+        w.z = predecode_a(g, v.z, bA, off, tmax);
+        w.w = predecode_a(g, v.w, bA, off, tmax);
+        zeros = (v.x == 0.0f) + (v.y == 0.0f) + (v.z == 0.0f) + (v.w == 0.0f);
+        *reinterpret_cast<uint4*>(Pw + i4) = w;
+    }
+    if (off) *a.offgrid = 1;
+    if (a.tmax) {
+        tmax = __reduce_max_sync(0xFFFFFFFFu, tmax);
+        if ((threadIdx.x & 31) == 0 && tmax > *(volatile int*)a.tmax) atomicMax(a.tmax, tmax);
+    }
+    if (a.zero_count && (blockIdx.x & 7) == 0) {   // sampled zero statistics, as in predecode_kernel
+        __shared__ int s_zeros;
+        if (threadIdx.x == 0) s_zeros = 0;
+        __syncthreads();
+        zeros = __reduce_add_sync(0xFFFFFFFFu, zeros);
+        if ((threadIdx.x & 31) == 0 && zeros) atomicAdd(&s_zeros, zeros);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const int64_t n = min((int64_t)1024, total - (int64_t)blockIdx.x * 1024);
+            if (n > 0) atomicAdd(a.zero_count, (unsigned long long)s_zeros | ((unsigned long long)n << 32));
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // Table-driven GEMM.  Template <WARPS, RPW, CPL>: CTA tile (RPW*WARPS) x (32*CPL); one warp =
 // RPW rows x 32*CPL columns; one lane = RPW rows x CPL consecutive columns (RPW*CPL = 64 or 32 fp32
@@ -402,11 +467,13 @@ struct LutGemmArgs {
     const int* tmax;      // [2]: largest table row index of A / of B seen by the predecode pass
     int t_bias;           // t = tA_idx + tB_idx - t_bias
     const int* gate;      // non-null: run only if *gate != 0
+    ConvPlane cp;         // CONV instantiations: the A operand is gathered from a decoded NCHW plane
 };
 
 // KT: k-tile depth (8 where a large table leaves little shared memory for the operand ring).
 // SIDX: signed-index table layout (lut.cuh): the B word is a full 32-bit byte offset, multiplier +1.0.
-template <int WARPS, int RPW, int CPL, int KT, bool SIDX>
+// CONV: implicit im2col in the A-tile loader (ConvPlane) instead of a pre-gathered Aw plane.
+template <int WARPS, int RPW, int CPL, int KT, bool SIDX, bool CONV>
 __global__ void __launch_bounds__(32 * WARPS, (WARPS >= 16) ? 1 : ((RPW * CPL >= 64) ? 16 / WARPS : 24 / WARPS))
 approx_gemm_lut_kernel(LutGemmArgs a)
 {
@@ -430,13 +497,41 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     const uint32_t lut_base = smem_u32(smem);
     const uint32_t As_u = smem_u32(As), Bs_u = smem_u32(Bs);
 
+    // CONV: this thread gathers row (tid % BM) of every A tile, k = tid / BM + j * (NTHR / BM)
+    static_assert(NTHR % BM == 0 && (KT * BM) % NTHR == 0, "A-tile gather mapping");
+    const uint32_t* crow = nullptr;   // address of the row's top-left tap (may lie outside the image: never read)
+    int ch0 = 0, cw0 = 0;
+    if (CONV) {
+        const int64_t r = m0 + tid % BM;
+        const int wo = (int)(r % a.cp.Wo);
+        const int64_t t2 = r / a.cp.Wo;
+        const int ho = (int)(t2 % a.cp.Ho);
+        const int64_t b = t2 / a.cp.Ho;
+        ch0 = ho * a.cp.sh - a.cp.ph;
+        cw0 = wo * a.cp.sw - a.cp.pw;
+        if (r >= a.Mrows) ch0 = -(1 << 20);   // rows beyond the matrix: every tap out of range
+        crow = a.cp.Pw + b * a.cp.img_words + (int64_t)ch0 * a.cp.W + cw0;
+    }
     auto load_tile = [&](int kt, int stage) {
-        const uint32_t* ga = a.Aw + (int64_t)kt * KT * a.Mpad + m0;
         const uint32_t* gb = a.Bw + (int64_t)kt * KT * a.Npad + n0;
+        if (CONV) {
+            const int2* ki = a.cp.kinfo + kt * KT + tid / BM;
+            const uint32_t dst = As_u + 4u * (uint32_t)((stage * KT + tid / BM) * BM + tid % BM);
 #pragma unroll
-        for (int i = tid; i < KT * BM / 4; i += NTHR) {
-            const int r = i / (BM / 4), c = i % (BM / 4);
-            cp_async16(As_u + 4u * (uint32_t)((stage * KT + r) * BM + c * 4), ga + (int64_t)r * a.Mpad + c * 4);
+            for (int j = 0; j < KT * BM / NTHR; ++j) {
+                const int2 q = __ldg(ki + j * (NTHR / BM));
+                const int h = ch0 + (int)(short)(q.y & 0xFFFF), w = cw0 + (q.y >> 16);
+                const bool ok = (unsigned)h < (unsigned)a.cp.H && (unsigned)w < (unsigned)a.cp.W;
+                const uint32_t* src = ok ? crow + q.x : a.cp.zero_src;
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + 4u * (uint32_t)(j * (NTHR / BM) * BM)), "l"(src) : "memory");
+            }
+        } else {
+            const uint32_t* ga = a.Aw + (int64_t)kt * KT * a.Mpad + m0;
+#pragma unroll
+            for (int i = tid; i < KT * BM / 4; i += NTHR) {
+                const int r = i / (BM / 4), c = i % (BM / 4);
+                cp_async16(As_u + 4u * (uint32_t)((stage * KT + r) * BM + c * 4), ga + (int64_t)r * a.Mpad + c * 4);
+            }
         }
 #pragma unroll
         for (int i = tid; i < KT * BN / 4; i += NTHR) {
@@ -606,11 +701,13 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
 struct LutTileCfg {
     int warps, rpw, cpl, kt, sidx;
     void (*kernel)(LutGemmArgs);
+    void (*conv_kernel)(LutGemmArgs);
     int BM() const { return warps * rpw; }
     int BN() const { return 32 * cpl; }
     size_t smem(int lut_bytes) const { return (size_t)lut_bytes + (size_t)LUT_STAGES * kt * (BM() + BN()) * 4; }
 };
-#define LUT_TILE(W, R, C, KT, S) {W, R, C, KT, S, approx_gemm_lut_kernel<W, R, C, KT, (S) != 0>}
+#define LUT_TILE(W, R, C, KT, S) \
+    {W, R, C, KT, S, approx_gemm_lut_kernel<W, R, C, KT, (S) != 0, false>, approx_gemm_lut_kernel<W, R, C, KT, (S) != 0, true>}
 static const LutTileCfg kLutTiles[] = {
     LUT_TILE(8, 16, 4, 16, 0),    // 128 x 128
     LUT_TILE(8, 32, 2, 16, 0),    // 256 x  64   (N <= 64)
@@ -632,6 +729,10 @@ static int max_splits(int64_t Mrows, int64_t N)
     const int64_t el = Mrows * N;
     if (el <= 0 || el > ((int64_t)1 << 21)) return 1;
     return (int)std::min<int64_t>(8, ((int64_t)8 << 20) / el);
+}
+static size_t conv_plane_bytes(int64_t plane_words, int64_t Kpad)
+{
+    return (size_t)round_up(plane_words, 4) * 4 + (size_t)Kpad * 8 + 256;
 }
 static size_t splitk_partial_bytes(int64_t Mrows, int64_t N)
 {
@@ -838,7 +939,8 @@ static thread_local int g_last_splits = 1;
 static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc,
                         int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const LutGeom& geom,
                         const uint16_t* d_lut, int lut_bytes, int* flag, uint32_t* Aw, uint32_t* Bw, int64_t Mpad,
-                        int64_t Npad, int64_t Kpad, const QamaaOp* qop, float* partial, cudaStream_t st)
+                        int64_t Npad, int64_t Kpad, const QamaaOp* qop, float* partial, void* conv_ws, size_t conv_ws_bytes,
+                        cudaStream_t st)
 {
     const int M = geom.M;
     static int sms = 0;
@@ -848,7 +950,10 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (sms <= 0) sms = 148;
         for (const LutTileCfg& c : kLutTiles)
+        {
             B200_CUDA_TRY(cudaFuncSetAttribute(c.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            B200_CUDA_TRY(cudaFuncSetAttribute(c.conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        }
     }
     int S = 1;
     const LutTileCfg* tc = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, partial ? max_splits(Mrows, N) : 1, &S);
@@ -858,10 +963,38 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
     pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
     pa.zero_count = reinterpret_cast<unsigned long long*>(flag + 2);
-    // GEMM rows are k-contiguous (transpose through shared memory); an im2col view is contiguous along
-    // the output pixel, i.e. along rows: read and write row-fastest
-    if (A.conv) predecode_conv_kernel<<<dim3((unsigned)(Mpad / PC_ROWS), (unsigned)ceil_div(Kpad, PC_KCH)), PC_ROWS, 0, st>>>(pa, geom);
-    else        predecode_kernel<false, true><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, geom);
+    // Conv form: decode the input once and let the GEMM gather (needs 16-byte-aligned images and the extra
+    // workspace b200_approx_conv2d_workspace_bytes reserves); else write the im2col plane from the NCHW tensor
+    // (contiguous along the output pixel, i.e. along rows: read and write row-fastest).
+    // GEMM form: rows are k-contiguous (transpose through shared memory).
+    ConvPlane cp{};
+    bool gather = false;
+    if (A.conv) {
+        const int64_t Cg = K / ((int64_t)A.kh * A.kw), img = Cg * A.H * A.W;
+        const int64_t nB = Mrows / ((int64_t)A.Ho * A.Wo), total = nB * img;
+        const size_t need = conv_plane_bytes(total, Kpad);
+        // The gather costs the GEMM ~4-12 % (4-byte copies, address arithmetic) and saves the kh*kw-fold plane
+        // write of the predecode pass, which is amortised over the N columns: measured on ResNet-18 it wins
+        // for 3x3 / 7x7 taps up to N ~ 256 and loses for 1x1 taps (nothing to save) and wide layers.
+        const char* e = getenv("B200_CONV_GATHER");   // experiments / tests: 0 = never, 1 = heuristic, 2 = whenever possible
+        const int mode = e ? atoi(e) : 1;
+        const bool pays = mode >= 2 || (A.kh * A.kw >= 4 && N <= 256);
+        gather = mode != 0 && pays && conv_ws && conv_ws_bytes >= need && img % 4 == 0 && total < ((int64_t)1 << 31) &&
+                 ((uintptr_t)A.p & 15) == 0 && A.H < 16384 && A.W < 16384 && nB * A.Ho * A.Wo == Mrows;
+        if (gather) {
+            uint32_t* Pw = reinterpret_cast<uint32_t*>(conv_ws);
+            int2* kinfo = reinterpret_cast<int2*>(Pw + round_up(total, 4));
+            uint32_t* zsrc = reinterpret_cast<uint32_t*>(kinfo + Kpad);
+            cp.Pw = Pw; cp.kinfo = kinfo; cp.zero_src = zsrc; cp.img_words = img;
+            cp.H = A.H; cp.W = A.W; cp.Ho = A.Ho; cp.Wo = A.Wo; cp.sh = A.sh; cp.sw = A.sw; cp.ph = A.ph; cp.pw = A.pw;
+            const int64_t threads = std::max<int64_t>(ceil_div(total, 4), Kpad);
+            predecode_plane_kernel<<<(unsigned)ceil_div(threads, 256), 256, 0, st>>>(pa, geom, Pw, kinfo, zsrc, nB, Cg);
+        } else {
+            predecode_conv_kernel<<<dim3((unsigned)(Mpad / PC_ROWS), (unsigned)ceil_div(Kpad, PC_KCH)), PC_ROWS, 0, st>>>(pa, geom);
+        }
+    } else {
+        predecode_kernel<false, true><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, geom);
+    }
     B200_LAUNCH_CHECK("predecode_kernel<A>");
     PredecodeArgs pb = pa;
     pb.zero_count = nullptr;
@@ -886,7 +1019,8 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     prof_record(true, st);
     la.splits = S; la.partial = partial; la.inexact = flag + 6; la.tmax = flag + 4; la.t_bias = geom.RA + M + 2;
     la.gate = nullptr;
-    tc->kernel<<<dim3((unsigned)ceil_div(Mrows, tc->BM()), (unsigned)ceil_div(N, tc->BN()), (unsigned)S), 32 * tc->warps,
+    la.cp = cp;
+    (gather ? tc->conv_kernel : tc->kernel)<<<dim3((unsigned)ceil_div(Mrows, tc->BM()), (unsigned)ceil_div(N, tc->BN()), (unsigned)S), 32 * tc->warps,
                  tc->smem(lut_bytes), st>>>(la);
     if (S > 1) {
         B200_LAUNCH_CHECK("approx_gemm_lut_kernel(split-K)");
@@ -897,7 +1031,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         int S1 = 1;
         const LutTileCfg* t1 = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, 1, &S1);
         la.splits = 1; la.gate = flag + 6;
-        t1->kernel<<<dim3((unsigned)ceil_div(Mrows, t1->BM()), (unsigned)ceil_div(N, t1->BN())), 32 * t1->warps,
+        (gather ? t1->conv_kernel : t1->kernel)<<<dim3((unsigned)ceil_div(Mrows, t1->BM()), (unsigned)ceil_div(N, t1->BN())), 32 * t1->warps,
                      t1->smem(lut_bytes), st>>>(la);
     }
     g_last_splits = S;
@@ -917,6 +1051,11 @@ extern "C" size_t b200_approx_gemm_workspace_bytes(int64_t Mrows, int64_t K, int
     const int64_t Mpad = round_up(Mrows > 0 ? Mrows : 1, kPadM), Npad = round_up(N > 0 ? N : 1, kPadN);
     const int64_t Kpad = round_up(K > 0 ? K : 1, kPadK);
     return kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4 + splitk_partial_bytes(Mrows, N);
+}
+
+size_t b200::conv_gather_workspace_bytes(int64_t nB, int64_t Cg, int64_t H, int64_t W, int64_t Kg)
+{
+    return conv_plane_bytes(nB * Cg * H * W, round_up(Kg > 0 ? Kg : 1, kPadK));
 }
 
 // Shared by the GEMM and conv entry points (conv.cu): `A` is either a row-major matrix or an
@@ -979,10 +1118,13 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 32, st));
 
     // split-K partial sums: only if the caller's workspace has the room b200_approx_gemm_workspace_bytes asks for
-    float* partial = (splitk_partial_bytes(Mrows, N) && workspace_bytes >= words + splitk_partial_bytes(Mrows, N))
-                         ? reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + words) : nullptr;
+    const size_t pbytes = splitk_partial_bytes(Mrows, N);
+    float* partial = (pbytes && workspace_bytes >= words + pbytes) ? reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + words) : nullptr;
+    // whatever the caller provides beyond the GEMM-form workspace holds the decoded conv plane
+    void* conv_ws = workspace_bytes > words + pbytes ? reinterpret_cast<char*>(workspace) + words + pbytes : nullptr;
+    const size_t conv_ws_bytes = conv_ws ? workspace_bytes - words - pbytes : 0;
     if (int rc = run_lut_gemm(A, B, sb_k, sb_n, C, ldc, Mrows, K, N, bias, lut->geom, lut->d_lut, lut->lut_bytes, flag,
-                              Aw, Bw, Mpad, Npad, Kpad, nullptr, partial, st))
+                              Aw, Bw, Mpad, Npad, Kpad, nullptr, partial, conv_ws, conv_ws_bytes, st))
         return rc;
     // runs only if the predecode found an off-grid operand
     pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
@@ -1040,8 +1182,11 @@ int b200::qamaa_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t s
     bias.fR = bias_R;                                   // result bias = the quantizer's, computed on the device
     float* partial = splitk_partial_bytes(Mrows, N)
                          ? reinterpret_cast<float*>(reinterpret_cast<char*>(d_lut) + kQamaaTableBytes) : nullptr;
+    const size_t base_bytes = b200_qamaa_gemm_workspace_bytes(Mrows, K, N);
+    void* conv_ws = workspace_bytes > base_bytes ? reinterpret_cast<char*>(workspace) + base_bytes : nullptr;
+    const size_t conv_ws_bytes = conv_ws ? workspace_bytes - base_bytes : 0;
     if (int rc = run_lut_gemm(A, B, sb_k, sb_n, C, ldc, Mrows, K, N, bias, geom, d_lut, lut_bytes, flag, Aw, Bw, Mpad,
-                              Npad, Kpad, &op, partial, st))
+                              Npad, Kpad, &op, partial, conv_ws, conv_ws_bytes, st))
         return rc;
     pair_gemm_kernel<QamaaOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<QamaaOp>(conditional)");

@@ -225,7 +225,7 @@ extern "C" size_t b200_approx_conv2d_workspace_bytes(const b200_conv_geom* g)
     ConvDims d;
     if (conv_dims(g, &d) != B200_OK) return 0;
     if (d.Ng == 1) return 256;   // device-side fallback flag of the single-column table kernel
-    return b200_approx_gemm_workspace_bytes(d.rows, d.Kg, d.Ng);
+    return b200_approx_gemm_workspace_bytes(d.rows, d.Kg, d.Ng) + conv_gather_workspace_bytes(g->batch, d.Cg, g->H, g->W, d.Kg);
 }
 
 extern "C" int b200_approx_conv2d_fbias(const float* x, const float* w, float* out, const b200_conv_geom* g,

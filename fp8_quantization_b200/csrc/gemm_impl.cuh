@@ -32,6 +32,10 @@ int approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, 
                      int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const b200_approx_params* p,
                      void* workspace, size_t workspace_bytes, void* stream);
 
+// extra workspace (beyond the GEMM-form bytes) with which the conv form decodes the input once and lets the
+// table GEMM do the im2col gather (approx_gemm.cu)
+size_t conv_gather_workspace_bytes(int64_t nB, int64_t Cg, int64_t H, int64_t W, int64_t Kg);
+
 // quantize_after_mult_and_add GEMM: table kernel when `hint` (operand exponent biases) is given and the
 // format allows it, arithmetic kernel otherwise (approx_gemm.cu)
 int qamaa_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc, int64_t Mrows,

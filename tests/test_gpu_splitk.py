@@ -111,3 +111,49 @@ def test_splitk_qamaa(fq):
             os.environ.pop("B200_LUT_SPLITK", None)
         assert path == ("qamaa-lut" if s == 1 else "qamaa-lut-splitk"), path
     assert torch.equal(outs[1].view(torch.int32), outs[3].view(torch.int32))
+
+
+CONV_CASES = [
+    # B, C, H, W, C_out, k, stride, pad, dil, groups
+    (2, 16, 14, 14, 32, 3, 1, 1, 1, 1),
+    (2, 16, 14, 14, 32, 3, 2, 1, 1, 1),
+    (3, 8, 12, 10, 24, 3, 1, 2, 2, 1),       # dilation, non-square
+    (2, 3, 32, 32, 16, 7, 2, 3, 1, 1),       # the ResNet stem shape
+    (2, 32, 8, 8, 64, 1, 2, 0, 1, 1),        # 1x1 stride-2 downsample
+    (2, 32, 8, 8, 64, 1, 1, 0, 1, 1),        # pointwise
+    (2, 16, 10, 10, 32, 3, 1, 1, 1, 4),      # grouped, 8 columns per group
+    (4, 64, 7, 7, 128, 3, 1, 1, 1, 1),       # 49-pixel images: image size not a multiple of 4 words per channel
+    (1, 5, 7, 9, 6, 3, 1, 1, 1, 1),          # image of 315 words: the gather path must decline (alignment)
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+@pytest.mark.parametrize("mode", ["approx", "qamaa"])
+def test_conv_gather_equals_im2col_plane(fq, case, mode):
+    """Conv form: decoding the NCHW input once and gathering in the GEMM's tile loader must give the
+    bits of the older path that writes the im2col plane (B200_CONV_GATHER=0), which the layer fixtures from the
+    reference's QCustomBNConv2dTorch pinned (approx/approx_calculation.py:724-747, :846-906)."""
+    B, C, H, W, Co, k, st, pad, dil, groups = case
+    E, M, bA, bW = 4, 3, 7, 9
+    x = grid_values(E, M, bA, (B, C, H, W), 11, 0.8)
+    x[np.random.default_rng(12).random(x.shape) < 0.4] = 0.0
+    w = grid_values(E, M, bW, (Co, C // groups, k, k), 13, 0.8)
+    xd, wd = torch.from_numpy(x).cuda(), torch.from_numpy(w).cuda()
+    xb = torch.tensor([float(bA)], device="cuda")
+    wb = torch.full((Co,), float(bW), device="cuda")
+    outs = []
+    for env in ("0", "2"):      # never / whenever the geometry allows it
+        os.environ["B200_CONV_GATHER"] = env
+        try:
+            if mode == "approx":
+                rb = torch.tensor([8.0], device="cuda")
+                o = fq.ops.approx_conv2d(xd, wd, xb, wb, rb, fq.ops.make_params(MAIN), (st, st), (pad, pad), (dil, dil), groups)
+            else:
+                mv = torch.tensor([float(np.abs(x).max() * np.abs(w).max() * 16)], device="cuda")
+                o = fq.ops.qamaa_conv2d(xd, wd, 8, mv, 3.0, 1, (st, st), (pad, pad), (dil, dil), groups, x_bias=xb, w_bias=wb)
+            assert fq.ops.last_path().startswith("lut" if mode == "approx" else "qamaa-lut"), fq.ops.last_path()
+            outs.append(o)
+        finally:
+            os.environ.pop("B200_CONV_GATHER", None)
+    assert float(outs[0].abs().max()) > 0
+    assert torch.equal(outs[0].view(torch.int32), outs[1].view(torch.int32)), case

@@ -28,6 +28,13 @@ SHAPES = {
     "square": [(1, 4096, 4096, 4096)],
 }
 
+# conv form (--conv): (count, C_in, H, C_out, k, stride, pad)
+CONVS = {
+    "resnet18": [(1, 3, 224, 64, 7, 2, 3), (4, 64, 56, 64, 3, 1, 1), (1, 64, 56, 128, 3, 2, 1), (3, 128, 28, 128, 3, 1, 1),
+                 (1, 128, 28, 256, 3, 2, 1), (3, 256, 14, 256, 3, 1, 1), (1, 256, 14, 512, 3, 2, 1), (3, 512, 7, 512, 3, 1, 1),
+                 (1, 64, 56, 128, 1, 2, 0), (1, 128, 28, 256, 1, 2, 0), (1, 256, 14, 512, 1, 2, 0)],
+}
+
 
 def main():
     ap = argparse.ArgumentParser()
@@ -38,6 +45,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--mode", default="approx", choices=["approx", "qamaa"])
     ap.add_argument("--check", action="store_true", help="compare with the arithmetic kernel, bit for bit")
+    ap.add_argument("--conv", action="store_true", help="conv form (implicit im2col) over the model's conv geometries")
     a = ap.parse_args()
     import torch
     import fp8_quantization_b200 as pkg
@@ -52,21 +60,42 @@ def main():
     g = torch.Generator(device="cpu").manual_seed(10)
     mant = torch.tensor([float(M)])
     tot_ms = tot_kern = tot_macs = 0.0
-    for cnt, mr, K, N in SHAPES[a.model]:
-        rows = mr * (a.batch if a.model != "square" else 1)
-        x = torch.randn(rows, K, generator=g).abs_() * 0.5
-        x[torch.rand(rows, K, generator=g) < a.zero_frac] = 0.0
-        w = torch.randn(N, K, generator=g) * 0.05
-        x, w = x.to(dev), w.to(dev)
-        xq, bA = ops.fp8_fakequant(x, 8, x.abs().max().reshape(1), mant, 1)
-        wq, bB = ops.fp8_fakequant(w, 8, w.abs().amax(dim=1), mant, 1)
-        ref = xq[:64] @ wq.t()
-        _, bR = ops.fp8_fakequant(ref, 8, (ref.abs().max() * 2).reshape(1), mant, 1)
-        out = torch.empty((rows, N), device=dev)
-        step = lambda: ops.approx_matmul(xq, wq.t(), bA, bB, bR, params, out=out)
-        if a.mode == "qamaa":
-            mv = (ref.abs().max() * 2).reshape(1)
-            step = lambda: ops.qamaa_matmul(xq, wq.t(), 8, mv, mant, 1, out=out, x_bias=bA, y_bias=bB)
+    shapes = SHAPES[a.model] if not a.conv else CONVS[a.model]
+    for shape in shapes:
+        if a.conv:
+            cnt, Ci, H, N, k, st, pad = shape
+            Ho = (H + 2 * pad - k) // st + 1
+            rows, K = a.batch * Ho * Ho, Ci * k * k
+            x = torch.randn(a.batch, Ci, H, H, generator=g).abs_() * 0.5
+            x[torch.rand(x.shape, generator=g) < a.zero_frac] = 0.0
+            w = torch.randn(N, Ci, k, k, generator=g) * 0.05
+            x, w = x.to(dev), w.to(dev)
+            xq, bA = ops.fp8_fakequant(x, 8, x.abs().max().reshape(1), mant, 1)
+            wq, bB = ops.fp8_fakequant(w.reshape(N, -1), 8, w.reshape(N, -1).abs().amax(dim=1), mant, 1)
+            wq = wq.reshape(w.shape)
+            ref = torch.nn.functional.conv2d(xq[:1], wq, stride=st, padding=pad)
+            _, bR = ops.fp8_fakequant(ref, 8, (ref.abs().max() * 2).reshape(1), mant, 1)
+            outs = []
+            step = lambda: outs.__setitem__(slice(None), [ops.approx_conv2d(xq, wq, bA, bB, bR, params, (st, st), (pad, pad), (1, 1), 1)])
+            if a.mode == "qamaa":
+                mv = (ref.abs().max() * 2).reshape(1)
+                step = lambda: outs.__setitem__(slice(None), [ops.qamaa_conv2d(xq, wq, 8, mv, mant, 1, (st, st), (pad, pad), (1, 1), 1, x_bias=bA, w_bias=bB)])
+        else:
+            cnt, mr, K, N = shape
+            rows = mr * (a.batch if a.model != "square" else 1)
+            x = torch.randn(rows, K, generator=g).abs_() * 0.5
+            x[torch.rand(rows, K, generator=g) < a.zero_frac] = 0.0
+            w = torch.randn(N, K, generator=g) * 0.05
+            x, w = x.to(dev), w.to(dev)
+            xq, bA = ops.fp8_fakequant(x, 8, x.abs().max().reshape(1), mant, 1)
+            wq, bB = ops.fp8_fakequant(w, 8, w.abs().amax(dim=1), mant, 1)
+            ref = xq[:64] @ wq.t()
+            _, bR = ops.fp8_fakequant(ref, 8, (ref.abs().max() * 2).reshape(1), mant, 1)
+            out = torch.empty((rows, N), device=dev)
+            step = lambda: ops.approx_matmul(xq, wq.t(), bA, bB, bR, params, out=out)
+            if a.mode == "qamaa":
+                mv = (ref.abs().max() * 2).reshape(1)
+                step = lambda: ops.qamaa_matmul(xq, wq.t(), 8, mv, mant, 1, out=out, x_bias=bA, y_bias=bB)
         for _ in range(2):
             step()
         torch.cuda.synchronize()
@@ -84,7 +113,7 @@ def main():
         lib.b200_profile_end(ctypes.byref(t), ctypes.byref(c))
         kms = t.value / max(c.value, 1)
         macs = rows * K * N
-        if a.check:
+        if a.check and not a.conv:
             pg = ops.make_params(dict(expo_width=E, mant_width=M, dnsmp_factor=3, withComp=True, with_approx=True,
                                       with_s2nn2s_opt=True, quant_btw_mult_accu=True), force_generic=True)
             want = ops.approx_matmul(xq, wq.t(), bA, bB, bR, pg)
