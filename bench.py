@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--mant-width", type=int, default=3)
     ap.add_argument("--rows", type=int, default=ROWS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--e2e-chunks", type=int, default=2, help="row chunks the e2e leg streams the batch in")
+    ap.add_argument("--e2e-chunks", type=int, default=1, help="row chunks the e2e leg streams the batch in")
     ap.add_argument("--sweep", action="store_true", help="also report mant_width 2..5 and the qamaa mode")
     return ap.parse_args()
 
@@ -120,6 +120,42 @@ def measured_traffic(M, rows):
         return t.get(f"approx_gemm_lut_kernel E{7 - M}M{M} {rows}x{K_DIM}x{N_DIM}")
     except Exception:
         return None
+
+
+def sweep_legs(rows, dev, steps):
+    """BASELINE configs[1] in full: mant_width 2..5 x {approx_v9, quantize_after_mult_and_add}, whole step
+    (operand predecode + table GEMM), operands resident in HBM.  mant_width 2 (E5M2) has no reference answer
+    (approx_v9 raises for it): all-zero table, parity unpinned."""
+    import torch
+    from fp8_quantization_b200 import ops
+    legs = []
+    for M in (2, 3, 4, 5):
+        x, w, _ = host_inputs(rows, M)
+        x, w = x.to(dev), w.to(dev)
+        mant = torch.tensor([float(M)])
+        xq, bA = ops.fp8_fakequant(x, 8, x.abs().max().reshape(1), mant, 1)
+        wq, bB = ops.fp8_fakequant(w, 8, w.abs().amax(dim=1), mant, 1)
+        mv = ((xq[:256] @ wq.t()).abs().max() * 1.5).reshape(1)
+        _, bR = ops.fp8_fakequant(mv.clone(), 8, mv, mant, 1)
+        out = torch.empty((rows, N_DIM), device=dev)
+        params = ops.make_params(approx_params(M), allow_unpinned_format=(M == 2))
+        for mode, step in (("approx_v9", lambda: ops.approx_matmul(xq, wq.t(), bA, bB, bR, params, out=out)),
+                           ("quantize_after_mult_and_add",
+                            lambda: ops.qamaa_matmul(xq, wq.t(), 8, mv, mant, 1, out=out, x_bias=bA, y_bias=bB))):
+            for _ in range(3):
+                step()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                step()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            legs.append({"mant_width": M, "expo_width": 7 - M, "mode": mode, "kernel_path": ops.last_path(),
+                         "ms_per_step": round(ms, 4), "gmacs": round(rows * K_DIM * N_DIM / ms / 1e6, 1),
+                         "parity": "unpinned (approx_v9 raises for E5M2)" if M == 2 else "pinned"})
+    return legs
 
 
 def build_layer(M, device, w, b):
@@ -218,43 +254,49 @@ def run_ours(args):
         achieved = ALG_INT_OPS_PER_MAC * macs / (kern_ms * 1e-3) / 1e12 if kern_ms > 0 else 0.0
 
         # e2e: through QCustomLinearTorch.forward with pinned HOST buffers, copies inside the timed region.
-        # The batch is streamed in row chunks (rows are independent once the ranges are fixed): the H2D copy
-        # of chunk i+1 and the D2H copy of chunk i-1 overlap the forward of chunk i on separate streams.
+        # Every step copies its whole input batch host->device and its whole result device->host.  Steps are
+        # software pipelined (rows are independent once the ranges are fixed): the H2D copy of step i+1 and the
+        # D2H copy of step i-1 run on side streams while the forward of step i computes; the input is double
+        # buffered on the device.  --e2e-chunks > 1 additionally splits a step's batch into row chunks.
         x_pin = x_host.pin_memory()
         y_pin = torch.empty((rows, N_DIM), dtype=torch.float32).pin_memory()
         nch = args.e2e_chunks if rows % args.e2e_chunks == 0 and rows >= 256 * args.e2e_chunks else 1
         rc = rows // nch
         cur, s_in, s_out = torch.cuda.current_stream(), torch.cuda.Stream(), torch.cuda.Stream()
-        xd = [torch.empty((rc, K_DIM), device=dev) for _ in range(nch)]
-        consumed = [None] * nch
+        xd = [torch.empty((rc, K_DIM), device=dev) for _ in range(2 * nch)]
+        consumed = [None] * (2 * nch)
+        e2e_count = [0]
 
         def e2e_step():
             for c in range(nch):
+                slot = (e2e_count[0] % 2) * nch + c
                 with torch.cuda.stream(s_in):
-                    if consumed[c] is not None:
-                        s_in.wait_event(consumed[c])          # the previous step's forward has read xd[c]
-                    xd[c].copy_(x_pin[c * rc:(c + 1) * rc], non_blocking=True)
+                    if consumed[slot] is not None:
+                        s_in.wait_event(consumed[slot])       # the forward that read xd[slot] two steps ago is done
+                    xd[slot].copy_(x_pin[c * rc:(c + 1) * rc], non_blocking=True)
                     arrived = torch.cuda.Event()
                     arrived.record(s_in)
                 cur.wait_event(arrived)
-                y = layer(xd[c])
+                y = layer(xd[slot])
                 done = torch.cuda.Event()
                 done.record(cur)
-                consumed[c] = done
+                consumed[slot] = done
                 s_out.wait_event(done)
                 with torch.cuda.stream(s_out):
                     y_pin[c * rc:(c + 1) * rc].copy_(y, non_blocking=True)
                 y.record_stream(s_out)
-            cur.wait_stream(s_out)
+            e2e_count[0] += 1
 
         for _ in range(3):
             e2e_step()
+        cur.wait_stream(s_out)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         e0.record()
         for _ in range(args.steps):
             e2e_step()
+        cur.wait_stream(s_out)                                # the last step's D2H copy ends inside the timed region
         e1.record()
         torch.cuda.synchronize()
         ems = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -276,7 +318,7 @@ def run_ours(args):
         "per_gpu": round(value / world, 2),
         "e2e": {"value": round(e2e_value, 2), "unit": "GMAC/s", "h2d_bytes_per_step": rows * K_DIM * 4,
                 "d2h_bytes_per_step": rows * N_DIM * 4, "through": "QCustomLinearTorch.forward (fake-quant x, "
-                "fake-quant W, approx GEMM, +bias), pinned host in/out, row chunks with copies overlapped on side streams", "chunks": nch, "checksum": checksum},
+                "fake-quant W, approx GEMM, +bias), pinned host in/out; steps software pipelined: copies of adjacent steps overlap the forward on side streams", "chunks": nch, "checksum": checksum},
         "gpu_launches": int(launches),
         "roofline": {"bound": "int-issue", "achieved": round(achieved, 3), "peak": round(tiops.value, 3),
                      "unit": "Tiop/s", "frac": round(achieved / tiops.value, 4) if tiops.value else None,
@@ -296,6 +338,22 @@ def run_ours(args):
                                    "note": "ncu: l1tex__data_pipe_lsu_wavefronts_mem_shared at 96.7 % of peak "
                                            "(profiles/r1b_approx_gemm_lut_full.txt)"}
     line["roofline"]["traffic"] = measured_traffic(M, rows)
+    # achieved HBM rate of the same kernel (north_star asks for it beside the issue-rate figure): algorithmic
+    # bytes 4*(Mrows*K + K*N + Mrows*N) + 4*N / kernel time, against the measured copy peak
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        hbm_peak, hbm_src = float(peaks["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:
+        hbm_peak, hbm_src = 6550.0, "fallback of B200_PROFILING.md (MEASURED_PEAKS.json absent)"
+    alg_bytes = 4 * (rows * K_DIM + K_DIM * N_DIM + rows * N_DIM) + 4 * N_DIM
+    if kern_ms > 0:
+        gbs = alg_bytes / (kern_ms * 1e-3) / 1e9
+        line["roofline"]["hbm"] = {"achieved": round(gbs, 1), "peak": hbm_peak, "unit": "GB/s", "frac": round(gbs / hbm_peak, 4),
+                                   "alg_bytes": alg_bytes, "peak_source": hbm_src,
+                                   "note": "not the bound: 342 MAC per algorithmic byte"}
+    if args.sweep and rank == 0:
+        with torch.inference_mode():
+            line["sweep"] = sweep_legs(rows, dev, max(3, args.steps // 2))
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             rate, ncols, dt, thr = cpu_port_rate(rows, M, 12.0, xq.cpu().numpy(), wq.cpu().numpy(),

@@ -80,6 +80,7 @@ SIGNATURES = {
                                     ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32),
                                     ctypes.POINTER(ctypes.c_int32)]),
     "b200_im2col": (c_int, [c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp]),
+    "b200_exact_grouped_conv2d": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp]),
     "b200_approx_conv2d_workspace_bytes": (c_sz, [ctypes.POINTER(ConvGeom)]),
     "b200_approx_conv2d_fbias": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_vp, c_i64, c_vp,
                                          ctypes.POINTER(ApproxParams), c_vp, c_sz, c_vp]),

@@ -96,15 +96,11 @@ class _ConvMixin(_ApproxMixin):
             out = ops.qamaa_conv2d(x, weight, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits, self.stride,
                                    self.padding, self.dilation, self.groups, x_bias=self.get_acts_fp_bias(),
                                    w_bias=self.get_weights_fp_bias())
-        else:
+        elif self.groups == 1:
             col = self.im2col(x, kh, kw, self.stride, self.padding, self.dilation)
-            Kg = Cg * kh * kw
-            wcol = weight.reshape(Cout, -1)
-            if self.groups == 1:
-                out = self.multiply(col, wcol.t())
-            else:                                 # approx_calculation.py:858-906, exact branch
-                out = torch.bmm(col.view(-1, self.groups, Kg).transpose(0, 1),
-                                wcol.view(self.groups, Ng, Kg).transpose(1, 2)).permute(1, 0, 2).reshape(-1, Cout)
+            out = self.multiply(col, weight.reshape(Cout, -1).t())
+        else:                                     # approx_calculation.py:858-906, exact branch, all groups at once
+            out = ops.exact_grouped_conv2d(x, weight, self.stride, self.padding, self.dilation, self.groups)
         out = out.reshape(B, Ho, Wo, Cout).permute(0, 3, 1, 2)      # :909-910 (a view, like the reference)
         if bias is not None:
             out = out + bias.view(1, -1, 1, 1)

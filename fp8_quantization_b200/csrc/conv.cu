@@ -181,6 +181,58 @@ __global__ void __launch_bounds__(256) approx_dw_lut_kernel(DwLutArgs d)
     if (off) *d.flag = 1;
 }
 
+// ---- exact grouped conv (non-approx configuration, groups > 1) ---------------------------------------
+// out[m, n] = sum_{k < Kg, ascending} col[m, grp(n)*Kg + k] * w[n, k]: the reference's exact branch of the
+// group loop (`input_col_group @ weight_group.T`, approx/approx_calculation.py:810-811, :796-797) for every
+// group in ONE launch, implicit im2col (no [rows, C*kh*kw] matrix in HBM).  32 rows x 32 output channels per
+// CTA: rows across lanes for the gather (coalesced along wo), transposed through shared memory for the store.
+__global__ void __launch_bounds__(256) exact_grouped_conv_kernel(ASrc s, const float* __restrict__ w, float* __restrict__ out,
+                                                                 int64_t rows, int64_t n_row_tiles, int n_ch_tiles, int C_out,
+                                                                 int Kg, int Cg, int Ng)
+{
+    __shared__ float tile[32][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int64_t t = blockIdx.x; t < n_row_tiles * n_ch_tiles; t += gridDim.x) {
+        const int64_t rt = t / n_ch_tiles;
+        const int ct = (int)(t - rt * n_ch_tiles);
+        const int64_t m = rt * 32 + tx;
+        const int wo = (int)(m % s.Wo);
+        const int64_t t2 = m / s.Wo;
+        const int ho = (int)(t2 % s.Ho);
+        const int64_t b = t2 / s.Ho;
+        const int h0 = ho * s.sh - s.ph, w0 = wo * s.sw - s.pw;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int nl = ty + 8 * i;
+            const int n = ct * 32 + nl;
+            float acc = 0.0f;
+            if (n < C_out && m < rows) {
+                const int grp = n / Ng;
+                const float* wn = w + (int64_t)n * Kg;
+                const float* base = s.p + (b * s.C + (int64_t)grp * Cg) * (int64_t)s.H * s.W;
+                int kx = 0, ky = 0, c = 0;
+                for (int k = 0; k < Kg; ++k) {
+                    const int h = h0 + ky * s.dh, wi = w0 + kx * s.dw;
+                    float av = 0.0f;
+                    if (h >= 0 && h < s.H && wi >= 0 && wi < s.W) av = __ldg(base + ((int64_t)c * s.H + h) * s.W + wi);
+                    if (++kx == s.kw) { kx = 0; if (++ky == s.kh) { ky = 0; ++c; } }
+                    acc = fmaf(av, __ldg(wn + k), acc);
+                }
+            }
+            tile[nl][tx] = acc;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int ml = ty + 8 * i;
+            const int64_t mm = rt * 32 + ml;
+            const int n = ct * 32 + tx;
+            if (mm < rows && n < C_out) out[mm * C_out + n] = tile[tx][ml];
+        }
+        __syncthreads();
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -217,6 +269,28 @@ extern "C" int b200_im2col(const float* x, float* out, const b200_conv_geom* g, 
     if (blocks > (int64_t)sms * 16) blocks = (int64_t)sms * 16;
     im2col_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a, out, d.rows, K);
     B200_LAUNCH_CHECK("im2col_kernel");
+    return B200_OK;
+}
+
+extern "C" int b200_exact_grouped_conv2d(const float* x, const float* w, float* out, const b200_conv_geom* g, void* stream)
+{
+    if (int rc = check_device()) return rc;
+    ConvDims d;
+    if (int rc = conv_dims(g, &d)) return rc;
+    if (d.rows == 0) return B200_OK;
+    if (!x || !w || !out) { set_error("b200_exact_grouped_conv2d: NULL operand"); return B200_ERR_ARGUMENT; }
+    ASrc a = make_conv_asrc(x, g, d, 0);
+    int sms = 148;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int64_t n_row_tiles = ceil_div(d.rows, 32);
+    const int n_ch_tiles = (int)ceil_div(g->C_out, 32);
+    const int64_t blocks = std::min<int64_t>(n_row_tiles * n_ch_tiles, (int64_t)sms * 8);
+    exact_grouped_conv_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a, w, out, d.rows, n_row_tiles, n_ch_tiles,
+                                                                                   g->C_out, d.Kg, d.Cg, d.Ng);
+    B200_LAUNCH_CHECK("exact_grouped_conv_kernel");
+    set_path("exact-grouped-conv");
     return B200_OK;
 }
 

@@ -257,6 +257,21 @@ def im2col(x, kernel_size, stride, padding, dilation):
     return out
 
 
+def exact_grouped_conv2d(x, weight, stride, padding, dilation, groups):
+    """Exact branch of the conv group loop (approx/approx_calculation.py:796-797, :810-811) for groups > 1:
+    every group in one launch over an implicit im2col view.  Returns [B*Ho*Wo, C_out] fp32."""
+    lib = _lib.load()
+    _require_cuda(x, weight)
+    x = x.float().contiguous()
+    weight = weight.float().contiguous()
+    g = conv_geom(x.shape, weight.shape, stride, padding, dilation, groups)
+    rows, _, _, _, _ = conv_out_shape(g)
+    out = torch.empty((rows, g.C_out), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.b200_exact_grouped_conv2d(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _stream()))
+    return out
+
+
 def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, dilation, groups):
     """im2col + group loop + approx_multiply of QCustomBNConv2dTorch.run_forward
     (approx/approx_calculation.py:846-906) in one C-ABI call.  Returns [B*Ho*Wo, C_out] fp32.

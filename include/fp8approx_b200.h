@@ -181,6 +181,12 @@ int b200_conv_out_shape(const b200_conv_geom *g, int64_t *rows, int32_t *Ho, int
                         int32_t *Ng);
 /* im2col (:724-747): out [rows, C_in*kh*kw] row-major, K order (c, ky, kx), zero padded borders */
 int b200_im2col(const float *x, float *out, const b200_conv_geom *g, void *stream);
+/* exact (non-approx, non-qamaa) branch of the group loop for groups > 1, every group in one launch:
+ * out[m, n] = sum_k col[m, grp(n)*Kg + k] * w[n, k]  (`input_col_group @ weight_group.T`,
+ * approx/approx_calculation.py:796-797, :810-811), implicit im2col, fp32 FMA with k ascending.
+ * out is [rows, C_out] row-major.  (groups == 1 goes through b200_im2col + b200_fq_gemm_tc.) */
+int b200_exact_grouped_conv2d(const float *x, const float *w, float *out, const b200_conv_geom *g,
+                              void *stream);
 /* im2col + group loop + approx_multiply (:846-906) in one call; out is [rows, C_out] row-major (the
  * tensor the reference then views as [B,Ho,Wo,C_out] and permutes, :909-910).  Groups with more than
  * one output channel: table GEMM over an implicit im2col view (no im2col matrix in HBM).  Groups
