@@ -87,6 +87,8 @@ SIGNATURES = {
     "b200_qamaa_conv2d": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_int, c_f32, c_int, c_vp]),
     "b200_bn_act": (c_int, [c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_int, c_i64, c_vp, c_vp, c_vp, c_vp, c_f32, c_int,
                             c_vp]),
+    "b200_set_autotune": (c_int, [c_int]),
+    "b200_autotune_runs": (ctypes.c_uint64, []),
     "b200_int_peak_probe": (c_int, [c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
     "b200_profile_begin": (c_int, []),
     "b200_profile_end": (c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_int)]),

@@ -723,12 +723,15 @@ static const LutTileCfg kLutTiles[] = {
     LUT_TILE(4, 16, 2, 16, 1),
 };
 
-// Largest split-K factor the workspace reserves partial-sum room for (32 MB at most).
+// Largest split-K factor the workspace reserves partial-sum room for: up to 8 slices, 256 MB in all (HBM is
+// 180 GB; the partial sums cost one extra write + read of S*Mrows*N*4 bytes, a few % of the GEMM's time).
 static int max_splits(int64_t Mrows, int64_t N)
 {
     const int64_t el = Mrows * N;
-    if (el <= 0 || el > ((int64_t)1 << 21)) return 1;
-    return (int)std::min<int64_t>(8, ((int64_t)8 << 20) / el);
+    if (el <= 0 || el > ((int64_t)1 << 24)) return 1;
+    int64_t cap = ((int64_t)64 << 20) / el;
+    if (const char* e = getenv("B200_LUT_PARTIAL_MB")) cap = ((int64_t)atoi(e) << 18) / el;   // experiments
+    return (int)std::max<int64_t>(1, std::min<int64_t>(8, cap));
 }
 static size_t conv_plane_bytes(int64_t plane_words, int64_t Kpad)
 {
@@ -744,9 +747,15 @@ static size_t splitk_partial_bytes(int64_t Mrows, int64_t N)
 // BM*BN lookups per k; CTAs are dealt round-robin over the SMs, `r` resident at a time.  Splitting k by S
 // multiplies the CTA count and divides each CTA's k range; it costs a pipeline prologue/epilogue per CTA
 // and two more launches (the ordered reduction and the gated unsplit fallback).
+struct LutCand {
+    double cost;
+    const LutTileCfg* cfg;
+    int S;
+};
 static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int64_t Kpad, int lut_bytes, int sidx, int sms,
-                                         int max_s, int* splits)
+                                         int max_s, int* splits, std::vector<LutCand>* all = nullptr, bool* forced = nullptr)
 {
+    if (forced) *forced = getenv("B200_LUT_SPLITK") || getenv("B200_LUT_TILE");
     const LutTileCfg* best = nullptr;
     double best_cost = 0;
     *splits = 1;
@@ -791,6 +800,7 @@ static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int64_t Kpad,
             if (rem_per_sm > 0) cost += rem_per_sm * Tc / rate(rem_per_sm);
             if (S > 1) cost += 3.0e5 + 4.0 * (double)S * Mrows * N / sms;
             if (!best || cost < best_cost) { best = &c; best_cost = cost; *splits = S; }
+            if (all) all->push_back(LutCand{cost, &c, S});
         }
     }
     return best;
@@ -930,6 +940,38 @@ static void prof_record(bool start, cudaStream_t st)
     }
 }
 
+// Measured choice of (tile, split-K factor).  The cost model above ranks the candidates; the first call for a
+// new problem shape times the best few on the caller's own operands (CUDA events on the caller's stream, one
+// host synchronisation per candidate) and caches the winner.  Every candidate computes the same bits (split-K
+// runs under the exactness certificate), so the choice never changes a result.  Skipped while the stream is
+// being captured into a CUDA graph, for small problems, and when B200_LUT_TILE / B200_LUT_SPLITK force a
+// configuration; b200_set_autotune(0) or B200_AUTOTUNE=0 turns it off (then no call ever synchronises).
+struct TuneKey {
+    int64_t Mrows, N, Kpad;
+    int lut_bytes, sidx, gather, max_s, qamaa;
+    bool operator<(const TuneKey& o) const
+    {
+        return std::tie(Mrows, N, Kpad, lut_bytes, sidx, gather, max_s, qamaa) <
+               std::tie(o.Mrows, o.N, o.Kpad, o.lut_bytes, o.sidx, o.gather, o.max_s, o.qamaa);
+    }
+};
+static std::map<TuneKey, std::pair<const LutTileCfg*, int>> g_tuned;
+static std::mutex g_tuned_mu;
+static std::atomic<int> g_autotune{-1};
+static std::atomic<uint64_t> g_tune_runs{0};
+static bool autotune_on()
+{
+    int v = g_autotune.load(std::memory_order_relaxed);
+    if (v < 0) {
+        const char* e = getenv("B200_AUTOTUNE");
+        v = e ? (atoi(e) != 0) : 1;
+        g_autotune.store(v, std::memory_order_relaxed);
+    }
+    return v != 0;
+}
+constexpr int kTuneCandidates = 6;
+constexpr int64_t kTuneMinMacs = (int64_t)1 << 26;
+
 constexpr int64_t kPadM = 256, kPadN = 128, kPadK = 32;
 constexpr size_t kFlagBytes = 256;   // ints: [0] off-grid, [2..3] zero statistics, [4..5] row maxima, [6] split-K inexact
 static thread_local int g_last_splits = 1;
@@ -956,10 +998,13 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         }
     }
     int S = 1;
-    const LutTileCfg* tc = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, partial ? max_splits(Mrows, N) : 1, &S);
+    const int max_s = partial ? max_splits(Mrows, N) : 1;
+    std::vector<LutCand> cands;
+    bool forced = false;
+    const LutTileCfg* tc = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, max_s, &S, &cands, &forced);
     if (!tc) { set_error("b200_approx_gemm: pair table does not fit shared memory"); return B200_ERR_ARGUMENT; }
     PredecodeArgs pa;
-    pa.tmax = S > 1 ? flag + 4 : nullptr;
+    pa.tmax = max_s > 1 ? flag + 4 : nullptr;
     pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
     pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
     pa.zero_count = reinterpret_cast<unsigned long long*>(flag + 2);
@@ -998,7 +1043,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     B200_LAUNCH_CHECK("predecode_kernel<A>");
     PredecodeArgs pb = pa;
     pb.zero_count = nullptr;
-    pb.tmax = S > 1 ? flag + 5 : nullptr;
+    pb.tmax = max_s > 1 ? flag + 5 : nullptr;
     pb.src = B; pb.s_row = sb_n; pb.s_k = sb_k; pb.dst = Bw; pb.rows = N; pb.Rpad = Npad;
     const dim3 pgrid((unsigned)(Npad / 32), (unsigned)(Kpad / 32));
     if (sb_k == 1 && sb_n != 1) predecode_kernel<true, true><<<pgrid, 256, 0, st>>>(pb, geom);
@@ -1016,27 +1061,74 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     la.offgrid = flag;
     la.qamaa = qop ? 1 : 0;
     if (qop) la.qop = *qop; else la.qop = QamaaOp{};
-    prof_record(true, st);
-    la.splits = S; la.partial = partial; la.inexact = flag + 6; la.tmax = flag + 4; la.t_bias = geom.RA + M + 2;
-    la.gate = nullptr;
+    la.partial = partial; la.inexact = flag + 6; la.tmax = flag + 4; la.t_bias = geom.RA + M + 2;
     la.cp = cp;
-    (gather ? tc->conv_kernel : tc->kernel)<<<dim3((unsigned)ceil_div(Mrows, tc->BM()), (unsigned)ceil_div(N, tc->BN()), (unsigned)S), 32 * tc->warps,
-                 tc->smem(lut_bytes), st>>>(la);
-    if (S > 1) {
-        B200_LAUNCH_CHECK("approx_gemm_lut_kernel(split-K)");
-        splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(Mrows * N, 256), 4 * sms), 256, 0, st>>>(
-            partial, S, C, ldc, Mrows, N, bias, M, la.qamaa, la.qop, flag + 6, flag);
-        B200_LAUNCH_CHECK("splitk_reduce_kernel");
-        // runs only if the exactness certificate failed
-        int S1 = 1;
-        const LutTileCfg* t1 = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, 1, &S1);
-        la.splits = 1; la.gate = flag + 6;
-        (gather ? t1->conv_kernel : t1->kernel)<<<dim3((unsigned)ceil_div(Mrows, t1->BM()), (unsigned)ceil_div(N, t1->BN())), 32 * t1->warps,
-                     t1->smem(lut_bytes), st>>>(la);
+    // one (tile, split) configuration: the GEMM, and for split-K the ordered reduction plus the gated unsplit kernel
+    auto launch = [&](const LutTileCfg* cfg, int splits) -> int {
+        LutGemmArgs l = la;
+        l.splits = splits; l.gate = nullptr;
+        (gather ? cfg->conv_kernel : cfg->kernel)<<<dim3((unsigned)ceil_div(Mrows, cfg->BM()), (unsigned)ceil_div(N, cfg->BN()), (unsigned)splits),
+                                                    32 * cfg->warps, cfg->smem(lut_bytes), st>>>(l);
+        if (splits > 1) {
+            B200_LAUNCH_CHECK("approx_gemm_lut_kernel(split-K)");
+            splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(Mrows * N, 256), 4 * sms), 256, 0, st>>>(
+                partial, splits, C, ldc, Mrows, N, bias, M, l.qamaa, l.qop, flag + 6, flag);
+            B200_LAUNCH_CHECK("splitk_reduce_kernel");
+            // runs only if the exactness certificate failed
+            int S1 = 1;
+            const LutTileCfg* t1 = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, 1, &S1);
+            l.splits = 1; l.gate = flag + 6;
+            (gather ? t1->conv_kernel : t1->kernel)<<<dim3((unsigned)ceil_div(Mrows, t1->BM()), (unsigned)ceil_div(N, t1->BN())), 32 * t1->warps,
+                                                     t1->smem(lut_bytes), st>>>(l);
+        }
+        B200_LAUNCH_CHECK("approx_gemm_lut_kernel");
+        return B200_OK;
+    };
+    // measured choice (see TuneKey above)
+    if (autotune_on() && !forced && cands.size() > 1 && Mrows * N * Kpad >= kTuneMinMacs) {
+        const TuneKey key{Mrows, N, Kpad, lut_bytes, geom.sidx, gather ? 1 : 0, max_s, qop ? 1 : 0};
+        bool have = false;
+        {
+            std::lock_guard<std::mutex> lk(g_tuned_mu);
+            auto it = g_tuned.find(key);
+            if (it != g_tuned.end()) { tc = it->second.first; S = it->second.second; have = true; }
+        }
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        if (!have && cudaStreamIsCapturing(st, &cap) == cudaSuccess && cap == cudaStreamCaptureStatusNone) {
+            std::sort(cands.begin(), cands.end(), [](const LutCand& x, const LutCand& y) { return x.cost < y.cost; });
+            if ((int)cands.size() > kTuneCandidates) cands.resize(kTuneCandidates);
+            cudaEvent_t e0, e1;
+            B200_CUDA_TRY(cudaEventCreate(&e0));
+            B200_CUDA_TRY(cudaEventCreate(&e1));
+            float best_ms = 0.0f;
+            int rc = B200_OK;
+            for (size_t i = 0; i < cands.size() && rc == B200_OK; ++i) {
+                if (cands[i].cost > 1.6 * cands[0].cost) break;
+                for (int rep = 0; rep < 3 && rc == B200_OK; ++rep) {   // one warm run, two timed
+                    if (rep == 1) cudaEventRecord(e0, st);
+                    cudaMemsetAsync(flag + 6, 0, 4, st);
+                    rc = launch(cands[i].cfg, cands[i].S);
+                }
+                if (rc != B200_OK) break;
+                cudaEventRecord(e1, st);
+                if (cudaEventSynchronize(e1) != cudaSuccess) { rc = cuda_fail(cudaGetLastError(), "autotune"); break; }
+                float ms = 0.0f;
+                cudaEventElapsedTime(&ms, e0, e1);
+                g_tune_runs.fetch_add(1, std::memory_order_relaxed);
+                if (i == 0 || ms < best_ms) { best_ms = ms; tc = cands[i].cfg; S = cands[i].S; }
+            }
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+            if (rc != B200_OK) return rc;
+            cudaMemsetAsync(flag + 6, 0, 4, st);
+            std::lock_guard<std::mutex> lk(g_tuned_mu);
+            g_tuned[key] = std::make_pair(tc, S);
+        }
     }
+    prof_record(true, st);
+    if (int rc = launch(tc, S)) return rc;
     g_last_splits = S;
     prof_record(false, st);
-    B200_LAUNCH_CHECK("approx_gemm_lut_kernel");
     return B200_OK;
 }
 
@@ -1044,6 +1136,15 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_set_autotune(int on)
+{
+    const int prev = autotune_on() ? 1 : 0;
+    g_autotune.store(on ? 1 : 0, std::memory_order_relaxed);
+    return prev;
+}
+
+extern "C" uint64_t b200_autotune_runs(void) { return g_tune_runs.load(std::memory_order_relaxed); }
 
 extern "C" size_t b200_approx_gemm_workspace_bytes(int64_t Mrows, int64_t K, int64_t N)
 {

@@ -15,7 +15,8 @@
  *     the first call for a new (format, flags) combination, which builds and caches the pair
  *     table (one small cudaMalloc + one kernel + one 4-byte read-back);
  *   - the caller owns all buffers, including the scratch `workspace` whose size is returned by the
- *     matching *_workspace_bytes function;
+ *     matching *_workspace_bytes function (the table GEMM's first call per problem shape may also time
+ *     candidate tile configurations, see b200_set_autotune);
  *   - return value: B200_OK or a negative B200_ERR_* code; b200_last_error() gives the text.
  *     The Python host maps codes to the exceptions the reference raises at the same condition.
  */
@@ -69,6 +70,15 @@ const char *b200_last_error(void);
 uint64_t b200_kernel_launches(void);
 /* name of the kernel path the last b200_approx_gemm / conv call took: "lut", "generic", ... */
 const char *b200_last_path(void);
+
+/* Measured (tile, split-K) choice of the table GEMM: with autotune on (the default; B200_AUTOTUNE=0 in the
+ * environment or b200_set_autotune(0) turns it off) the FIRST call for a new problem shape times the cost
+ * model's best few configurations on the caller's operands and caches the winner -- a handful of extra runs
+ * and host synchronisations, once per shape, never while the stream is being captured into a CUDA graph.
+ * All configurations compute identical bits.  Returns the previous setting. */
+int b200_set_autotune(int on);
+/* number of candidate configurations timed so far (0 = the cost model alone has decided everything) */
+uint64_t b200_autotune_runs(void);
 
 /* ---- A5: get_error_table_NN, approx/approx_matmul_whole_v9.py:555-592 ------------------------ */
 /* host_out: 2^M * 2^M int8, row-major, HOST memory. */
