@@ -102,14 +102,27 @@ struct DwLutArgs {
     int* flag;
 };
 
+// Weight fields are decoded once per (group, k) of a tile into `wpart` (they are the same for every row), the
+// per-k input offsets once per CTA into `kinfo`; the inner loop then only extracts the fields of `a`.
+// KG: compile-time Kg (9 = 3x3 depthwise, fully unrolled) or 0 for a run-time Kg.
+constexpr uint32_t kDwSkip = 0xFFFFFFFFu;
+template <int KG>
 __global__ void __launch_bounds__(256) approx_dw_lut_kernel(DwLutArgs d)
 {
     extern __shared__ __align__(16) unsigned char dw_smem[];
+    const int Kg = KG ? KG : d.Kg;
     float (*tile)[33] = reinterpret_cast<float (*)[33]>(dw_smem + d.lut_bytes);
+    uint32_t* wpart = reinterpret_cast<uint32_t*>(dw_smem + d.lut_bytes + 32 * 33 * sizeof(float));   // [32][Kg]
+    int2* kinfo = reinterpret_cast<int2*>(wpart + ((32 * Kg + 1) & ~1));                               // [Kg]
     {
         const uint4* src = reinterpret_cast<const uint4*>(d.lut);
         uint4* dst = reinterpret_cast<uint4*>(dw_smem);
         for (int i = threadIdx.x; i < d.lut_bytes / 16; i += 256) dst[i] = __ldg(src + i);
+    }
+    const ASrc& s = d.a;
+    for (int k = threadIdx.x; k < Kg; k += 256) {   // K order (c, ky, kx), approx_calculation.py:724-747
+        const int kx = k % s.kw, t = k / s.kw, ky = t % s.kh, c = t / s.kh;
+        kinfo[k] = make_int2((c * s.H + ky * s.dh) * s.W + kx * s.dw, (ky * s.dh) | ((kx * s.dw) << 16));
     }
     const uint16_t* lut_s = reinterpret_cast<const uint16_t*>(dw_smem);
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -118,12 +131,34 @@ __global__ void __launch_bounds__(256) approx_dw_lut_kernel(DwLutArgs d)
     const int bA = d.bias.A(), bR = d.bias.R();
     int off = (bA < 2 || bR < 2 || bA >= 64 || bR >= 64) ? 1 : 0;
     const float unit = pow2f_i(1 - bR - M);
-    const uint32_t frac_mask = (1u << (23 - M)) - 1u;
-    const ASrc& s = d.a;
-    __syncthreads();
+    const uint32_t frac_mask = (1u << (23 - M)) - 1u, mmask = (1u << M) - 1u;
+    const int ea_lo = 127 + 1 - bA - M;          // exponent field of the smallest sub-normal of A's format
     for (int64_t t = blockIdx.x; t < d.n_row_tiles * d.n_grp_tiles; t += gridDim.x) {
         const int64_t rt = t / d.n_grp_tiles;
         const int gt = (int)(t - rt * d.n_grp_tiles);
+        __syncthreads();                          // previous tile's wpart / tile readers are done; first pass: lut, kinfo
+        for (int i = threadIdx.x; i < 32 * Kg; i += 256) {
+            const int gl = i / Kg, k = i - gl * Kg, grp = gt * 32 + gl;
+            uint32_t wp = kDwSkip;
+            if (grp < d.groups) {
+                const int bB = d.bias.B(grp);
+                if (bB < 2 || bB >= 64) off = 1;
+                const uint32_t wb = __float_as_uint(__ldg(d.w + (int64_t)grp * Kg + k));
+                const uint32_t wmag = wb & 0x7FFFFFFFu;
+                if (wmag != 0u) {                 // zero weight: addend 0 (v9 :81)
+                    const int LB = (int)(wmag >> 23) - 127;
+                    const int tB = LB + bR - bA + 3 + g.RA;          // no clamp: every row is live here
+                    if ((wmag & frac_mask) || tB < 0 || tB > g.NTB - 1 || LB < 1 - bB - M || (wmag >> 23) == 0 ||
+                        (wmag >> 23) == 255)
+                        off = 1;                  // outside the table's domain: the arithmetic kernel recomputes
+                    else
+                        wp = (uint32_t)g.s_stride * (wb >> 31) + (uint32_t)g.row_entries * (uint32_t)tB +
+                             ((wmag & 0x7FFFFFu) >> (23 - M));
+                }
+            }
+            wpart[i] = wp;
+        }
+        __syncthreads();
         const int64_t m = rt * 32 + tx;
         const int wo = (int)(m % s.Wo);
         const int64_t t2 = m / s.Wo;
@@ -136,33 +171,24 @@ __global__ void __launch_bounds__(256) approx_dw_lut_kernel(DwLutArgs d)
             const int grp = gt * 32 + gl;
             float acc = 0.0f;
             if (grp < d.groups && m < d.rows) {
-                const int bB = d.bias.B(grp);
-                if (bB < 2 || bB >= 64) off = 1;
-                const float* wg = d.w + (int64_t)grp * d.Kg;
-                const float* base = s.p + (b * s.C + (int64_t)grp * d.Cg) * (int64_t)s.H * s.W;
-                int kx = 0, ky = 0, c = 0;
-                for (int k = 0; k < d.Kg; ++k) {
-                    const uint32_t wb = __float_as_uint(__ldg(wg + k));      // warp-uniform
-                    const int h = h0 + ky * s.dh, wi = w0 + kx * s.dw;
-                    float av = 0.0f;
-                    if (h >= 0 && h < s.H && wi >= 0 && wi < s.W) av = __ldg(base + ((int64_t)c * s.H + h) * s.W + wi);
-                    if (++kx == s.kw) { kx = 0; if (++ky == s.kh) { ky = 0; ++c; } }
-                    const uint32_t ab = __float_as_uint(av);
-                    const uint32_t wmag = wb & 0x7FFFFFFFu, amag = ab & 0x7FFFFFFFu;
-                    if (wmag == 0u || amag == 0u) continue;                   // zero product: addend 0 (v9 :81)
-                    const int LB = (int)(wmag >> 23) - 127, LA = (int)(amag >> 23) - 127;
-                    const int tA = LA - (1 - bA - M);
-                    const int tB = LB + bR - bA + 3 + g.RA;                   // no clamp: every row is live here
-                    if ((wmag & frac_mask) || (amag & frac_mask) || tA < 0 || tA > g.RA || tB < 0 || tB > g.NTB - 1 ||
-                        LB < 1 - bB - M || (wmag >> 23) == 0 || (wmag >> 23) == 255 || (amag >> 23) == 0 ||
-                        (amag >> 23) == 255) {
-                        off = 1;
-                        continue;
-                    }
-                    const uint32_t mA = (amag & 0x7FFFFFu) >> (23 - M), mB = (wmag & 0x7FFFFFu) >> (23 - M);
-                    const uint32_t sreg = (ab >> 31) + (wb >> 31);             // 0, 1 or 2: region s = sreg & 1
-                    const uint32_t idx = (uint32_t)g.s_stride * sreg + (uint32_t)g.a_stride * mA +
-                                         (uint32_t)g.row_entries * (uint32_t)(tA + tB) + mB;
+                // address of tap (0, 0, 0); may lie outside the image (padding): only in-range taps are read
+                const float* p0 = s.p + ((b * s.C + (int64_t)grp * d.Cg) * s.H + h0) * (int64_t)s.W + w0;
+                const uint32_t* wrow = wpart + gl * Kg;
+#pragma unroll
+                for (int k = 0; k < Kg; ++k) {
+                    const uint32_t wp = wrow[k];                                 // warp-uniform
+                    if (wp == kDwSkip) continue;
+                    const int2 ki = kinfo[k];
+                    const int h = h0 + (ki.y & 0xFFFF), wi = w0 + (ki.y >> 16);
+                    if ((unsigned)h >= (unsigned)s.H || (unsigned)wi >= (unsigned)s.W) continue;   // F.pad zeros (:727)
+                    const uint32_t ab = __float_as_uint(__ldg(p0 + ki.x));
+                    const uint32_t amag = ab & 0x7FFFFFFFu;
+                    if (amag == 0u) continue;                                    // zero product: addend 0 (v9 :81)
+                    const uint32_t tA = (amag >> 23) - (uint32_t)ea_lo;          // wraps for fp32 sub-normals
+                    if ((amag & frac_mask) || tA > (uint32_t)g.RA) { off = 1; continue; }
+                    const uint32_t mA = (amag >> (23 - M)) & mmask;
+                    const uint32_t idx = wp + (uint32_t)g.s_stride * (ab >> 31) + (uint32_t)g.a_stride * mA +
+                                         (uint32_t)g.row_entries * tA;
                     acc += __uint_as_float((uint32_t)lut_s[idx] << 16);
                 }
             }
@@ -176,7 +202,6 @@ __global__ void __launch_bounds__(256) approx_dw_lut_kernel(DwLutArgs d)
             const int grp = gt * 32 + tx;
             if (mm < d.rows && grp < d.groups) d.out[mm * d.groups + grp] = tile[tx][ml];
         }
-        __syncthreads();
     }
     if (off) *d.flag = 1;
 }
@@ -360,15 +385,19 @@ extern "C" int b200_approx_conv2d_fbias(const float* x, const float* w, float* o
         if (int rc = get_quirk_lut(E, M, a.cfg.with_approx ? host_table : nullptr, a.T, a.cfg.with_approx, &la.g, &la.lut,
                                    &la.lut_bytes, &usable))
             return rc;
-        const size_t smem = (size_t)la.lut_bytes + 32 * 33 * sizeof(float);
-        if (usable && smem <= 227 * 1024) {
+        const size_t smem = (size_t)la.lut_bytes + 32 * 33 * sizeof(float) + (size_t)((32 * d.Kg + 1) & ~1) * 4 + (size_t)d.Kg * 8;
+        // the kernel keeps per-k input offsets in 32 bits and tap offsets in 16
+        const bool small = (int64_t)d.Cg * g->H * g->W < ((int64_t)1 << 31) && (int64_t)g->kh * g->dil_h < 32768 &&
+                           (int64_t)g->kw * g->dil_w < 32768;
+        if (usable && small && smem <= 227 * 1024) {
             static int sms = 0;
             if (sms == 0) {
                 int dev = 0;
                 cudaGetDevice(&dev);
                 cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
                 if (sms <= 0) sms = 148;
-                B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_lut_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_lut_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_lut_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
             }
             la.a = a.a; la.w = w; la.out = out; la.rows = d.rows; la.groups = g->groups; la.Kg = d.Kg; la.Cg = d.Cg;
             la.n_row_tiles = ceil_div(d.rows, 32); la.n_grp_tiles = (int)ceil_div(g->groups, 32);
@@ -377,7 +406,8 @@ extern "C" int b200_approx_conv2d_fbias(const float* x, const float* w, float* o
             const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (227 * 1024) / (smem + 1024)));
             const int64_t tiles = la.n_row_tiles * la.n_grp_tiles;
             const unsigned blocks = (unsigned)std::min<int64_t>(tiles, (int64_t)sms * per_sm);
-            approx_dw_lut_kernel<<<blocks, 256, smem, st>>>(la);
+            if (d.Kg == 9) approx_dw_lut_kernel<9><<<blocks, 256, smem, st>>>(la);
+            else           approx_dw_lut_kernel<0><<<blocks, 256, smem, st>>>(la);
             B200_LAUNCH_CHECK("approx_dw_lut_kernel");
             // runs only if the table kernel met an operand / bias outside its domain
             approx_dw_kernel<<<grid, 256, 0, st>>>(a, la.flag, 1);
