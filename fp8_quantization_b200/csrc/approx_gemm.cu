@@ -1115,7 +1115,8 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
                 float ms = 0.0f;
                 cudaEventElapsedTime(&ms, e0, e1);
                 g_tune_runs.fetch_add(1, std::memory_order_relaxed);
-                if (i == 0 || ms < best_ms) { best_ms = ms; tc = cands[i].cfg; S = cands[i].S; }
+                // a later candidate must win by 2 %: timing noise must not displace the cost model's choice
+                if (i == 0 || ms < 0.98f * best_ms) { best_ms = ms; tc = cands[i].cfg; S = cands[i].S; }
             }
             cudaEventDestroy(e0);
             cudaEventDestroy(e1);

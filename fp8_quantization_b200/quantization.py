@@ -131,6 +131,7 @@ class FPQuantizer(nn.Module):
         self.allow_unsigned = allow_unsigned
         self.sign_bits = 1
         self.custom_bias = None
+        self._range_version = 0          # bumped by set_quant_range: keys the fixed-weight cache of the hijacker
         if learn_maxval or learn_mantissa_bits:
             raise NotImplementedError("learned ranges belong to QAT, which the reference never wires up (SURVEY.md 2 row 16)")
 
@@ -147,6 +148,7 @@ class FPQuantizer(nn.Module):
 
     def set_quant_range(self, x_min, x_max):
         """fp8_quantizer.py:268-287."""
+        self._range_version += 1
         if self.allow_unsigned and bool(torch.all(torch.as_tensor(x_min) >= 0)):
             self.sign_bits = 0
         if self.set_maxval:
@@ -337,6 +339,9 @@ ACTIVATIONS = (nn.ReLU, nn.ReLU6, nn.Hardtanh, nn.Sigmoid, nn.Tanh, nn.GELU, nn.
 
 
 # ---- QuantizationHijacker (hijacker.py:32-151) -------------------------------------------------
+CACHE_FIXED_WEIGHTS = True   # False: re-quantize the weights in every forward, like the reference
+
+
 class QuantizationHijacker(QuantizedModule):
     def __init__(self, *args, activation=None, **kwargs):
         super().__init__(*args, **kwargs)
@@ -384,9 +389,27 @@ class QuantizationHijacker(QuantizedModule):
         return res
 
     def get_params(self):
+        """hijacker.py:117-123.  Once the ranges are fixed the quantized weights are a pure function of
+        (weight, maxval): they are computed once and reused until either changes -- the
+        reference re-runs the weight quantizer in every forward."""
         weight, bias = self.get_weight_bias()
         if self._quant_w:
-            weight = self.quantize_weights(weight)
+            wq = self.weight_quantizer
+            q = wq.quantizer
+            fixed = CACHE_FIXED_WEIGHTS and self.fix_ranges_flag and not self.training and \
+                wq.state == Qstates.fix_ranges and hasattr(q, "_range_version") and not weight.is_inference()
+            if not fixed:
+                self.__dict__.pop("_b200_wcache", None)
+                return self.quantize_weights(weight), bias
+            key = (weight.data_ptr(), weight._version, tuple(weight.shape), weight.device, q._range_version,
+                   float(q.mantissa_bits), q.sign_bits)
+            ent = self.__dict__.get("_b200_wcache")
+            if ent is None or ent[0] != key:
+                w_q = self.quantize_weights(weight)
+                ent = (key, w_q, q.custom_bias)
+                self.__dict__["_b200_wcache"] = ent
+            q.custom_bias = ent[2]
+            weight = ent[1]
         return weight, bias
 
     def quantize_weights(self, weights):
