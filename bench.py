@@ -318,7 +318,7 @@ def run_ours(args):
         "per_gpu": round(value / world, 2),
         "e2e": {"value": round(e2e_value, 2), "unit": "GMAC/s", "h2d_bytes_per_step": rows * K_DIM * 4,
                 "d2h_bytes_per_step": rows * N_DIM * 4, "through": "QCustomLinearTorch.forward (fake-quant x, "
-                "fake-quant W, approx GEMM, +bias), pinned host in/out; steps software pipelined: copies of adjacent steps overlap the forward on side streams", "chunks": nch, "checksum": checksum},
+                "quantized W cached once the ranges are fixed, approx GEMM, +bias), pinned host in/out; steps software pipelined: copies of adjacent steps overlap the forward on side streams", "chunks": nch, "checksum": checksum},
         "gpu_launches": int(launches),
         "roofline": {"bound": "int-issue", "achieved": round(achieved, 3), "peak": round(tiops.value, 3),
                      "unit": "Tiop/s", "frac": round(achieved / tiops.value, 4) if tiops.value else None,
@@ -335,8 +335,9 @@ def run_ours(args):
         lds_peak = 32.0 * sms * clocks["sm_mhz"] * 1e6
         line["roofline"]["lds"] = {"achieved": round(macs / (kern_ms * 1e-3) / 1e12, 3), "peak": round(lds_peak / 1e12, 3),
                                    "unit": "T lookups/s", "frac": round(macs / (kern_ms * 1e-3) / lds_peak, 4),
-                                   "note": "ncu: l1tex__data_pipe_lsu_wavefronts_mem_shared at 96.7 % of peak "
-                                           "(profiles/r1b_approx_gemm_lut_full.txt)"}
+                                   "note": "ncu: l1tex__data_pipe_lsu_wavefronts_mem_shared at 96.7 % of peak: the kernel "
+                                           "runs at the shared-memory wavefront rate; 1.38 wavefronts per lookup (operand "
+                                           "words, bank-conflict replays) (profiles/r1d_approx_gemm_lut_E4M3_full.txt)"}
     line["roofline"]["traffic"] = measured_traffic(M, rows)
     # achieved HBM rate of the same kernel (north_star asks for it beside the issue-rate figure): algorithmic
     # bytes 4*(Mrows*K + K*N + Mrows*N) + 4*N / kernel time, against the measured copy peak
