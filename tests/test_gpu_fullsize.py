@@ -136,3 +136,47 @@ def test_fullsize_qamaa_properties(fq, M):
     pc = torch.randperm(N_DIM, device="cuda", generator=g)
     assert same_bits(fq.ops.qamaa_matmul(xq, wq[pc].contiguous().t(), 8, mv, mant, 1, x_bias=bA,
                                          y_bias=bB[pc].contiguous()), C[:, pc])
+
+
+def test_output_beyond_int32_indexing(fq):
+    """Maximum sizes: an output of more than 2^31 elements (2^21 + 77 rows x 1030 columns, 8.6 GB) -- every
+    index on the path must be 64-bit.  Rows at both ends and around 2^20 / 2^21 against the oracle, and the
+    checksum of the rest against a second launch over a row-shifted view (row independence)."""
+    E, M = 4, 3
+    Mr, K, N = (1 << 21) + 77, 40, 1030
+    bA, bR = 9, 7
+    rng = np.random.default_rng(21)
+    c = np.arange(2 ** (E + M), dtype=np.int32)
+    va = orc.decode(c >> M, c & (2 ** M - 1), E, M, bA)
+    va = torch.from_numpy(np.concatenate([va, -va, np.zeros(64, np.float32)]).astype(np.float32)).cuda()
+    g = torch.Generator(device="cuda").manual_seed(5)
+    A = va[torch.randint(0, va.numel(), (Mr, K), device="cuda", generator=g)]
+    bB = rng.integers(8, 12, size=N).astype(np.int32)
+    W = np.stack([orc.decode(cc >> M, cc & (2 ** M - 1), E, M, int(bB[j])) * rng.choice([-1.0, 1.0], size=K)
+                  for j, cc in enumerate(rng.integers(0, 2 ** (E + M), size=(N, K)))]).astype(np.float32)
+    p = fq.ops.make_params(approx_kw(M))
+    C = fq.ops.approx_matmul(A, torch.from_numpy(W).cuda().t(), bA, torch.from_numpy(bB).cuda(), bR, p)
+    assert fq.ops.last_path().startswith("lut") and C.numel() > 2 ** 31
+    rows = np.array([0, 1, (1 << 20) - 1, 1 << 20, (1 << 21) - 1, 1 << 21, Mr - 1])
+    T = orc.get_error_table_NN(E, M, True, 3)
+    want = orc.approx_matmul(A[rows].cpu().numpy(), np.ascontiguousarray(W.T), T, bA, bB, bR, E=E, M=M, with_approx=1,
+                             with_s2nn2s_opt=1, quant_btw_mult_accu=1)
+    assert same_bits(C[rows].cpu().numpy(), want)
+    # rows 3.. of the same matrix as a separate problem: its row i must equal row i + 3 of the first launch
+    C2 = fq.ops.approx_matmul(A[3:], torch.from_numpy(W).cuda().t(), bA, torch.from_numpy(bB).cuda(), bR, p)
+    assert same_bits(C2, C[3:])
+
+
+def test_empty_conv_and_depthwise(fq):
+    """Empty inputs on the conv forms: batch 0 returns an empty [0, C_out] matrix without launching."""
+    p = fq.ops.make_params(approx_kw(3))
+    one = torch.tensor([8.0]).cuda()
+    for groups, cout in ((1, 6), (4, 4)):
+        x = torch.zeros(0, 4, 8, 8).cuda()
+        w = torch.zeros(cout, 4 // groups, 3, 3).cuda()
+        bw = torch.full((cout,), 8.0).cuda()
+        pp = fq.ops.make_params(approx_kw(3), single_column_quirk=(groups == 4))
+        out = fq.ops.approx_conv2d(x, w, one, bw, one, pp, (1, 1), (1, 1), (1, 1), groups)
+        assert out.shape == (0, cout)
+    assert fq.ops.exact_grouped_conv2d(torch.zeros(0, 4, 8, 8).cuda(), torch.zeros(4, 1, 3, 3).cuda(), (1, 1), (1, 1),
+                                       (1, 1), 4).shape == (0, 4)
