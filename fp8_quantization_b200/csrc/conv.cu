@@ -104,10 +104,12 @@ struct DwLutArgs {
 
 // Weight fields are decoded once per (group, k) of a tile into `wpart` (they are the same for every row), the
 // per-k input offsets once per CTA into `kinfo`; the inner loop then only extracts the fields of `a`.
-// KG: compile-time Kg (9 = 3x3 depthwise, fully unrolled) or 0 for a run-time Kg.
+// KG: compile-time Kg (9 = 3x3 depthwise) or 0 for a run-time Kg.  The KG > 0 body is branch free: all KG input
+// loads are issued first (memory-level parallelism), then every tap is evaluated under predicates; taps that
+// contribute nothing (zero operand, padding) or that leave the table's domain look up an all-zero cell.
 constexpr uint32_t kDwSkip = 0xFFFFFFFFu;
 template <int KG>
-__global__ void __launch_bounds__(256) approx_dw_lut_kernel(DwLutArgs d)
+__global__ void __launch_bounds__(256, 3) approx_dw_lut_kernel(DwLutArgs d)
 {
     extern __shared__ __align__(16) unsigned char dw_smem[];
     const int Kg = KG ? KG : d.Kg;
@@ -132,10 +134,22 @@ __global__ void __launch_bounds__(256) approx_dw_lut_kernel(DwLutArgs d)
     int off = (bA < 2 || bR < 2 || bA >= 64 || bR >= 64) ? 1 : 0;
     const float unit = pow2f_i(1 - bR - M);
     const uint32_t frac_mask = (1u << (23 - M)) - 1u, mmask = (1u << M) - 1u;
-    const int ea_lo = 127 + 1 - bA - M;          // exponent field of the smallest sub-normal of A's format
+    const uint32_t ea_lo = (uint32_t)(127 + 1 - bA - M);   // exponent field of the smallest sub-normal of A's format
+    const uint32_t RA = (uint32_t)g.RA, s_stride = (uint32_t)g.s_stride, a_stride = (uint32_t)g.a_stride,
+                   row_entries = (uint32_t)g.row_entries, zero_idx = (uint32_t)g.zeroA_off;
+    const int mshift = 23 - M;
+    const bool small = d.rows < ((int64_t)1 << 31) && d.n_row_tiles * d.n_grp_tiles < ((int64_t)1 << 31);
+    int2 kreg[KG > 0 ? KG : 1];
+    if (KG > 0) {
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < KG; ++k) kreg[k] = kinfo[k];
+    }
     for (int64_t t = blockIdx.x; t < d.n_row_tiles * d.n_grp_tiles; t += gridDim.x) {
-        const int64_t rt = t / d.n_grp_tiles;
-        const int gt = (int)(t - rt * d.n_grp_tiles);
+        int64_t rt;
+        int gt;
+        if (small) { rt = (uint32_t)t / (uint32_t)d.n_grp_tiles; gt = (int)((uint32_t)t - (uint32_t)rt * (uint32_t)d.n_grp_tiles); }
+        else       { rt = t / d.n_grp_tiles; gt = (int)(t - rt * d.n_grp_tiles); }
         __syncthreads();                          // previous tile's wpart / tile readers are done; first pass: lut, kinfo
         for (int i = threadIdx.x; i < 32 * Kg; i += 256) {
             const int gl = i / Kg, k = i - gl * Kg, grp = gt * 32 + gl;
@@ -152,18 +166,26 @@ __global__ void __launch_bounds__(256) approx_dw_lut_kernel(DwLutArgs d)
                         (wmag >> 23) == 255)
                         off = 1;                  // outside the table's domain: the arithmetic kernel recomputes
                     else
-                        wp = (uint32_t)g.s_stride * (wb >> 31) + (uint32_t)g.row_entries * (uint32_t)tB +
-                             ((wmag & 0x7FFFFFu) >> (23 - M));
+                        wp = s_stride * (wb >> 31) + row_entries * (uint32_t)tB + ((wmag & 0x7FFFFFu) >> mshift);
                 }
             }
             wpart[i] = wp;
         }
         __syncthreads();
         const int64_t m = rt * 32 + tx;
-        const int wo = (int)(m % s.Wo);
-        const int64_t t2 = m / s.Wo;
-        const int ho = (int)(t2 % s.Ho);
-        const int64_t b = t2 / s.Ho;
+        int wo, ho;
+        int64_t b;
+        if (small) {
+            const uint32_t mm = (uint32_t)m, t2 = mm / (uint32_t)s.Wo;
+            wo = (int)(mm - t2 * (uint32_t)s.Wo);
+            b = t2 / (uint32_t)s.Ho;
+            ho = (int)(t2 - (uint32_t)b * (uint32_t)s.Ho);
+        } else {
+            wo = (int)(m % s.Wo);
+            const int64_t t2 = m / s.Wo;
+            ho = (int)(t2 % s.Ho);
+            b = t2 / s.Ho;
+        }
         const int h0 = ho * s.sh - s.ph, w0 = wo * s.sw - s.pw;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -174,22 +196,43 @@ __global__ void __launch_bounds__(256) approx_dw_lut_kernel(DwLutArgs d)
                 // address of tap (0, 0, 0); may lie outside the image (padding): only in-range taps are read
                 const float* p0 = s.p + ((b * s.C + (int64_t)grp * d.Cg) * s.H + h0) * (int64_t)s.W + w0;
                 const uint32_t* wrow = wpart + gl * Kg;
+                if (KG > 0) {
+                    uint32_t ab[KG > 0 ? KG : 1];
 #pragma unroll
-                for (int k = 0; k < Kg; ++k) {
-                    const uint32_t wp = wrow[k];                                 // warp-uniform
-                    if (wp == kDwSkip) continue;
-                    const int2 ki = kinfo[k];
-                    const int h = h0 + (ki.y & 0xFFFF), wi = w0 + (ki.y >> 16);
-                    if ((unsigned)h >= (unsigned)s.H || (unsigned)wi >= (unsigned)s.W) continue;   // F.pad zeros (:727)
-                    const uint32_t ab = __float_as_uint(__ldg(p0 + ki.x));
-                    const uint32_t amag = ab & 0x7FFFFFFFu;
-                    if (amag == 0u) continue;                                    // zero product: addend 0 (v9 :81)
-                    const uint32_t tA = (amag >> 23) - (uint32_t)ea_lo;          // wraps for fp32 sub-normals
-                    if ((amag & frac_mask) || tA > (uint32_t)g.RA) { off = 1; continue; }
-                    const uint32_t mA = (amag >> (23 - M)) & mmask;
-                    const uint32_t idx = wp + (uint32_t)g.s_stride * (ab >> 31) + (uint32_t)g.a_stride * mA +
-                                         (uint32_t)g.row_entries * tA;
-                    acc += __uint_as_float((uint32_t)lut_s[idx] << 16);
+                    for (int k = 0; k < KG; ++k) {
+                        const int h = h0 + (kreg[k].y & 0xFFFF), wi = w0 + (kreg[k].y >> 16);
+                        const bool inb = (unsigned)h < (unsigned)s.H && (unsigned)wi < (unsigned)s.W;   // F.pad zeros (:727)
+                        ab[k] = inb ? __float_as_uint(__ldg(p0 + kreg[k].x)) : 0u;
+                    }
+#pragma unroll
+                    for (int k = 0; k < KG; ++k) {
+                        const uint32_t wp = wrow[k];                             // warp-uniform
+                        const uint32_t amag = ab[k] & 0x7FFFFFFFu;
+                        const uint32_t tA = (amag >> 23) - ea_lo;                // wraps for fp32 sub-normals
+                        const bool live = (wp != kDwSkip) && (amag != 0u);       // else: zero product, addend 0 (v9 :81)
+                        const bool bad = live && (((amag & frac_mask) != 0u) || tA > RA);
+                        if (bad) off = 1;
+                        const uint32_t mA = (amag >> mshift) & mmask;
+                        uint32_t idx = wp + s_stride * (ab[k] >> 31) + a_stride * mA + row_entries * tA;
+                        idx = (live && !bad) ? idx : zero_idx;
+                        acc += __uint_as_float((uint32_t)lut_s[idx] << 16);
+                    }
+                } else {
+                    for (int k = 0; k < Kg; ++k) {
+                        const uint32_t wp = wrow[k];                             // warp-uniform
+                        if (wp == kDwSkip) continue;
+                        const int2 ki = kinfo[k];
+                        const int h = h0 + (ki.y & 0xFFFF), wi = w0 + (ki.y >> 16);
+                        if ((unsigned)h >= (unsigned)s.H || (unsigned)wi >= (unsigned)s.W) continue;   // F.pad zeros (:727)
+                        const uint32_t abk = __float_as_uint(__ldg(p0 + ki.x));
+                        const uint32_t amag = abk & 0x7FFFFFFFu;
+                        if (amag == 0u) continue;                                // zero product: addend 0 (v9 :81)
+                        const uint32_t tA = (amag >> 23) - ea_lo;                // wraps for fp32 sub-normals
+                        if ((amag & frac_mask) || tA > RA) { off = 1; continue; }
+                        const uint32_t mA = (amag >> mshift) & mmask;
+                        const uint32_t idx = wp + s_stride * (abk >> 31) + a_stride * mA + row_entries * tA;
+                        acc += __uint_as_float((uint32_t)lut_s[idx] << 16);
+                    }
                 }
             }
             tile[gl][tx] = acc * unit;
