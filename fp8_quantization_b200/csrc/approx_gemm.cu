@@ -468,12 +468,20 @@ struct LutGemmArgs {
     int t_bias;           // t = tA_idx + tB_idx - t_bias
     const int* gate;      // non-null: run only if *gate != 0
     ConvPlane cp;         // CONV instantiations: the A operand is gathered from a decoded NCHW plane
+    // stream-K (sk_ctas > 0): a 1-D grid of sk_ctas persistent CTAs; the (tile, k-tile) work units, tiles in
+    // column-fastest order, are dealt in equal contiguous ranges.  A CTA that covers a tile's whole K range
+    // stores it directly; partial ranges go to `partial` as [cta][slot][BM][BN] (slot 0: the CTA's first
+    // segment, slot 1: its last) and streamk_fixup_kernel adds a tile's segments in k order -- under the same
+    // exactness certificate as split-K (`splits` = upper bound of segments per tile).
+    int sk_ctas, sk_tiles_n;
+    int64_t sk_tiles;
 };
 
 // KT: k-tile depth (8 where a large table leaves little shared memory for the operand ring).
 // SIDX: signed-index table layout (lut.cuh): the B word is a full 32-bit byte offset, multiplier +1.0.
 // CONV: implicit im2col in the A-tile loader (ConvPlane) instead of a pre-gathered Aw plane.
-template <int WARPS, int RPW, int CPL, int KT, bool SIDX, bool CONV>
+// SK: stream-K instantiation (persistent CTAs over (tile, k-tile) ranges, see LutGemmArgs::sk_ctas).
+template <int WARPS, int RPW, int CPL, int KT, bool SIDX, bool CONV, bool SK>
 __global__ void __launch_bounds__(32 * WARPS, (WARPS >= 16) ? 1 : ((RPW * CPL >= 64) ? 16 / WARPS : 24 / WARPS))
 approx_gemm_lut_kernel(LutGemmArgs a)
 {
@@ -486,7 +494,7 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     uint32_t* As = reinterpret_cast<uint32_t*>(smem + a.lut_bytes);   // [ST][KT][BM]
     uint32_t* Bs = As + ST * KT * BM;                                 // [ST][KT][BN]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t m0 = (int64_t)blockIdx.x * BM, n0 = (int64_t)blockIdx.y * BN;
+    int64_t m0 = (int64_t)blockIdx.x * BM, n0 = (int64_t)blockIdx.y * BN;
 
     // pair table -> shared memory
     {
@@ -501,7 +509,7 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     static_assert(NTHR % BM == 0 && (KT * BM) % NTHR == 0, "A-tile gather mapping");
     const uint32_t* crow = nullptr;   // address of the row's top-left tap (may lie outside the image: never read)
     int ch0 = 0, cw0 = 0;
-    if (CONV) {
+    auto conv_row_setup = [&]() {
         const int64_t r = m0 + tid % BM;
         const int wo = (int)(r % a.cp.Wo);
         const int64_t t2 = r / a.cp.Wo;
@@ -511,7 +519,8 @@ approx_gemm_lut_kernel(LutGemmArgs a)
         cw0 = wo * a.cp.sw - a.cp.pw;
         if (r >= a.Mrows) ch0 = -(1 << 20);   // rows beyond the matrix: every tap out of range
         crow = a.cp.Pw + b * a.cp.img_words + (int64_t)ch0 * a.cp.W + cw0;
-    }
+    };
+    if (CONV) conv_row_setup();
     auto load_tile = [&](int kt, int stage) {
         const uint32_t* gb = a.Bw + (int64_t)kt * KT * a.Npad + n0;
         if (CONV) {
@@ -547,10 +556,38 @@ approx_gemm_lut_kernel(LutGemmArgs a)
         for (int j = 0; j < CPL; ++j) acc[i][j] = 0.0f;
 
     const int nk_all = a.Kpad / KT;
-    const int kt0 = (a.splits > 1) ? (int)((int64_t)blockIdx.z * nk_all / a.splits) : 0;
-    const int nk = ((a.splits > 1) ? (int)((int64_t)(blockIdx.z + 1) * nk_all / a.splits) : nk_all) - kt0;
-    float macc = 0.0f;   // split-K: largest |partial sum| seen at a k-tile boundary
+    constexpr bool streamk = SK;
+    int kt0 = (!streamk && a.splits > 1) ? (int)((int64_t)blockIdx.z * nk_all / a.splits) : 0;
+    int nk = ((!streamk && a.splits > 1) ? (int)((int64_t)(blockIdx.z + 1) * nk_all / a.splits) : nk_all) - kt0;
+    float macc = 0.0f;   // split-K / stream-K: largest |partial sum| seen at a k-tile boundary
     const uint32_t zero_word = a.zero_word;
+    // sampled zero statistics of the activations (predecode pass): low half zeros, high half elements
+    const unsigned long long zc = *a.zero_count;
+    const bool sparse = a.sparse_a >= 0 ? a.sparse_a != 0
+                                        : (CPL == 4 && 10ull * (zc & 0xFFFFFFFFull) >= 4ull * (zc >> 32));
+    // stream-K: this CTA's contiguous range of (tile, k-tile) units
+    const int64_t sk_units = a.sk_tiles * nk_all;
+    int64_t sk_u = streamk ? (int64_t)blockIdx.x * sk_units / a.sk_ctas : 0;
+    const int64_t sk_end = streamk ? (int64_t)(blockIdx.x + 1) * sk_units / a.sk_ctas : 1;
+    bool sk_first = true;
+  for (; sk_u < sk_end; sk_first = false) {
+    if (streamk) {
+        const int64_t tile = sk_u / nk_all;
+        kt0 = (int)(sk_u - tile * nk_all);
+        nk = (int)((nk_all - kt0 < sk_end - sk_u) ? (nk_all - kt0) : (sk_end - sk_u));
+        sk_u += nk;
+        m0 = (tile / a.sk_tiles_n) * BM;
+        n0 = (tile % a.sk_tiles_n) * BN;
+        if (CONV) conv_row_setup();
+#pragma unroll
+        for (int i = 0; i < RPW; ++i)
+#pragma unroll
+            for (int j = 0; j < CPL; ++j) acc[i][j] = 0.0f;
+        macc = 0.0f;
+        __syncthreads();   // every warp is done with the previous segment's operand stages
+    } else {
+        sk_u = sk_end;
+    }
 #pragma unroll
     for (int s = 0; s < ST - 1; ++s) {
         if (s < nk) load_tile(kt0 + s, s);
@@ -614,15 +651,27 @@ approx_gemm_lut_kernel(LutGemmArgs a)
             }
         }
     };
-    // sampled zero statistics of the activations (predecode pass): low half zeros, high half elements
-    const unsigned long long zc = *a.zero_count;
-    const bool sparse = a.sparse_a >= 0 ? a.sparse_a != 0
-                                        : (CPL == 4 && 10ull * (zc & 0xFFFFFFFFull) >= 4ull * (zc >> 32));
     if (sparse) mainloop(std::true_type{});
     else            mainloop(std::false_type{});
     cp_async_wait<0>();
 
-    if (a.splits > 1) {
+    if (streamk && nk < nk_all) {
+        // a partial k range of this tile: certificate as for split-K (see below), then the slot store
+        const int t_max = a.tmax[0] + a.tmax[1] - a.t_bias;
+        int lg = 0;
+        while ((1 << lg) < KT) ++lg;
+        const int dl = t_max + a.M + 1 + lg;
+        if (dl > 23 || !(macc * (float)a.splits <= 16777216.0f - (float)(1 << (dl > 0 ? dl : 0)))) *a.inexact = 1;
+        float* P = a.partial + ((int64_t)blockIdx.x * 2 + (sk_first ? 0 : 1)) * (int64_t)(BM * BN);
+#pragma unroll
+        for (int i = 0; i < RPW; ++i) {
+            float* prow = P + (warp * RPW + i) * BN + lane * CPL;
+            if (CPL == 4) *reinterpret_cast<float4*>(prow) = make_float4(acc[i][0], acc[i][1], acc[i][CPL - 2], acc[i][CPL - 1]);
+            else          *reinterpret_cast<float2*>(prow) = make_float2(acc[i][0], acc[i][1]);
+        }
+        continue;
+    }
+    if (!streamk && a.splits > 1) {
         // Exactness certificate.  Table entries are integers (units of u) of magnitude <= 2^(t + M + 1), so one
         // k tile moves a running sum by at most D = KT * 2^(t_max + M + 1).  If every slice's running sum stayed
         // within (2^24 - D) / splits at all of its k-tile boundaries, then every intermediate sum of every slice,
@@ -675,6 +724,43 @@ approx_gemm_lut_kernel(LutGemmArgs a)
                 if (n + j < a.N) crow[n + j] = acc[i][j] * unit;
         }
     }
+  }   // stream-K segment loop (one pass otherwise)
+}
+
+// stream-K fix-up: one CTA per output tile.  Finds the CTAs whose unit ranges intersect the tile's K range; a
+// tile covered by a single CTA was stored by the GEMM itself, otherwise its segments are added in k order.
+__global__ void __launch_bounds__(256) streamk_fixup_kernel(const float* __restrict__ P, int G, int64_t tiles, int tiles_n,
+                                                            int nk_all, int BM, int BN, float* __restrict__ C, int64_t ldc,
+                                                            int64_t Mrows, int64_t N, BiasSrc bias, int M, int qamaa,
+                                                            QamaaOp qop, const int* __restrict__ inexact,
+                                                            const int* __restrict__ offgrid)
+{
+    if (*inexact != 0 || *offgrid != 0) return;
+    const int64_t U = tiles * nk_all, tile = blockIdx.x;
+    const int64_t u_lo = tile * nk_all, u_hi = u_lo + nk_all;
+    auto start = [&](int64_t g) { return g * U / G; };
+    int64_t g0 = u_lo * G / U;
+    while (g0 > 0 && start(g0) > u_lo) --g0;
+    while (start(g0 + 1) <= u_lo) ++g0;
+    if (start(g0 + 1) >= u_hi) return;            // one CTA covered the whole K range: stored directly
+    const float unit = pow2f_i(1 - bias.R() - M);
+    if (qamaa) qop.begin();
+    const int64_t m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
+    for (int e = threadIdx.x; e < BM * BN; e += 256) {
+        const int r = e / BN, c = e - r * BN;
+        if (m0 + r >= Mrows || n0 + c >= N) continue;
+        float s = 0.0f;
+        bool have = false;
+        for (int64_t g = g0; g < G && start(g) < u_hi; ++g) {
+            const int slot = start(g) >= u_lo ? 0 : 1;
+            const float v = P[(g * 2 + slot) * (int64_t)(BM * BN) + e];
+            s = have ? s + v : v;
+            have = true;
+        }
+        s *= unit;
+        if (qamaa) s = qop.quant(s);
+        C[(m0 + r) * ldc + n0 + c] = s;
+    }
 }
 
 // Ordered sum of the split-K slices; does nothing when the exactness certificate failed.
@@ -702,12 +788,16 @@ struct LutTileCfg {
     int warps, rpw, cpl, kt, sidx;
     void (*kernel)(LutGemmArgs);
     void (*conv_kernel)(LutGemmArgs);
+    void (*sk_kernel)(LutGemmArgs);
+    void (*sk_conv_kernel)(LutGemmArgs);
     int BM() const { return warps * rpw; }
     int BN() const { return 32 * cpl; }
     size_t smem(int lut_bytes) const { return (size_t)lut_bytes + (size_t)LUT_STAGES * kt * (BM() + BN()) * 4; }
 };
 #define LUT_TILE(W, R, C, KT, S) \
-    {W, R, C, KT, S, approx_gemm_lut_kernel<W, R, C, KT, (S) != 0, false>, approx_gemm_lut_kernel<W, R, C, KT, (S) != 0, true>}
+    {W, R, C, KT, S, approx_gemm_lut_kernel<W, R, C, KT, (S) != 0, false, false>,          \
+     approx_gemm_lut_kernel<W, R, C, KT, (S) != 0, true, false>, approx_gemm_lut_kernel<W, R, C, KT, (S) != 0, false, true>, \
+     approx_gemm_lut_kernel<W, R, C, KT, (S) != 0, true, true>}
 static const LutTileCfg kLutTiles[] = {
     LUT_TILE(8, 16, 4, 16, 0),    // 128 x 128
     LUT_TILE(8, 32, 2, 16, 0),    // 256 x  64   (N <= 64)
@@ -737,10 +827,27 @@ static size_t conv_plane_bytes(int64_t plane_words, int64_t Kpad)
 {
     return (size_t)round_up(plane_words, 4) * 4 + (size_t)Kpad * 8 + 256;
 }
+// stream-K partial tiles: 2 slots per persistent CTA, at most 2 * 592 * 8192 (or 2 * 296 * 16384) floats
+constexpr size_t kStreamKBytes = (size_t)40 << 20;
 static size_t splitk_partial_bytes(int64_t Mrows, int64_t N)
 {
+    const int64_t el = Mrows * N;
+    if (el <= 0 || el > ((int64_t)1 << 24)) return 0;
     const int s = max_splits(Mrows, N);
-    return s > 1 ? round_up((size_t)s * Mrows * N * 4, 256) : 0;
+    return std::max<size_t>(kStreamKBytes, s > 1 ? round_up((size_t)s * Mrows * N * 4, 256) : 0);
+}
+struct LutTileCfg;
+static int resident_ctas(const LutTileCfg& c, int lut_bytes);
+
+static int resident_ctas(const LutTileCfg& c, int lut_bytes)
+{
+    const size_t sm = c.smem(lut_bytes) + 1024;
+    if (sm > 227 * 1024) return 0;
+    int r = (int)((227 * 1024) / sm);
+    const int acc_regs = c.rpw * c.cpl >= 64 ? 128 : 80;
+    r = std::min(r, 65536 / (acc_regs * 32 * c.warps));
+    r = std::min(r, 64 / c.warps);
+    return r;
 }
 
 // Cost model (in table lookups per SM): an SM's lookup rate saturates with 8 resident warps; a CTA does
@@ -774,12 +881,7 @@ static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int64_t Kpad,
     for (int pass = 0; pass < 2 && !best; ++pass, forced_s = 0)
     for (const LutTileCfg& c : kLutTiles) {
         if (c.sidx != sidx) continue;
-        const size_t sm = c.smem(lut_bytes) + 1024;
-        if (sm > 227 * 1024) continue;
-        int r = (int)((227 * 1024) / sm);
-        const int acc_regs = c.rpw * c.cpl >= 64 ? 128 : 80;
-        r = std::min(r, 65536 / (acc_regs * 32 * c.warps));
-        r = std::min(r, 64 / c.warps);
+        const int r = resident_ctas(c, lut_bytes);
         if (r < 1) continue;
         const int64_t nk = Kpad / c.kt;
         const double T = (double)c.BM() * c.BN() * c.kt * (c.cpl == 2 ? 1.06 : 1.0) * (c.kt < 16 ? 1.05 : 1.0);
@@ -792,6 +894,9 @@ static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int64_t Kpad,
         for (int S = 1; S <= max_s; ++S) {
             if (forced_s && S != forced_s) continue;
             if (S > 1 && nk / S < 4) break;
+            // two full waves of whole tiles already balance well: measured on 4096^3, splitting then only adds
+            // the partial-sum traffic (6.36 vs 6.43 T MAC/s)
+            if (S > 1 && !forced_s && ceil_div(Mrows, c.BM()) * ceil_div(N, c.BN()) >= (int64_t)2 * sms * r) break;
             const int64_t nc = ceil_div(Mrows, c.BM()) * ceil_div(N, c.BN()) * S;
             const int64_t full = nc / ((int64_t)sms * r), rem = nc - full * sms * r;
             const int rem_per_sm = (int)ceil_div(rem, sms);
@@ -801,6 +906,16 @@ static const LutTileCfg* choose_lut_tile(int64_t Mrows, int64_t N, int64_t Kpad,
             if (S > 1) cost += 3.0e5 + 4.0 * (double)S * Mrows * N / sms;
             if (!best || cost < best_cost) { best = &c; best_cost = cost; *splits = S; }
             if (all) all->push_back(LutCand{cost, &c, S});
+        }
+        // stream-K (S == 0): the (tile, k-tile) units dealt evenly over sms * r persistent CTAs -- no tile
+        // quantisation; costs the partial-tile traffic and the fix-up launch.  Only a measured candidate.
+        if (all && max_s > 1 && !forced_s) {
+            const int64_t tiles = ceil_div(Mrows, c.BM()) * ceil_div(N, c.BN()), G = (int64_t)sms * r;
+            if (tiles * nk >= 4 * G && tiles < 8 * G && (size_t)(2 * G) * c.BM() * c.BN() * 4 <= kStreamKBytes) {
+                const double cost = (double)tiles * T * ((double)nk + 2.0) / sms / rate(r) + 2.0 * T + 3.0e5 +
+                                    8.0 * (double)G * c.BM() * c.BN() / sms;
+                all->push_back(LutCand{cost, &c, 0});
+            }
         }
     }
     return best;
@@ -995,6 +1110,8 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         {
             B200_CUDA_TRY(cudaFuncSetAttribute(c.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
             B200_CUDA_TRY(cudaFuncSetAttribute(c.conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            B200_CUDA_TRY(cudaFuncSetAttribute(c.sk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            B200_CUDA_TRY(cudaFuncSetAttribute(c.sk_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         }
     }
     int S = 1;
@@ -1004,7 +1121,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     const LutTileCfg* tc = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, max_s, &S, &cands, &forced);
     if (!tc) { set_error("b200_approx_gemm: pair table does not fit shared memory"); return B200_ERR_ARGUMENT; }
     PredecodeArgs pa;
-    pa.tmax = max_s > 1 ? flag + 4 : nullptr;
+    pa.tmax = partial ? flag + 4 : nullptr;
     pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
     pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
     pa.zero_count = reinterpret_cast<unsigned long long*>(flag + 2);
@@ -1043,7 +1160,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     B200_LAUNCH_CHECK("predecode_kernel<A>");
     PredecodeArgs pb = pa;
     pb.zero_count = nullptr;
-    pb.tmax = max_s > 1 ? flag + 5 : nullptr;
+    pb.tmax = partial ? flag + 5 : nullptr;
     pb.src = B; pb.s_row = sb_n; pb.s_k = sb_k; pb.dst = Bw; pb.rows = N; pb.Rpad = Npad;
     const dim3 pgrid((unsigned)(Npad / 32), (unsigned)(Kpad / 32));
     if (sb_k == 1 && sb_n != 1) predecode_kernel<true, true><<<pgrid, 256, 0, st>>>(pb, geom);
@@ -1067,23 +1184,46 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     auto launch = [&](const LutTileCfg* cfg, int splits) -> int {
         LutGemmArgs l = la;
         l.splits = splits; l.gate = nullptr;
-        (gather ? cfg->conv_kernel : cfg->kernel)<<<dim3((unsigned)ceil_div(Mrows, cfg->BM()), (unsigned)ceil_div(N, cfg->BN()), (unsigned)splits),
-                                                    32 * cfg->warps, cfg->smem(lut_bytes), st>>>(l);
+        l.sk_ctas = 0; l.sk_tiles_n = 0; l.sk_tiles = 0;
+        const dim3 tgrid((unsigned)ceil_div(Mrows, cfg->BM()), (unsigned)ceil_div(N, cfg->BN()), (unsigned)std::max(splits, 1));
+        if (splits == 0) {   // stream-K
+            const int64_t tiles = (int64_t)tgrid.x * tgrid.y, nk_all = Kpad / cfg->kt;
+            const int64_t G = std::min<int64_t>((int64_t)sms * resident_ctas(*cfg, lut_bytes), tiles * nk_all);
+            l.sk_ctas = (int)G; l.sk_tiles_n = (int)tgrid.y; l.sk_tiles = tiles;
+            l.splits = (int)(2 + nk_all / std::max<int64_t>(1, tiles * nk_all / G));   // segments per tile, upper bound
+            (gather ? cfg->sk_conv_kernel : cfg->sk_kernel)<<<dim3((unsigned)G), 32 * cfg->warps, cfg->smem(lut_bytes), st>>>(l);
+            B200_LAUNCH_CHECK("approx_gemm_lut_kernel(stream-K)");
+            streamk_fixup_kernel<<<(unsigned)tiles, 256, 0, st>>>(partial, (int)G, tiles, (int)tgrid.y, (int)nk_all, cfg->BM(),
+                                                                  cfg->BN(), C, ldc, Mrows, N, bias, M, l.qamaa, l.qop,
+                                                                  flag + 6, flag);
+            B200_LAUNCH_CHECK("streamk_fixup_kernel");
+        } else {
+            (gather ? cfg->conv_kernel : cfg->kernel)<<<tgrid, 32 * cfg->warps, cfg->smem(lut_bytes), st>>>(l);
+        }
         if (splits > 1) {
             B200_LAUNCH_CHECK("approx_gemm_lut_kernel(split-K)");
             splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(Mrows * N, 256), 4 * sms), 256, 0, st>>>(
                 partial, splits, C, ldc, Mrows, N, bias, M, l.qamaa, l.qop, flag + 6, flag);
             B200_LAUNCH_CHECK("splitk_reduce_kernel");
+        }
+        if (splits != 1) {
             // runs only if the exactness certificate failed
             int S1 = 1;
             const LutTileCfg* t1 = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, 1, &S1);
-            l.splits = 1; l.gate = flag + 6;
+            l.splits = 1; l.gate = flag + 6; l.sk_ctas = 0;
             (gather ? t1->conv_kernel : t1->kernel)<<<dim3((unsigned)ceil_div(Mrows, t1->BM()), (unsigned)ceil_div(N, t1->BN())), 32 * t1->warps,
                                                      t1->smem(lut_bytes), st>>>(l);
         }
         B200_LAUNCH_CHECK("approx_gemm_lut_kernel");
         return B200_OK;
     };
+    if (partial && getenv("B200_LUT_STREAMK") && atoi(getenv("B200_LUT_STREAMK")) != 0 && partial) {   // experiments / tests
+        const int64_t tiles = ceil_div(Mrows, tc->BM()) * ceil_div(N, tc->BN());
+        if ((size_t)(2 * (int64_t)sms * resident_ctas(*tc, lut_bytes)) * tc->BM() * tc->BN() * 4 <= kStreamKBytes && tiles > 0) {
+            S = 0;
+            forced = true;
+        }
+    }
     // measured choice (see TuneKey above)
     if (autotune_on() && !forced && cands.size() > 1 && Mrows * N * Kpad >= kTuneMinMacs) {
         const TuneKey key{Mrows, N, Kpad, lut_bytes, geom.sidx, gather ? 1 : 0, max_s, qop ? 1 : 0};
@@ -1095,28 +1235,46 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         }
         cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
         if (!have && cudaStreamIsCapturing(st, &cap) == cudaSuccess && cap == cudaStreamCaptureStatusNone) {
-            std::sort(cands.begin(), cands.end(), [](const LutCand& x, const LutCand& y) { return x.cost < y.cost; });
-            if ((int)cands.size() > kTuneCandidates) cands.resize(kTuneCandidates);
+            // the model's best regular configurations (within 1.6x of its favourite) plus the two best stream-K ones
+            auto by_cost = [](const LutCand& x, const LutCand& y) { return x.cost < y.cost; };
+            std::vector<LutCand> reg, sk;
+            for (const LutCand& c : cands) (c.S == 0 ? sk : reg).push_back(c);
+            std::sort(reg.begin(), reg.end(), by_cost);
+            std::sort(sk.begin(), sk.end(), by_cost);
+            cands.clear();
+            for (size_t i = 0; i < reg.size() && (int)i < kTuneCandidates - 1 && reg[i].cost <= 1.6 * reg[0].cost; ++i) cands.push_back(reg[i]);
+            for (size_t i = 0; i < sk.size() && i < 2; ++i) cands.push_back(sk[i]);
             cudaEvent_t e0, e1;
             B200_CUDA_TRY(cudaEventCreate(&e0));
             B200_CUDA_TRY(cudaEventCreate(&e1));
-            float best_ms = 0.0f;
             int rc = B200_OK;
-            for (size_t i = 0; i < cands.size() && rc == B200_OK; ++i) {
-                if (cands[i].cost > 1.6 * cands[0].cost) break;
-                for (int rep = 0; rep < 3 && rc == B200_OK; ++rep) {   // one warm run, two timed
+            auto time_cand = [&](const LutCand& c, float* ms) {
+                for (int rep = 0; rep < 4 && rc == B200_OK; ++rep) {   // one warm run, three timed
                     if (rep == 1) cudaEventRecord(e0, st);
                     cudaMemsetAsync(flag + 6, 0, 4, st);
-                    rc = launch(cands[i].cfg, cands[i].S);
+                    rc = launch(c.cfg, c.S);
                 }
-                if (rc != B200_OK) break;
+                if (rc != B200_OK) return;
                 cudaEventRecord(e1, st);
-                if (cudaEventSynchronize(e1) != cudaSuccess) { rc = cuda_fail(cudaGetLastError(), "autotune"); break; }
-                float ms = 0.0f;
-                cudaEventElapsedTime(&ms, e0, e1);
+                if (cudaEventSynchronize(e1) != cudaSuccess) { rc = cuda_fail(cudaGetLastError(), "autotune"); return; }
+                cudaEventElapsedTime(ms, e0, e1);
                 g_tune_runs.fetch_add(1, std::memory_order_relaxed);
-                // a later candidate must win by 2 %: timing noise must not displace the cost model's choice
-                if (i == 0 || ms < 0.98f * best_ms) { best_ms = ms; tc = cands[i].cfg; S = cands[i].S; }
+            };
+            // The model's favourite is timed first AND last (clocks ramp up during the first runs of a process);
+            // a challenger has to beat its better time by 1.5 %: timing noise must not displace the model's choice.
+            std::vector<float> ms(cands.size(), 0.0f);
+            for (size_t i = 0; i < cands.size() && rc == B200_OK; ++i) time_cand(cands[i], &ms[i]);
+            if (rc == B200_OK && cands.size() > 1) {
+                float again = 0.0f;
+                time_cand(cands[0], &again);
+                if (rc == B200_OK && again < ms[0]) ms[0] = again;
+            }
+            if (rc == B200_OK) {
+                size_t best = 0;
+                for (size_t i = 1; i < cands.size(); ++i)
+                    if (ms[i] < 0.985f * ms[0] && (best == 0 || ms[i] < ms[best])) best = i;
+                tc = cands[best].cfg;
+                S = cands[best].S;
             }
             cudaEventDestroy(e0);
             cudaEventDestroy(e1);
@@ -1231,7 +1389,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     // runs only if the predecode found an off-grid operand
     pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<ApproxPairOp>(conditional)");
-    set_path(lut->geom.sidx ? "lut-signed" : (g_last_splits > 1 ? "lut-splitk" : "lut"));
+    set_path(lut->geom.sidx ? "lut-signed" : (g_last_splits > 1 ? "lut-splitk" : (g_last_splits == 0 ? "lut-streamk" : "lut")));
     return B200_OK;
 }
 
@@ -1292,7 +1450,7 @@ int b200::qamaa_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t s
         return rc;
     pair_gemm_kernel<QamaaOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<QamaaOp>(conditional)");
-    set_path(g_last_splits > 1 ? "qamaa-lut-splitk" : "qamaa-lut");
+    set_path(g_last_splits > 1 ? "qamaa-lut-splitk" : (g_last_splits == 0 ? "qamaa-lut-streamk" : "qamaa-lut"));
     return B200_OK;
 }
 

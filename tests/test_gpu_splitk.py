@@ -75,8 +75,8 @@ def test_splitk_bit_identical_to_unsplit(fq, shape, top_frac, expect_exact):
 
 
 def test_splitk_default_choice_and_oracle(fq):
-    """The cost model splits a ResNet-18 layer4-shaped GEMM at batch 8 (392 x 4608 x 512: 16 CTAs of 128 x 128
-    on 148 SMs) without being told to; a sample of output columns is checked against the oracle."""
+    """A ResNet-18 layer4-shaped GEMM at batch 8 (392 x 4608 x 512: 16 CTAs of 128 x 128 on 148 SMs) is split
+    along K (split-K or stream-K) without being told to; a sample of output columns is checked against the oracle."""
     Mr, K, N = 392, 4608, 512
     E, M, bA, bB, bR = 4, 3, 6, 10, 7
     a = grid_values(E, M, bA, (Mr, K), 3, 0.6)
@@ -84,7 +84,7 @@ def test_splitk_default_choice_and_oracle(fq):
     b = grid_values(E, M, bB, (K, N), 5, 0.8)
     p = fq.ops.make_params(MAIN)
     got, path, fl = run(fq, torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda(), bA, bB, bR, p, None)
-    assert path == "lut-splitk" and fl[6] == 0, (path, fl)
+    assert path in ("lut-splitk", "lut-streamk") and fl[6] == 0, (path, fl)     # split or stream-K, whichever measured faster
     T = orc.get_error_table_NN(E, M, True, 3)
     cols = [0, 1, 255, 511]
     rows = slice(0, 48)
@@ -157,3 +157,71 @@ def test_conv_gather_equals_im2col_plane(fq, case, mode):
             os.environ.pop("B200_CONV_GATHER", None)
     assert float(outs[0].abs().max()) > 0
     assert torch.equal(outs[0].view(torch.int32), outs[1].view(torch.int32)), case
+
+
+def _streamk(fn):
+    os.environ["B200_LUT_STREAMK"] = "1"
+    try:
+        return fn(), __import__("fp8_quantization_b200").ops.last_path()
+    finally:
+        os.environ.pop("B200_LUT_STREAMK", None)
+
+
+@pytest.mark.parametrize("shape", [(3152, 768, 768), (392, 4608, 512), (1000, 200, 130), (300, 1152, 128), (129, 96, 257)])
+@pytest.mark.parametrize("top_frac,expect_exact", [(0.5, True), (1.0, False)])
+def test_streamk_bit_identical_to_unsplit(fq, shape, top_frac, expect_exact):
+    """Stream-K (persistent CTAs over equal ranges of (tile, k-tile) units, partial tiles added in k order by the
+    fix-up kernel): bit-identical to the unsplit launch whether the exactness certificate holds or fails."""
+    Mr, K, N = shape
+    E, M = 4, 3
+    bA, bB = 8, 8
+    bR = 8 if expect_exact else 20
+    a = torch.from_numpy(grid_values(E, M, bA, (Mr, K), 21, top_frac)).cuda()
+    a[torch.rand(a.shape, device="cuda") < 0.3] = 0.0
+    b = torch.from_numpy(grid_values(E, M, bB, (K, N), 22, top_frac)).cuda()
+    p = fq.ops.make_params(MAIN)
+    ref, path1, _ = run(fq, a, b, bA, bB, bR, p, 1)
+    assert path1 == "lut"
+    got, path = _streamk(lambda: fq.ops.approx_matmul(a, b, bA, bB, bR, p))
+    fl = flags(fq)
+    assert path == "lut-streamk", path
+    assert fl[0] == 0 and (fl[6] == 0) == expect_exact, fl
+    assert torch.equal(got.view(torch.int32), ref.view(torch.int32)), shape
+
+
+def test_streamk_qamaa_and_conv(fq):
+    """Stream-K under the quantizing epilogue (the result quantizer runs in the fix-up) and with the conv gather
+    loader (the row setup is redone per tile)."""
+    Mr, K, N = 392, 2304, 256
+    x = torch.from_numpy(grid_values(4, 3, 7, (Mr, K), 6, 0.7)).cuda()
+    y = torch.from_numpy(grid_values(4, 3, 9, (K, N), 7, 0.7)).cuda()
+    maxval = torch.tensor([float(x.abs().max() * y.abs().max() * 8)], device="cuda")
+    kw = dict(x_bias=torch.tensor([7.0], device="cuda"), y_bias=torch.full((N,), 9.0, device="cuda"))
+    os.environ["B200_LUT_SPLITK"] = "1"
+    try:
+        ref = fq.ops.qamaa_matmul(x, y, 8, maxval, 3.0, 1, **kw)
+    finally:
+        os.environ.pop("B200_LUT_SPLITK", None)
+    got, path = _streamk(lambda: fq.ops.qamaa_matmul(x, y, 8, maxval, 3.0, 1, **kw))
+    assert path == "qamaa-lut-streamk", path
+    assert torch.equal(got.view(torch.int32), ref.view(torch.int32))
+    for case in CONV_CASES[:5] + CONV_CASES[6:8]:
+        B, C, H, W, Co, k, st, pad, dil, groups = case
+        E, M, bA, bW = 4, 3, 7, 9
+        xn = grid_values(E, M, bA, (B, C, H, W), 11, 0.8)
+        xn[np.random.default_rng(12).random(xn.shape) < 0.4] = 0.0
+        xd = torch.from_numpy(xn).cuda()
+        wd = torch.from_numpy(grid_values(E, M, bW, (Co, C // groups, k, k), 13, 0.8)).cuda()
+        xb, rb = torch.tensor([float(bA)], device="cuda"), torch.tensor([8.0], device="cuda")
+        wb = torch.full((Co,), float(bW), device="cuda")
+        call = lambda: fq.ops.approx_conv2d(xd, wd, xb, wb, rb, fq.ops.make_params(MAIN), (st, st), (pad, pad), (dil, dil), groups)
+        os.environ["B200_LUT_SPLITK"] = "1"
+        os.environ["B200_CONV_GATHER"] = "2"
+        try:
+            want = call()
+            got, path = _streamk(call)
+        finally:
+            os.environ.pop("B200_LUT_SPLITK", None)
+            os.environ.pop("B200_CONV_GATHER", None)
+        assert path == "lut-streamk", (path, case)
+        assert torch.equal(got.view(torch.int32), want.view(torch.int32)), case
