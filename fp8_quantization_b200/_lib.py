@@ -38,6 +38,12 @@ class ApproxParams(ctypes.Structure):
     ]
 
 
+class ActQuant(ctypes.Structure):
+    """struct b200_act_quant (include/fp8approx_b200.h): the fused input fake-quantizer."""
+    _fields_ = [("maxval_dev", ctypes.c_void_p), ("bias_dev", ctypes.c_void_p), ("mantissa_bits", ctypes.c_float),
+                ("n_bits", ctypes.c_int32), ("sign_bits", ctypes.c_int32)]
+
+
 class ConvGeom(ctypes.Structure):
     """struct b200_conv_geom (conv geometry of QCustomBNConv2dTorch.run_forward, approx_calculation.py:822-857)."""
     _fields_ = [("batch", ctypes.c_int64), ("C_in", ctypes.c_int32), ("H", ctypes.c_int32), ("W", ctypes.c_int32),
@@ -65,6 +71,11 @@ SIGNATURES = {
                                  c_int, ctypes.POINTER(ApproxParams), c_vp, c_sz, c_vp]),
     "b200_approx_gemm_fbias": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp,
                                        c_i64, c_vp, ctypes.POINTER(ApproxParams), c_vp, c_sz, c_vp]),
+    "b200_approx_gemm_fbias_fq": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp,
+                                          c_i64, c_vp, ctypes.POINTER(ApproxParams), ctypes.POINTER(ActQuant), c_vp, c_sz,
+                                          c_vp]),
+    "b200_approx_conv2d_fbias_fq": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_vp, c_i64, c_vp,
+                                            ctypes.POINTER(ApproxParams), ctypes.POINTER(ActQuant), c_vp, c_sz, c_vp]),
     "b200_qamaa_gemm": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_int, c_f32,
                                 c_int, c_vp]),
     "b200_qamaa_gemm_workspace_bytes": (c_sz, [c_i64, c_i64, c_i64]),

@@ -31,7 +31,8 @@ class _ApproxMixin:
     def approx_multiply(self, x, y, x_bias, y_bias, res_bias):
         if y.shape[1] != 1:
             if self.approx_flag:
-                return ops.approx_matmul(x, y, x_bias, y_bias, res_bias, self._params(False))
+                return ops.approx_matmul(x, y, x_bias, y_bias, res_bias, self._params(False),
+                                         act_quant=self.__dict__.pop("_b200_act_quant", None))
             if self.quantize_after_mult_and_add:
                 q = self.res_quantizer.quantizer
                 return ops.qamaa_matmul(x, y, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits, x_bias=x_bias,
@@ -49,6 +50,9 @@ class _ApproxMixin:
 
 
 class QCustomLinearTorch(_ApproxMixin, QuantizationHijacker, nn.Linear):
+    def _fusable_input_quant(self, x):
+        return self.out_features != 1          # a single output column takes the tensor-bias branch on x_q
+
     def run_forward(self, x, weight, bias, offsets=None):
         """approx_calculation.py:1007-1023.  Inputs with more than two dims are flattened to
         [rows, K] (the reference asserts on them)."""
@@ -90,7 +94,7 @@ class _ConvMixin(_ApproxMixin):
         if use_approx and self.approx_flag:
             out = ops.approx_conv2d(x, weight, self.get_acts_fp_bias(), self.get_weights_fp_bias(),
                                     self.get_res_fp_bias(), self._params(Ng == 1), self.stride, self.padding,
-                                    self.dilation, self.groups)
+                                    self.dilation, self.groups, act_quant=self.__dict__.pop("_b200_act_quant", None))
         elif use_approx and self.quantize_after_mult_and_add and Ng != 1:
             q = self.res_quantizer.quantizer
             out = ops.qamaa_conv2d(x, weight, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits, self.stride,
@@ -108,6 +112,9 @@ class _ConvMixin(_ApproxMixin):
 
 
 class QCustomBNConv2dTorch(_ConvMixin, BNFusedHijacker, nn.Conv2d):
+    def _fusable_input_quant(self, x):
+        return x.dim() == 4 and self.out_channels // self.groups != 1     # depthwise groups read x_q directly
+
     def run_forward(self, x, weight, bias, offsets=None):
         """approx_calculation.py:822-917."""
         return self._conv_forward_cols(x, weight, bias, use_approx=True)

@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(PC_ROWS) predecode_conv_kernel(PredecodeArgs a
         if (valid_r && k0 + kk < a.K) {
             const int h = h0 + ky * s.dh, wi = w0 + kx * s.dw;
             float v = 0.0f;                                              // F.pad zeros (:727)
-            if (h >= 0 && h < s.H && wi >= 0 && wi < s.W) v = __ldg(base + ((int64_t)c * s.H + h) * s.W + wi);
+            if (h >= 0 && h < s.H && wi >= 0 && wi < s.W) v = s.fq(__ldg(base + ((int64_t)c * s.H + h) * s.W + wi));
             w = predecode_a(g, v, bA, off, tmax);
             zeros += (v == 0.0f);
         }
@@ -351,7 +351,8 @@ __global__ void __launch_bounds__(256) predecode_plane_kernel(PredecodeArgs a, L
     if (i4 < total) {
         // img % 4 == 0 (checked by the host): the four elements are in one image and 16-byte aligned
         const int64_t b = i4 / img, j = i4 - b * img;
-        const float4 v = __ldg(reinterpret_cast<const float4*>(s.p + (b * s.C + s.c0) * (int64_t)s.H * s.W + j));
+        float4 v = __ldg(reinterpret_cast<const float4*>(s.p + (b * s.C + s.c0) * (int64_t)s.H * s.W + j));
+        v.x = s.fq(v.x); v.y = s.fq(v.y); v.z = s.fq(v.z); v.w = s.fq(v.w);   // fused input fake-quantizer, if any
         uint4 w;
         w.x = predecode_a(g, v.x, bA, off, tmax);
         w.y = predecode_a(g, v.y, bA, off, tmax);
@@ -1460,6 +1461,35 @@ extern "C" int b200_approx_gemm(const float* A, int64_t lda, const float* B, int
 {
     BiasSrc b{bA, bR, nullptr, nullptr, bB, nullptr, 1};
     return approx_gemm_impl(make_gemm_asrc(A, lda), B, sb_k, sb_n, C, ldc, Mrows, K, N, b, p, workspace, workspace_bytes, stream);
+}
+
+// Sets the fused-input-quantizer fields of an operand view; B200_OK, or an error for a bad descriptor.
+int b200::apply_act_quant(ASrc* a, const b200_act_quant* aq)
+{
+    if (!aq) return B200_OK;
+    if (!aq->maxval_dev || !aq->bias_dev || aq->n_bits < 2 || aq->sign_bits < 0 || aq->sign_bits > 1) {
+        set_error("b200_act_quant: bad descriptor");
+        return B200_ERR_ARGUMENT;
+    }
+    a->fq_maxval = aq->maxval_dev;
+    a->fq_bias = aq->bias_dev;
+    a->fq_Mf = fminf(fmaxf(rintf(aq->mantissa_bits), 1.0f), (float)(aq->n_bits - aq->sign_bits));
+    a->fq_sign = aq->sign_bits;
+    return B200_OK;
+}
+
+extern "C" int b200_approx_gemm_fbias_fq(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n,
+                                         float* C, int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float* bA_dev,
+                                         const float* bB_dev, int64_t bB_stride, const float* bR_dev,
+                                         const b200_approx_params* p, const b200_act_quant* aq, void* workspace,
+                                         size_t workspace_bytes, void* stream)
+{
+    if (!p) { set_error("b200_approx_gemm_fbias_fq: params is NULL"); return B200_ERR_ARGUMENT; }
+    const int dflt = 1 << (p->expo_width > 0 ? p->expo_width - 1 : 0);
+    BiasSrc b{dflt, dflt, bA_dev, bR_dev, nullptr, bB_dev, bB_stride};
+    ASrc a = make_gemm_asrc(A, lda);
+    if (int rc = apply_act_quant(&a, aq)) return rc;
+    return approx_gemm_impl(a, B, sb_k, sb_n, C, ldc, Mrows, K, N, b, p, workspace, workspace_bytes, stream);
 }
 
 extern "C" int b200_approx_gemm_fbias(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n,

@@ -370,10 +370,29 @@ extern "C" size_t b200_approx_conv2d_workspace_bytes(const b200_conv_geom* g)
     return b200_approx_gemm_workspace_bytes(d.rows, d.Kg, d.Ng) + conv_gather_workspace_bytes(g->batch, d.Cg, g->H, g->W, d.Kg);
 }
 
+static int approx_conv2d_impl(const float* x, const float* w, float* out, const b200_conv_geom* g, const float* bA_dev,
+                              const float* bB_dev, int64_t bB_stride, const float* bR_dev, const b200_approx_params* p,
+                              const b200_act_quant* aq, void* workspace, size_t workspace_bytes, void* stream);
+
 extern "C" int b200_approx_conv2d_fbias(const float* x, const float* w, float* out, const b200_conv_geom* g,
                                         const float* bA_dev, const float* bB_dev, int64_t bB_stride,
                                         const float* bR_dev, const b200_approx_params* p, void* workspace,
                                         size_t workspace_bytes, void* stream)
+{
+    return approx_conv2d_impl(x, w, out, g, bA_dev, bB_dev, bB_stride, bR_dev, p, nullptr, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200_approx_conv2d_fbias_fq(const float* x, const float* w, float* out, const b200_conv_geom* g,
+                                           const float* bA_dev, const float* bB_dev, int64_t bB_stride,
+                                           const float* bR_dev, const b200_approx_params* p, const b200_act_quant* aq,
+                                           void* workspace, size_t workspace_bytes, void* stream)
+{
+    return approx_conv2d_impl(x, w, out, g, bA_dev, bB_dev, bB_stride, bR_dev, p, aq, workspace, workspace_bytes, stream);
+}
+
+static int approx_conv2d_impl(const float* x, const float* w, float* out, const b200_conv_geom* g, const float* bA_dev,
+                              const float* bB_dev, int64_t bB_stride, const float* bR_dev, const b200_approx_params* p,
+                              const b200_act_quant* aq, void* workspace, size_t workspace_bytes, void* stream)
 {
     if (int rc = check_device()) return rc;
     ConvDims d;
@@ -387,13 +406,16 @@ extern "C" int b200_approx_conv2d_fbias(const float* x, const float* w, float* o
             BiasSrc b{dflt, dflt, bA_dev, bR_dev, nullptr, bB_dev ? bB_dev + (int64_t)grp * d.Ng * bB_stride : nullptr,
                       bB_stride};
             const float* wg = w + (int64_t)grp * d.Ng * d.Kg;
-            if (int rc = approx_gemm_impl(make_conv_asrc(x, g, d, grp), wg, 1, d.Kg, out + (int64_t)grp * d.Ng,
+            ASrc av = make_conv_asrc(x, g, d, grp);
+            if (int rc = apply_act_quant(&av, aq)) return rc;
+            if (int rc = approx_gemm_impl(av, wg, 1, d.Kg, out + (int64_t)grp * d.Ng,
                                           g->C_out, d.rows, d.Kg, d.Ng, b, &pp, workspace, workspace_bytes, stream))
                 return rc;
         }
         return B200_OK;
     }
     // N == 1 per group: the reference's tensor-bias branch (approx_calculation.py:800-809)
+    if (aq) { set_error("b200_approx_conv2d_fbias_fq: the fused input quantizer is not available for depthwise groups"); return B200_ERR_ARGUMENT; }
     const int E = p->expo_width, M = p->mant_width;
     const signed char* host_table = nullptr;
     if (p->custom_table) {

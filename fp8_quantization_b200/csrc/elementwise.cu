@@ -45,21 +45,24 @@ fp8_fakequant_tensor_kernel(const float* __restrict__ x, float* __restrict__ y, 
     if (blockIdx.x == 0 && threadIdx.x == 0) bias_out[0] = bias;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const bool fast = fp8_ste_fast_ok(bias);          // exponent-field form: no log2f, no division (pair_math.cuh)
+    const int bias_i = (int)bias, M_i = (int)Mf;
+    auto q = [&](float v) { return fast ? fp8_ste_quant_fast(v, mx, bias_i, M_i, sign_bits) : fp8_ste_quant(v, mx, bias, Mf, sign_bits); };
     if (vec_ok) {
         const int64_t n4 = n >> 2;
         const float4* x4 = reinterpret_cast<const float4*>(x);
         float4* y4 = reinterpret_cast<float4*>(y);
         for (int64_t i = tid; i < n4; i += stride) {
             float4 v = __ldcs(x4 + i);
-            v.x = fp8_ste_quant(v.x, mx, bias, Mf, sign_bits);
-            v.y = fp8_ste_quant(v.y, mx, bias, Mf, sign_bits);
-            v.z = fp8_ste_quant(v.z, mx, bias, Mf, sign_bits);
-            v.w = fp8_ste_quant(v.w, mx, bias, Mf, sign_bits);
+            v.x = q(v.x);
+            v.y = q(v.y);
+            v.z = q(v.z);
+            v.w = q(v.w);
             y4[i] = v;
         }
-        for (int64_t i = (n4 << 2) + tid; i < n; i += stride) y[i] = fp8_ste_quant(x[i], mx, bias, Mf, sign_bits);
+        for (int64_t i = (n4 << 2) + tid; i < n; i += stride) y[i] = q(x[i]);
     } else {
-        for (int64_t i = tid; i < n; i += stride) y[i] = fp8_ste_quant(x[i], mx, bias, Mf, sign_bits);
+        for (int64_t i = tid; i < n; i += stride) y[i] = q(x[i]);
     }
 }
 

@@ -21,6 +21,9 @@ struct BiasSrc {
 };
 
 
+// fused input fake-quantizer of an operand view (approx_gemm.cu)
+int apply_act_quant(ASrc* a, const b200_act_quant* aq);
+
 // (device, host table) -> cached device copy of a 4^M int8 table; nullptr stays nullptr (zero table)
 int device_table(const signed char* host, int M, const signed char** dev_out);
 

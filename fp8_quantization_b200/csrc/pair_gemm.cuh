@@ -13,6 +13,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "pair_math.cuh"
+
 namespace b200 {
 
 // A operand: element (m, k) of the [Mrows, K] left matrix.
@@ -22,7 +24,23 @@ struct ASrc {
     int conv;        // 1: implicit im2col, K order (c, ky, kx), rows (b, ho, wo)
     int C, H, W, kh, kw, sh, sw, ph, pw, dh, dw, Ho, Wo;
     int c0;          // first input channel of the group being computed
-    __device__ __forceinline__ float load(int64_t m, int64_t k) const
+    // Fused input fake-quantizer: when fq_maxval is set, every element read through this
+    // view is quantize_to_fp8_ste_MM(x, maxval, ...) (quantization/quantizers/fp8_quantizer.py:119-154) of the
+    // raw tensor -- the same element function the stand-alone quantizer kernel evaluates, with the bias that
+    // kernel derived from the same maxval, so the bits are those of quantizing first.  Q(0) = 0: padding commutes.
+    const float* fq_maxval;   // device [1] or null
+    const float* fq_bias;     // device [1]: FPQuantizer.custom_bias
+    float fq_Mf;              // clamp(round(mantissa_bits), 1, n_bits - sign_bits)
+    int fq_sign;
+    __device__ __forceinline__ float fq(float v) const
+    {
+        if (!fq_maxval) return v;
+        const float mx = __ldg(fq_maxval), bias = __ldg(fq_bias);
+        return fp8_ste_fast_ok(bias) ? fp8_ste_quant_fast(v, mx, (int)bias, (int)fq_Mf, fq_sign)
+                                     : fp8_ste_quant(v, mx, bias, fq_Mf, fq_sign);
+    }
+    __device__ __forceinline__ float load(int64_t m, int64_t k) const { return fq(load_raw(m, k)); }
+    __device__ __forceinline__ float load_raw(int64_t m, int64_t k) const
     {
         if (!conv) return p[m * lda + k];
         const int kx = (int)(k % kw);

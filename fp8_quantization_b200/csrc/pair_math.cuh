@@ -173,6 +173,25 @@ __host__ __device__ inline float fp8_ste_quant(float x, float maxval, float bias
     return rintf(xc / scale) * scale;                           // :154
 }
 
+// The same element function without log2f / division, for an integral, moderate bias (what fp8_ste_bias returns
+// for any finite positive maxval): floor(log2|xc|) is the exponent field, and round-half-even to a multiple of
+// scale = 2^se is (xc + 1.5 * 2^(23+se)) - 1.5 * 2^(23+se), exact because |xc| < 2^(22+se).  Where log2f rounds
+// up to an integer just below a power of two the reference picks the coarser scale and still lands on the same
+// value (the all-ones mantissa rounds to the power of two on either grid).  Bit-identical to fp8_ste_quant on
+// every reference fixture (tests/golden/fakequant.npz) and against the oracle's log2f form on raw operands.
+__host__ __device__ inline bool fp8_ste_fast_ok(float bias) { const int b = (int)bias; return bias == (float)b && b > -90 && b < 90; }
+__device__ __forceinline__ float fp8_ste_quant_fast(float x, float maxval, int bias_i, int M_i, int sign_bits)
+{
+    const float mn = (sign_bits == 1) ? -maxval : 0.0f;                 // :119
+    const float xc = fminf(fmaxf(x, mn), maxval);                       // :120
+    const int ef = (int)((__float_as_uint(xc) >> 23) & 0xFFu);          // floor(log2|xc|) + 127 (0: zero / denormal)
+    int ls = ef - 127 + bias_i;                                         // :144
+    if (ls < 1) ls = 1;                                                 // clamp(min=1)
+    const int se = ls - M_i - bias_i;                                   // log2(scale), :151
+    const float magic = __uint_as_float(((uint32_t)(se + 23 + 127) << 23) | 0x00400000u);
+    return (xc + magic) - magic;                                        // == rint(xc / scale) * scale, :154
+}
+
 // bias = round(2**E - log2(maxval) + log2(2 - 2**-M) - 1), fp8_quantizer.py:111-117, fp32 op by op
 __host__ __device__ inline float fp8_ste_bias(float maxval, int n_bits, float mantissa_bits, int sign_bits, float* M_out)
 {

@@ -73,7 +73,18 @@ def error_table(expo_width, mant_width, withComp, dnsmp_factor, allow_unpinned_f
     return out
 
 
-def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out=None):
+def _act_quant_struct(act_quant, device):
+    """(maxval [1], bias [1], mantissa_bits, n_bits, sign_bits) -> (struct b200_act_quant, tensors kept alive)."""
+    maxval, bias, mbits, n_bits, sign_bits = act_quant
+    mv = maxval.to(device=device, dtype=torch.float32).reshape(-1)
+    bs = bias.to(device=device, dtype=torch.float32).reshape(-1)
+    if mv.numel() != 1 or bs.numel() != 1:
+        raise ValueError("the fused input quantizer needs a per-tensor range")
+    aq = _lib.ActQuant(mv.data_ptr(), bs.data_ptr(), float(mbits), int(n_bits), int(sign_bits))
+    return aq, (mv, bs)
+
+
+def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out=None, act_quant=None):
     """C = approx_multiply(x [Mrows,K], y [K,N]) in ONE launch sequence.
 
     Biases, two forms:
@@ -83,6 +94,8 @@ def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out
         elements; None -> 2^(E-1) like approx_calculation.py:938-939) -> b200_approx_gemm_fbias,
         which reads them on the device: no .item() host sync.
     `y` may be any strided view (e.g. weight.t()).
+    `act_quant` = (maxval, bias, mantissa_bits, n_bits, sign_bits): `x` holds RAW activations and the input
+    fake-quantizer runs inside the operand decode pass (b200_approx_gemm_fbias_fq); bit-identical to quantizing first.
     """
     lib = _lib.load()
     _require_cuda(x, y)
@@ -105,6 +118,8 @@ def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out
     nbytes = lib.b200_approx_gemm_workspace_bytes(Mrows, K, N)
     ws = _workspace(x.device, nbytes)
     int_path = isinstance(x_bias, int) and isinstance(res_bias, int)
+    if act_quant is not None and int_path:
+        raise ValueError("the fused input quantizer needs the device-bias form of the call")
     with torch.cuda.device(x.device):
         if int_path:
             if isinstance(y_bias, int):
@@ -134,9 +149,15 @@ def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out
                 if fb.numel() < N:
                     raise IndexError("index out of range: y_bias has fewer entries than output columns")
                 sB = fb.stride(0)
-            rc = lib.b200_approx_gemm_fbias(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out),
-                                            out.stride(0), Mrows, K, N, _ptr(fa), _ptr(fb), sB, _ptr(fr),
-                                            ctypes.byref(params), _ptr(ws), ws.numel(), _stream())
+            if act_quant is not None:
+                aq, alive = _act_quant_struct(act_quant, x.device)
+                rc = lib.b200_approx_gemm_fbias_fq(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out),
+                                                   out.stride(0), Mrows, K, N, _ptr(fa), _ptr(fb), sB, _ptr(fr),
+                                                   ctypes.byref(params), ctypes.byref(aq), _ptr(ws), ws.numel(), _stream())
+            else:
+                rc = lib.b200_approx_gemm_fbias(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out),
+                                                out.stride(0), Mrows, K, N, _ptr(fa), _ptr(fb), sB, _ptr(fr),
+                                                ctypes.byref(params), _ptr(ws), ws.numel(), _stream())
     if keep is not None:
         params.custom_table = None
     _lib.check(rc)
@@ -272,7 +293,7 @@ def exact_grouped_conv2d(x, weight, stride, padding, dilation, groups):
     return out
 
 
-def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, dilation, groups):
+def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, dilation, groups, act_quant=None):
     """im2col + group loop + approx_multiply of QCustomBNConv2dTorch.run_forward
     (approx/approx_calculation.py:846-906) in one C-ABI call.  Returns [B*Ho*Wo, C_out] fp32.
     Biases are the fake-quantizers' fp32 tensors (or None -> 2^(E-1)); read on the device."""
@@ -296,9 +317,15 @@ def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, 
     nbytes = lib.b200_approx_conv2d_workspace_bytes(ctypes.byref(g))
     ws = _workspace(x.device, nbytes) if nbytes else None
     with torch.cuda.device(x.device):
-        rc = lib.b200_approx_conv2d_fbias(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(fa), _ptr(fb), sB,
-                                          _ptr(fr), ctypes.byref(params), _ptr(ws), ws.numel() if ws is not None else 0,
-                                          _stream())
+        if act_quant is not None:
+            aq, alive = _act_quant_struct(act_quant, x.device)
+            rc = lib.b200_approx_conv2d_fbias_fq(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(fa), _ptr(fb), sB,
+                                                 _ptr(fr), ctypes.byref(params), ctypes.byref(aq), _ptr(ws),
+                                                 ws.numel() if ws is not None else 0, _stream())
+        else:
+            rc = lib.b200_approx_conv2d_fbias(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(fa), _ptr(fb), sB,
+                                              _ptr(fr), ctypes.byref(params), _ptr(ws), ws.numel() if ws is not None else 0,
+                                              _stream())
     _lib.check(rc)
     return out
 

@@ -132,6 +132,7 @@ class FPQuantizer(nn.Module):
         self.sign_bits = 1
         self.custom_bias = None
         self._range_version = 0          # bumped by set_quant_range: keys the fixed-weight cache of the hijacker
+        self._bias_version = -1          # range version custom_bias was computed for (fused input quantizer)
         if learn_maxval or learn_mantissa_bits:
             raise NotImplementedError("learned ranges belong to QAT, which the reference never wires up (SURVEY.md 2 row 16)")
 
@@ -140,6 +141,7 @@ class FPQuantizer(nn.Module):
             self.maxval = self.maxval.to(x_float.device)
         res, self.custom_bias = quantize_to_fp8_ste_MM(x_float, self.n_bits, self.maxval, self.mantissa_bits,
                                                        self.sign_bits)
+        self._bias_version = self._range_version     # custom_bias belongs to the current range
         return res
 
     @property
@@ -339,6 +341,7 @@ ACTIVATIONS = (nn.ReLU, nn.ReLU6, nn.Hardtanh, nn.Sigmoid, nn.Tanh, nn.GELU, nn.
 
 
 # ---- QuantizationHijacker (hijacker.py:32-151) -------------------------------------------------
+FUSE_INPUT_QUANT = True      # False: the activation quantizer always runs as its own pass, like the reference
 CACHE_FIXED_WEIGHTS = True   # False: re-quantize the weights in every forward, like the reference
 
 
@@ -363,7 +366,11 @@ class QuantizationHijacker(QuantizedModule):
     def _core(self, x, offsets=None):
         """hijacker.py:79-106 == quantized_folded_bn.py:34-58: calibrate twice / fixed once."""
         if self.quantize_input and self._quant_a:
-            x = self.activation_quantizer(x)
+            aq = self._fused_input_quant(x)
+            if aq is not None:
+                self.__dict__["_b200_act_quant"] = aq      # consumed by the one run_forward call below
+            else:
+                x = self.activation_quantizer(x)
         weight, bias = self.get_params()
         res = None
         if self.fix_ranges_flag is False or self.original_quantize_res:
@@ -378,6 +385,8 @@ class QuantizationHijacker(QuantizedModule):
             raise ValueError("quantize_after_mult_and_add or approx_flag is set but res_quantizer_flag is not set. "
                              "you need to set res_quantizer_flag to True if you want to use "
                              "quantize_after_mult_and_add or approx_flag")
+        if self.__dict__.pop("_b200_act_quant", None) is not None:
+            raise RuntimeError("fused input quantizer was requested but no kernel consumed it")
         return res
 
     def forward(self, x, offsets=None):
@@ -387,6 +396,26 @@ class QuantizationHijacker(QuantizedModule):
         if not self.quantize_input and self._quant_a:
             res = self.activation_quantizer(res)
         return res
+
+    def _fused_input_quant(self, x):
+        """with fixed ranges, in the approx configuration (exactly one run_forward per forward),
+        the input fake-quantizer is evaluated inside the GEMM's operand decode pass instead of as a separate pass
+        over the activations -- same element function, same bits.  Returns the descriptor, or None to quantize
+        the usual way (calibrating, other run modes, depthwise groups, per-channel ranges...)."""
+        if not FUSE_INPUT_QUANT or self.training or not self.fix_ranges_flag:
+            return None
+        if not (self.approx_flag and self.res_quantizer_flag) or self.original_quantize_res or \
+                self.quantize_after_mult_and_add:
+            return None
+        aqm = self.activation_quantizer
+        q = aqm.quantizer
+        if aqm.state != Qstates.fix_ranges or not isinstance(q, FPQuantizer) or q.custom_bias is None or \
+                q._bias_version != q._range_version or q.maxval.numel() != 1 or q.custom_bias.numel() != 1:
+            return None
+        fusable = getattr(self, "_fusable_input_quant", None)
+        if fusable is None or not x.is_cuda or x.dtype != torch.float32 or not fusable(x):
+            return None
+        return (q.maxval, q.custom_bias, float(q.mantissa_bits), q.n_bits, q.sign_bits)
 
     def get_params(self):
         """hijacker.py:117-123.  Once the ranges are fixed the quantized weights are a pure function of

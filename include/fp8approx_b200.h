@@ -179,6 +179,25 @@ int b200_fq_gemm_tc(const float *A, int64_t lda, const float *B, int64_t sb_k, i
                     int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *bias_dev,
                     void *workspace, size_t workspace_bytes, void *stream);
 
+/* Fused input fake-quantizer: the hijacker's `x = self.activation_quantizer(x)`
+ * (quantization/hijacker.py:82-88 -> fp8_quantizer.py:97-173) evaluated inside the operand decode pass of the
+ * GEMM / conv instead of as a separate pass over the activations.  A / x then hold the RAW activations;
+ * maxval_dev is the quantizer's per-tensor range, bias_dev the exponent bias the stand-alone quantizer derived
+ * from it (FPQuantizer.custom_bias; also what bA_dev must point at).  Results are bit-identical to
+ * quantizing first.  Not available for single-output-channel (depthwise) groups. */
+typedef struct b200_act_quant {
+    const float *maxval_dev; /* device [1] */
+    const float *bias_dev;   /* device [1] */
+    float mantissa_bits;
+    int32_t n_bits;
+    int32_t sign_bits;
+} b200_act_quant;
+int b200_approx_gemm_fbias_fq(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n, float *C,
+                              int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *bA_dev,
+                              const float *bB_dev, int64_t bB_stride, const float *bR_dev,
+                              const b200_approx_params *p, const b200_act_quant *aq, void *workspace,
+                              size_t workspace_bytes, void *stream);
+
 /* ---- A9: conv form, QCustomBNConv2dTorch.run_forward, approx/approx_calculation.py:822-917 -------- */
 typedef struct b200_conv_geom {
     int64_t batch;
@@ -208,6 +227,11 @@ int b200_approx_conv2d_fbias(const float *x, const float *w, float *out, const b
                              const float *bA_dev, const float *bB_dev, int64_t bB_stride,
                              const float *bR_dev, const b200_approx_params *p, void *workspace,
                              size_t workspace_bytes, void *stream);
+/* same, with the input fake-quantizer fused (b200_act_quant above); refuses depthwise groups */
+int b200_approx_conv2d_fbias_fq(const float *x, const float *w, float *out, const b200_conv_geom *g,
+                                const float *bA_dev, const float *bB_dev, int64_t bB_stride,
+                                const float *bR_dev, const b200_approx_params *p, const b200_act_quant *aq,
+                                void *workspace, size_t workspace_bytes, void *stream);
 /* quantize_after_mult_and_add conv (:787-795); groups with one output channel are refused
  * (B200_ERR_ARGUMENT): the reference computes those exactly (:810-811). */
 int b200_qamaa_conv2d(const float *x, const float *w, float *out, const b200_conv_geom *g,
