@@ -85,10 +85,18 @@ fp8_fakequant_channel_kernel(const float* __restrict__ x, float* __restrict__ y,
             const int64_t c = ((i << 2) / inner) % n_channels;
             const float mx = __ldg(maxval + c), b = __ldg(bias + c);
             float4 v = __ldcs(x4 + i);
-            v.x = fp8_ste_quant(v.x, mx, b, Mf, sign_bits);
-            v.y = fp8_ste_quant(v.y, mx, b, Mf, sign_bits);
-            v.z = fp8_ste_quant(v.z, mx, b, Mf, sign_bits);
-            v.w = fp8_ste_quant(v.w, mx, b, Mf, sign_bits);
+            if (fp8_ste_fast_ok(b)) {      // exponent-field form: no log2f, no division (pair_math.cuh)
+                const int bi = (int)b, Mi = (int)Mf;
+                v.x = fp8_ste_quant_fast(v.x, mx, bi, Mi, sign_bits);
+                v.y = fp8_ste_quant_fast(v.y, mx, bi, Mi, sign_bits);
+                v.z = fp8_ste_quant_fast(v.z, mx, bi, Mi, sign_bits);
+                v.w = fp8_ste_quant_fast(v.w, mx, bi, Mi, sign_bits);
+            } else {
+                v.x = fp8_ste_quant(v.x, mx, b, Mf, sign_bits);
+                v.y = fp8_ste_quant(v.y, mx, b, Mf, sign_bits);
+                v.z = fp8_ste_quant(v.z, mx, b, Mf, sign_bits);
+                v.w = fp8_ste_quant(v.w, mx, b, Mf, sign_bits);
+            }
             y4[i] = v;
         }
     } else {
