@@ -101,6 +101,7 @@ SIGNATURES = {
     "b200_set_autotune": (c_int, [c_int]),
     "b200_autotune_runs": (ctypes.c_uint64, []),
     "b200_int_peak_probe": (c_int, [c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
+    "b200_lds_peak_probe": (c_int, [c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
     "b200_profile_begin": (c_int, []),
     "b200_profile_end": (c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_int)]),
 }

@@ -18,7 +18,10 @@ from .quantization import BNFusedHijacker, QuantizationHijacker
 
 
 class _ApproxMixin:
-    """approx_multiply shared by the three operator classes (reference: :921-999, :749-814, :588-653)."""
+    """approx_multiply shared by the three operator classes (reference: :921-999, :749-814, :588-653).
+    Written against the attributes the reference's classes carry (custom_approx_params, approx_flag,
+    quantize_after_mult_and_add, res_quantizer) and called unbound, so that dropin.py can bind the very same
+    functions onto the reference's own classes."""
 
     def _params(self, quirk):
         cap = self.custom_approx_params or {}
@@ -31,7 +34,7 @@ class _ApproxMixin:
     def approx_multiply(self, x, y, x_bias, y_bias, res_bias):
         if y.shape[1] != 1:
             if self.approx_flag:
-                return ops.approx_matmul(x, y, x_bias, y_bias, res_bias, self._params(False),
+                return ops.approx_matmul(x, y, x_bias, y_bias, res_bias, _ApproxMixin._params(self, False),
                                          act_quant=self.__dict__.pop("_b200_act_quant", None))
             if self.quantize_after_mult_and_add:
                 q = self.res_quantizer.quantizer
@@ -41,7 +44,7 @@ class _ApproxMixin:
         # single output column (every depthwise group): int32-TENSOR biases in the reference
         # (:985-994) -> integer-pow numerics, no quantize_after_mult_and_add branch
         if self.approx_flag:
-            return ops.approx_matmul(x, y, x_bias, y_bias, res_bias, self._params(True))
+            return ops.approx_matmul(x, y, x_bias, y_bias, res_bias, _ApproxMixin._params(self, True))
         return ops.fq_matmul(x, y)
 
     def multiply(self, x, y):
@@ -93,7 +96,7 @@ class _ConvMixin(_ApproxMixin):
         Ng = Cout // self.groups
         if use_approx and self.approx_flag:
             out = ops.approx_conv2d(x, weight, self.get_acts_fp_bias(), self.get_weights_fp_bias(),
-                                    self.get_res_fp_bias(), self._params(Ng == 1), self.stride, self.padding,
+                                    self.get_res_fp_bias(), _ApproxMixin._params(self, Ng == 1), self.stride, self.padding,
                                     self.dilation, self.groups, act_quant=self.__dict__.pop("_b200_act_quant", None))
         elif use_approx and self.quantize_after_mult_and_add and Ng != 1:
             q = self.res_quantizer.quantizer

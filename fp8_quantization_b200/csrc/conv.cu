@@ -455,15 +455,14 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
         const bool small = (int64_t)d.Cg * g->H * g->W < ((int64_t)1 << 31) && (int64_t)g->kh * g->dil_h < 32768 &&
                            (int64_t)g->kw * g->dil_w < 32768;
         if (usable && small && smem <= 227 * 1024) {
-            static int sms = 0;
-            if (sms == 0) {
-                int dev = 0;
-                cudaGetDevice(&dev);
-                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-                if (sms <= 0) sms = 148;
-                B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_lut_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-                B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_lut_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            }
+            static PerDeviceOnce once;
+            int sms = 0;
+            if (int rc = once.get(&sms, []() -> int {
+                    B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_lut_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                    B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_lut_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                    return B200_OK;
+                }))
+                return rc;
             la.a = a.a; la.w = w; la.out = out; la.rows = d.rows; la.groups = g->groups; la.Kg = d.Kg; la.Cg = d.Cg;
             la.n_row_tiles = ceil_div(d.rows, 32); la.n_grp_tiles = (int)ceil_div(g->groups, 32);
             la.bias = a.bias; la.flag = reinterpret_cast<int*>(workspace);

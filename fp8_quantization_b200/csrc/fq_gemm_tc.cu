@@ -402,28 +402,25 @@ extern "C" int b200_fq_gemm_tc(const float* A, int64_t lda, const float* B, int6
     B200_LAUNCH_CHECK("to_bf16_kernel<B>");
 
     const int nkb = (int)(Kp / TC_BK);
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (sms <= 0) sms = 148;
-    }
+    static PerDeviceOnce once;
+    int sms = 0;
+    if (int rc = once.get(&sms, []() -> int {
+            B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<256, 4>::TOTAL));
+            B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<128, 4>::TOTAL));
+            return B200_OK;
+        }))
+        return rc;
     CUtensorMap mapA, mapB;
     if (int rc = make_map(enc, &mapA, Ah, Mrows, Kp, TC_BM)) return rc;
     if (N > 128) {
         constexpr int BN = 256, ST = 4;
         if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
-        static bool attr = false;
-        if (!attr) { B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN, ST>::TOTAL)); attr = true; }
         const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
         fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
             mapA, mapB, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
     } else {
         constexpr int BN = 128, ST = 4;
         if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
-        static bool attr = false;
-        if (!attr) { B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN, ST>::TOTAL)); attr = true; }
         const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
         fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
             mapA, mapB, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);

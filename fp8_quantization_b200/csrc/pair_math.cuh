@@ -162,11 +162,17 @@ __host__ __device__ inline float pair_generic(const PairCfg& c, const FmtParam& 
     return r;
 }
 
+// torch.min(torch.max(x, minval), maxval) (fp8_quantizer.py:120): torch's min / max PROPAGATE NaN, fminf / fmaxf do not
+__host__ __device__ __forceinline__ float clamp_nan(float x, float mn, float mx)
+{
+    return (x != x) ? x : fminf(fmaxf(x, mn), mx);
+}
+
 // quantize_to_fp8_ste_MM element body, quantization/quantizers/fp8_quantizer.py:119-154
 __host__ __device__ inline float fp8_ste_quant(float x, float maxval, float bias, float Mf, int sign_bits)
 {
     const float mn = (sign_bits == 1) ? -maxval : 0.0f;         // :119
-    const float xc = fminf(fmaxf(x, mn), maxval);               // :120
+    const float xc = clamp_nan(x, mn, maxval);                  // :120
     float ls = floorf(log2f(fabsf(xc)) + bias);                 // :144
     if (!(ls >= 1.0f)) ls = 1.0f;                               // clamp(min=1.0); -inf -> 1
     const float scale = pow2f_i((int)(ls - Mf - bias));         // :151 (integer-valued argument)
@@ -183,7 +189,7 @@ __host__ __device__ inline bool fp8_ste_fast_ok(float bias) { const int b = (int
 __device__ __forceinline__ float fp8_ste_quant_fast(float x, float maxval, int bias_i, int M_i, int sign_bits)
 {
     const float mn = (sign_bits == 1) ? -maxval : 0.0f;                 // :119
-    const float xc = fminf(fmaxf(x, mn), maxval);                       // :120
+    const float xc = clamp_nan(x, mn, maxval);                          // :120
     const int ef = (int)((__float_as_uint(xc) >> 23) & 0xFFu);          // floor(log2|xc|) + 127 (0: zero / denormal)
     int ls = ef - 127 + bias_i;                                         // :144
     if (ls < 1) ls = 1;                                                 // clamp(min=1)

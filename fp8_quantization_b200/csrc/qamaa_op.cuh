@@ -28,7 +28,7 @@ struct QamaaOp {
     __device__ __forceinline__ float quant(float x) const
     {
         if (!fast) return fp8_ste_quant(x, mx, bias, Mf, sign_bits);
-        const float xc = fminf(fmaxf(x, mn), mx);                          // :119-120
+        const float xc = clamp_nan(x, mn, mx);                             // :119-120
         const int ef = (int)((__float_as_uint(xc) >> 23) & 0xFFu);          // floor(log2|xc|) + 127 (0: zero / denormal)
         int ls = ef - 127 + bias_i;                                         // :144
         if (ls < 1) ls = 1;                                                 // clamp(min=1)

@@ -61,16 +61,28 @@ def calibrate(model, calib_batch, shard_calibration=False, group=None):
     return out
 
 
+_GATHER_BUFS = {}
+
+
 def gather_rows(local, n_total, group=None):
-    """all_gather of per-rank row blocks of unequal size (pads to the largest block)."""
+    """all_gather of per-rank row blocks (pads to the largest block when the shards are ragged).  The receive
+    buffer is allocated once per (shape, dtype, device) and reused: with equal shards the result is a VIEW of it
+    (valid until the next call with the same geometry) and no padding or concatenation pass runs."""
     rank, world = _world(group)
     if world == 1:
         return local
     sizes = [shard_range(n_total, r, world) for r in range(world)]
     width = max(hi - lo for lo, hi in sizes)
-    padded = local.new_zeros((width,) + tuple(local.shape[1:]))
+    tail = tuple(local.shape[1:])
+    key = (world, width, tail, local.dtype, local.device)
+    out = _GATHER_BUFS.get(key)
+    if out is None:
+        out = _GATHER_BUFS[key] = local.new_empty((world * width,) + tail)
+    if all(hi - lo == width for lo, hi in sizes):
+        dist.all_gather_into_tensor(out, local.contiguous(), group=group)
+        return out
+    padded = local.new_zeros((width,) + tail)
     padded[: local.shape[0]] = local
-    out = local.new_empty((world * width,) + tuple(local.shape[1:]))
     dist.all_gather_into_tensor(out, padded, group=group)
     return torch.cat([out[r * width: r * width + (hi - lo)] for r, (lo, hi) in enumerate(sizes)], dim=0)
 
@@ -80,10 +92,20 @@ class GraphedForward:
     shape.  A ResNet-18 forward at batch 8 is ~200 short launches: replaying them as one graph removes the
     host launch cost between kernels.  Only for models whose forward is launch-only on fixed ranges (no host
     reads): every operator of this package qualifies (device-side dispatch flags, biases read on the
-    device).  The captured kernels use the package's shared workspace; the runner keeps it alive."""
+    device).  The captured kernels use the package's shared workspace; the runner keeps it alive.
 
-    def __init__(self, model):
+    gather_total: with an initialised process group and equal shards, the ONE data-path collective -- the
+    all_gather of the logits -- is captured INSIDE the graph, after the forward, into a
+    pre-allocated buffer: a step is then a single graph launch.  The call returns the gathered [n_total, classes]
+    logits.  Falls back to an eager all_gather after the replay if the collective cannot be captured.
+
+    The returned tensor is a VIEW of the graph's static output: consume (or clone) it before the next call."""
+
+    def __init__(self, model, gather_total=None, group=None):
         self.model = model
+        self.gather_total = gather_total
+        self.group = group
+        self.collective_in_graph = None
         self._graphs = {}
 
     def __call__(self, x):
@@ -92,10 +114,14 @@ class GraphedForward:
         if ent is None:
             ent = self._capture(x)
             self._graphs[key] = ent
-        g, x_static, y_static, _ = ent
+        g, x_static, y_static, gathered, _ = ent
         x_static.copy_(x)
         g.replay()
-        return y_static.clone()
+        if gathered is not None:
+            return gathered
+        if self.gather_total is not None:
+            return gather_rows(y_static.float(), self.gather_total, self.group)
+        return y_static
 
     def _capture(self, x):
         from . import ops
@@ -104,31 +130,62 @@ class GraphedForward:
         side.wait_stream(torch.cuda.current_stream(x.device))
         with torch.cuda.stream(side), torch.inference_mode():   # warm-up: table builds, workspace growth
             self.model(x_static)
-            self.model(x_static)
+            y = self.model(x_static)
+            rank, world = _world(self.group)
+            want_gather = self.gather_total is not None and world > 1 and \
+                self.gather_total == world * x.shape[0] and y.dim() == 2
+            if want_gather:
+                gathered = y.new_empty((self.gather_total, y.shape[1]), dtype=torch.float32)
+                dist.all_gather_into_tensor(gathered, y.float().contiguous(), group=self.group)   # communicator warm-up
         torch.cuda.current_stream(x.device).wait_stream(side)
+        if want_gather:
+            try:
+                g = torch.cuda.CUDAGraph()
+                with torch.inference_mode(), torch.cuda.graph(g):
+                    y_static = self.model(x_static)
+                    dist.all_gather_into_tensor(gathered, y_static.float().contiguous(), group=self.group)
+                self.collective_in_graph = True
+                return g, x_static, y_static, gathered, dict(ops._WORKSPACES)
+            except Exception:    # the collective is not capturable on this stack: graph the forward only
+                self.collective_in_graph = False
+                torch.cuda.synchronize(x.device)
         g = torch.cuda.CUDAGraph()
         with torch.inference_mode(), torch.cuda.graph(g):
             y_static = self.model(x_static)
-        return g, x_static, y_static, dict(ops._WORKSPACES)
+        return g, x_static, y_static, None, dict(ops._WORKSPACES)
+
+
+_N_CLASSES = {}
 
 
 def evaluate(model, images, labels=None, group=None, forward=None):
     """Forward this rank's slice of `images`, gather the logits of the whole batch on every rank.
     Returns (logits [B, classes], metrics dict with top-1 / top-5 when labels are given).
-    `forward`: a callable used instead of `model` (e.g. a GraphedForward of it)."""
+    `forward`: a callable used instead of `model` (e.g. a GraphedForward of it; one built with
+    gather_total=len(images) does the gather inside its graph).
+    The class count an empty shard needs for the collective is agreed on ONCE per model (one all_reduce in the
+    first call), not every step; with equal shards the result is a view of a reused receive buffer."""
     rank, world = _world(group)
     n = images.shape[0]
     lo, hi = shard_range(n, rank, world)
+    fwd = forward or model
     with torch.inference_mode():
-        local = (forward or model)(images[lo:hi]) if hi > lo else images.new_zeros((0, 1))
-    if world > 1 and hi == lo:     # an empty shard still has to take part in the collective
-        cls = torch.zeros(1, dtype=torch.int64, device=images.device)
-        dist.all_reduce(cls, op=dist.ReduceOp.MAX, group=group)
-        local = images.new_zeros((0, int(cls.item())))
-    elif world > 1:
-        cls = torch.tensor([local.shape[1]], dtype=torch.int64, device=images.device)
-        dist.all_reduce(cls, op=dist.ReduceOp.MAX, group=group)
-    logits = gather_rows(local.float().contiguous(), n, group)
+        local = fwd(images[lo:hi]) if hi > lo else None
+    if isinstance(fwd, GraphedForward) and fwd.gather_total == n and world > 1 and local is not None \
+            and local.shape[0] == n:
+        logits = local                                   # gathered inside the graph (or right after the replay)
+    else:
+        if world > 1:
+            ncls = _N_CLASSES.get(id(model))
+            if ncls is None:
+                cls = torch.tensor([local.shape[1] if local is not None else 0], dtype=torch.int64).to(images.device)
+                dist.all_reduce(cls, op=dist.ReduceOp.MAX, group=group)
+                ncls = _N_CLASSES[id(model)] = int(cls.item())
+            if local is None:
+                local = images.new_zeros((0, ncls))
+        elif local is None:
+            local = images.new_zeros((0, 1))
+        logits = gather_rows(local.float().contiguous(), n, group)
     metrics = {}
     if labels is not None:
         top5 = logits.topk(min(5, logits.shape[1]), dim=1).indices

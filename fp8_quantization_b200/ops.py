@@ -31,8 +31,30 @@ def _ptr(t):
     return ctypes.c_void_p(t.data_ptr()) if t is not None else None
 
 
+_MBITS = {}
+
+
+def _mbits(t):
+    """mantissa_bits as a python float.  The reference keeps it as a one-element tensor that FPQuantizer.forward moves
+    to the input's device (fp8_quantizer.py:239-240): read it once per (storage, version), not once per call."""
+    if not torch.is_tensor(t):
+        return float(t)
+    if not t.is_cuda:
+        return float(t.item())
+    key = (t.data_ptr(), t._version, t.device)
+    v = _MBITS.get(key)
+    if v is None:
+        if len(_MBITS) > 4096:
+            _MBITS.clear()
+        v = _MBITS[key] = float(t.item())
+    return v
+
+
 def _workspace(device, nbytes):
-    key = (device.index if device.index is not None else torch.cuda.current_device())
+    """Scratch buffer of the calling (device, stream): it holds the device-side dispatch flags, the decoded operand
+    planes and the split-K partial sums of a call, so two streams running layers concurrently must not share one."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    key = (idx, torch.cuda.current_stream(idx).cuda_stream)
     ws = _WORKSPACES.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(int(nbytes * 1.25) + 1024, dtype=torch.uint8, device=device)
@@ -197,7 +219,7 @@ def qamaa_matmul(x, y, n_bits, maxval, mantissa_bits, sign_bits, out=None, x_bia
     mv = torch.as_tensor(maxval).to(device=x.device, dtype=torch.float32).reshape(-1)
     if mv.numel() != 1:
         raise ValueError("quantize_after_mult_and_add needs a per-tensor result range")
-    mbits = float(mantissa_bits.item()) if torch.is_tensor(mantissa_bits) else float(mantissa_bits)
+    mbits = _mbits(mantissa_bits)
     Mrows, K = x.shape
     N = y.shape[1]
     if out is None:
@@ -343,7 +365,7 @@ def qamaa_conv2d(x, weight, n_bits, maxval, mantissa_bits, sign_bits, stride, pa
     mv = torch.as_tensor(maxval).to(device=x.device, dtype=torch.float32).reshape(-1)
     if mv.numel() != 1:
         raise ValueError("quantize_after_mult_and_add needs a per-tensor result range")
-    mbits = float(mantissa_bits.item()) if torch.is_tensor(mantissa_bits) else float(mantissa_bits)
+    mbits = _mbits(mantissa_bits)
     with torch.cuda.device(x.device):
         if w_bias is not None:
             fb, sB = _bias_vec(w_bias, g.C_out, x.device, "weight fp bias")
@@ -366,7 +388,7 @@ def fp8_fakequant(x_float, n_bits, maxval, num_mantissa_bits, sign_bits):
     x = x_float if x_float.dtype == torch.float32 else x_float.float()
     x = x.contiguous()
     mv = maxval.to(device=x.device, dtype=torch.float32).reshape(-1).contiguous()
-    mbits = float(num_mantissa_bits.item()) if torch.is_tensor(num_mantissa_bits) else float(num_mantissa_bits)
+    mbits = _mbits(num_mantissa_bits)
     C = mv.numel()
     if C != 1:
         # maxval.view([-1] + [1]*(x.dim()-1)): per dim-0 channel (fp8_quantizer.py:114-115)
@@ -465,6 +487,14 @@ def bn_act(x, running_mean, running_var, gamma, beta, eps, act=0):
         _lib.check(lib.b200_bn_act(_ptr(x), x.stride(0), x.stride(1), sp, _ptr(y), B, C, H * W, _ptr(m), _ptr(v),
                                    _ptr(g), _ptr(b), float(eps), int(act), _stream()))
     return y
+
+
+def set_autotune(on):
+    """Measured (tile, split-K) choice of the table GEMM (b200_set_autotune).  OFF by default in the C ABI -- no
+    entry point ever synchronises with the host -- and switched on explicitly by the callers that want it (bench.py,
+    the eval harness, tools/): the first call per problem shape then times a few configurations (host syncs, never
+    inside CUDA-graph capture).  Every configuration computes identical bits.  Returns the previous setting."""
+    return bool(_lib.load().b200_set_autotune(1 if on else 0))
 
 
 def kernel_launches():

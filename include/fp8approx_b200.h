@@ -15,8 +15,8 @@
  *     the first call for a new (format, flags) combination, which builds and caches the pair
  *     table (one small cudaMalloc + one kernel + one 4-byte read-back);
  *   - the caller owns all buffers, including the scratch `workspace` whose size is returned by the
- *     matching *_workspace_bytes function (the table GEMM's first call per problem shape may also time
- *     candidate tile configurations, see b200_set_autotune);
+ *     matching *_workspace_bytes function (only if the caller opts in with b200_set_autotune(1) does the table
+ *     GEMM's first call per problem shape also time candidate tile configurations);
  *   - return value: B200_OK or a negative B200_ERR_* code; b200_last_error() gives the text.
  *     The Python host maps codes to the exceptions the reference raises at the same condition.
  */
@@ -71,11 +71,12 @@ uint64_t b200_kernel_launches(void);
 /* name of the kernel path the last b200_approx_gemm / conv call took: "lut", "generic", ... */
 const char *b200_last_path(void);
 
-/* Measured (tile, split-K) choice of the table GEMM: with autotune on (the default; B200_AUTOTUNE=0 in the
- * environment or b200_set_autotune(0) turns it off) the FIRST call for a new problem shape times the cost
- * model's best few configurations on the caller's operands and caches the winner -- a handful of extra runs
- * and host synchronisations, once per shape, never while the stream is being captured into a CUDA graph.
- * All configurations compute identical bits.  Returns the previous setting. */
+/* Measured (tile, split-K) choice of the table GEMM.  OFF by default: the cost model alone decides and no entry
+ * point ever synchronises with the host.  With autotune on (b200_set_autotune(1), or B200_AUTOTUNE=1 in the
+ * environment) the FIRST call for a new problem shape times the cost model's best few configurations on the
+ * caller's operands and caches the winner -- a handful of extra runs and host synchronisations, once per shape,
+ * never while the stream is being captured into a CUDA graph.  All configurations compute identical bits.
+ * Returns the previous setting. */
 int b200_set_autotune(int on);
 /* number of candidate configurations timed so far (0 = the cost model alone has decided everything) */
 uint64_t b200_autotune_runs(void);
@@ -256,6 +257,9 @@ int b200_bn_act(const float *x, int64_t sb, int64_t sc, int64_t sp, float *y, in
 /* ---- measurement tool: CUDA-core integer issue peak (roofline denominator) ------ */
 /* Synchronous.  tiops_out: IADD3/LOP3 lane-ops per second in Tiop/s over all SMs; ms_out may be NULL. */
 int b200_int_peak_probe(int iters, double *tiops_out, double *ms_out);
+/* Shared-memory lookup peak, the bound that binds the table GEMM (one LDS.U16 per MAC): conflict-free 16-bit
+ * shared-memory loads per second over all SMs, in T lookups/s.  Synchronous. */
+int b200_lds_peak_probe(int iters, double *tlookups_out, double *ms_out);
 /* Between begin and end, every table-GEMM launch is bracketed by CUDA events on its own stream;
  * end synchronises those events and returns their summed duration and the launch count. */
 int b200_profile_begin(void);

@@ -48,6 +48,12 @@ static float pow2f(int n)
 }
 
 /* torch integer pow `2 ** int_tensor` (int32): negative exponent -> 0, wraps above 2^31. */
+/* torch.min(torch.max(x, minval), maxval), fp8_quantizer.py:120: torch's min / max propagate NaN */
+static float clamp_nan(float x, float mn, float mx)
+{
+    return (x != x) ? x : fminf(fmaxf(x, mn), mx);
+}
+
 static int32_t ipow2(int n)
 {
     if (n < 0) return 0;
@@ -294,7 +300,7 @@ void orc_fp8_fakequant(const float *x, float *y, int64_t n, const float *maxval,
         int64_t c = (n_channels == 1) ? 0 : (i / inner) % n_channels;
         float mx = maxval[c], bias = bias_out[c];
         float mn = (sign_bits == 1) ? -mx : 0.0f;                 /* :119 */
-        float xc = fminf(fmaxf(x[i], mn), mx);                     /* :120 */
+        float xc = clamp_nan(x[i], mn, mx);                        /* :120 */
         float ls = floorf(log2f(fabsf(xc)) + bias);                /* :144 */
         if (!(ls >= 1.0f)) ls = 1.0f;                              /* clamp(min=1); -inf -> 1 */
         float scale = exp2f(ls - M - bias);                        /* :151 */
@@ -322,7 +328,7 @@ void orc_qamaa_matmul(const float *A, int64_t sa0, int64_t sa1,
             double accd = 0.0;
             for (int64_t k = 0; k < K; ++k) {
                 float g = A[m * sa0 + k * sa1] * B[k * sb0 + n * sb1];
-                float xc = fminf(fmaxf(g, mn), maxval);
+                float xc = clamp_nan(g, mn, maxval);
                 float ls = floorf(log2f(fabsf(xc)) + bias);
                 if (!(ls >= 1.0f)) ls = 1.0f;
                 float scale = exp2f(ls - M - bias);
@@ -331,7 +337,7 @@ void orc_qamaa_matmul(const float *A, int64_t sa0, int64_t sa1,
                 accd += (double)q;
             }
             float s = sum_mode ? (float)accd : accf;
-            float xc = fminf(fmaxf(s, mn), maxval);
+            float xc = clamp_nan(s, mn, maxval);
             float ls = floorf(log2f(fabsf(xc)) + bias);
             if (!(ls >= 1.0f)) ls = 1.0f;
             float scale = exp2f(ls - M - bias);
@@ -421,6 +427,16 @@ void orc_im2col(const float *x, int B, int C, int H, int W, int kh, int kw, int 
                             row[((int64_t)c * kh + ky) * kw + kx] = v;
                         }
             }
+}
+
+/* torchrun exports OMP_NUM_THREADS=1 to its workers: the timed CPU baseline sets its thread count explicitly */
+void orc_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
 }
 
 int orc_num_threads(void)

@@ -233,3 +233,9 @@ def im2col(x, kh, kw, stride, padding, dilation):
 
 def num_threads():
     return lib().orc_num_threads()
+
+
+def set_num_threads(n):
+    """OpenMP thread count of the port, whatever OMP_NUM_THREADS says (torchrun exports 1 to its workers)."""
+    lib().orc_set_num_threads(int(n))
+    return num_threads()

@@ -56,6 +56,9 @@ MODEL_CASES = [
     ("mobilenetv2_64", "mobilenetv2", 64, 2, (3, 4)),
     # BASELINE.json configs[0]: ResNet-18, approx_v9 mant_width=3 expo_width=4, batch 8 synthetic 224x224
     ("resnet18_224_b8", "resnet18", 224, 8, (4, 3)),
+    # BASELINE.json configs[2] at its real resolution: MobileNetV2 224x224 (112x112 / 56x56 depthwise tiles, the
+    # split-K choices of the 7x7 tail), E4M3 -- the format tools/model_bench.py times
+    ("mobilenetv2_224_b4", "mobilenetv2", 224, 4, (4, 3)),
 ]
 
 # hot-path layers whose (input, output) the golden file records in both passes
@@ -63,13 +66,14 @@ TAPPED_LAYERS = {
     "resnet18_64": ["features.0", "features.2.0.features.0", "features.3.0.downsample.0", "features.4.1.features.1",
                     "features.5.1.features.1", "fc"],
     "resnet18_224_b8": ["features.5.1.features.1", "fc"],
+    "mobilenetv2_224_b4": [],      # probes of all 53 hot-path layers instead (full taps would be tens of MB)
     "mobilenetv2_64": ["features.0.0", "features.1.conv.0", "features.2.conv.0", "features.2.conv.1",
                        "features.4.conv.2", "features.17.conv.1", "features.18.0", "classifier.1"],
 }
 
 # cases for which the golden file also holds, for EVERY hot-path layer, a fixed sample of the layer output
 # in the end-to-end pass (keys f"{case}_{layer}_p{cal|eval}")
-PROBED_CASES = ["resnet18_224_b8"]
+PROBED_CASES = ["resnet18_224_b8", "mobilenetv2_224_b4"]
 PROBE_N = 4096
 
 

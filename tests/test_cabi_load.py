@@ -63,3 +63,13 @@ def test_param_struct_layout():
     assert (p.expo_width, p.mant_width, p.dnsmp_factor, p.withComp, p.golden_clip_OF) == (3, 4, 5, 0, 1)
     assert ctypes.sizeof(pkg._lib.ApproxParams) == 32
     assert pkg._lib.ApproxParams.custom_table.offset == 24
+
+
+def test_integration_doc_quotes_the_dropin_file():
+    """INTEGRATION.md section B must show the file that tests/test_gpu_dropin.py installs on the reference classes."""
+    import re
+    root = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    m = re.search(r"<!-- dropin.py begin -->\n```python\n(.*?)```\n<!-- dropin.py end -->", doc, re.S)
+    assert m, "INTEGRATION.md: dropin.py block not found"
+    assert m.group(1) == open(os.path.join(root, "fp8_quantization_b200", "dropin.py")).read()

@@ -1,0 +1,140 @@
+"""The real drop-in (SURVEY.md 8(b) "Python seam"): the UNMODIFIED reference classes,
+imported from oracle/_ref (tools/install_ref.sh; /root/reference in the build container), with
+fp8_quantization_b200.dropin.install() rebinding approx_multiply / multiply / run_forward /
+quantize_to_fp8_ste_MM on them -- the same file INTEGRATION.md quotes.
+
+Checked, per layer fixture of tests/golden/layers.npz (16 cases: Linear / BN-conv; groups 1, grouped, depthwise;
+approx, quantize_after_mult_and_add, plain; E4M3 / E3M4 / E2M5), through the reference's own protocol
+quantized() -> estimate_ranges() -> forward -> fix_ranges() -> forward:
+  * the three fp biases equal the CPU reference run's (integer fields: exact);
+  * both outputs within 1e-6 of the output scale of the CPU reference run (layers.npz), for both patch levels;
+  * and of the UNPATCHED reference run on this same GPU (torch eager, its per-column Python loop).
+"""
+import contextlib
+import io
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+from torch import nn
+
+from oracle import ref_shim
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def ref():
+    if not ref_shim.available():
+        pytest.skip("reference not present (run tools/install_ref.sh in the build container)")
+    assert torch.cuda.is_available()
+    return ref_shim.load_operators()
+
+
+def _qparams(meta):
+    from quantization.quantizers import FPQuantizer
+    from quantization.range_estimators import RangeEstimators
+    M = meta["ap"]["mant_width"]
+    return dict(method=FPQuantizer, act_method=FPQuantizer, n_bits=8, n_bits_act=8, per_channel_weights=True,
+                weight_range_method=RangeEstimators.current_minmax.cls,
+                act_range_method=RangeEstimators.allminmax.cls, quantize_input=True,
+                fp8_kwargs=dict(mantissa_bits=M, set_maxval=True), custom_approx_params=dict(meta["ap"]),
+                run_method=dict(meta["rm"]))
+
+
+def _build(ref, z, i, meta):
+    if meta["kind"] == "linear":
+        layer = ref.QCustomLinearTorch(**meta["args"], bias=True, **_qparams(meta))
+        with torch.no_grad():
+            layer.weight.copy_(torch.from_numpy(z[f"w{i}"]))
+            layer.bias.copy_(torch.from_numpy(z[f"b{i}"]))
+    else:
+        act = {"relu": nn.ReLU(), "relu6": nn.ReLU6(), None: None}[meta["act"]]
+        layer = ref.QCustomBNConv2dTorch(**meta["args"], activation=act, **_qparams(meta))
+        with torch.no_grad():
+            layer.weight.copy_(torch.from_numpy(z[f"w{i}"]))
+            for name in ("running_mean", "running_var", "gamma", "beta"):
+                getattr(layer, name).copy_(torch.from_numpy(z[f"{name}{i}"]))
+    return layer.cuda().eval()
+
+
+def _protocol(layer, x_cal, x_eval):
+    with torch.inference_mode(), contextlib.redirect_stdout(io.StringIO()):   # the Linear variant prints tensors
+        layer.quantized()
+        layer.estimate_ranges()
+        y_cal = layer(x_cal)
+        layer.fix_ranges()
+        y_eval = layer(x_eval)
+    rb = layer.get_res_fp_bias()
+    biases = (layer.get_acts_fp_bias().reshape(-1).cpu().numpy(), layer.get_weights_fp_bias().reshape(-1).cpu().numpy(),
+              rb.reshape(-1).cpu().numpy() if rb is not None else np.zeros(0, np.float32))
+    return y_cal.contiguous().cpu().numpy(), y_eval.contiguous().cpu().numpy(), biases
+
+
+@pytest.mark.parametrize("level", ["approx_multiply", "run_forward"])
+def test_reference_classes_with_dropin(ref, level):
+    import fp8_quantization_b200.dropin as b200
+    from fp8_quantization_b200 import ops
+    z = np.load(os.path.join(GOLD, "layers.npz"))
+    metas = json.loads(bytes(z["meta"]).decode())
+    bad = []
+    for i, meta in enumerate(metas):
+        x_cal, x_eval = torch.from_numpy(z[f"xcal{i}"]).cuda(), torch.from_numpy(z[f"xeval{i}"]).cuda()
+        eager = _protocol(_build(ref, z, i, meta), x_cal, x_eval)         # unpatched reference, GPU eager
+        b200.install(level=level)
+        try:
+            l0 = ops.kernel_launches()
+            ours = _protocol(_build(ref, z, i, meta), x_cal, x_eval)      # same classes, our kernels underneath
+            assert ops.kernel_launches() > l0, "the patched classes launched none of our kernels"
+        finally:
+            b200.uninstall()
+        gold = (z[f"ycal{i}"], z[f"yeval{i}"], (z[f"bias_a{i}"], z[f"bias_w{i}"], z[f"bias_r{i}"]))
+        for who, want in (("cpu-reference", gold), ("gpu-eager-reference", eager)):
+            if not all(np.array_equal(a, b) for a, b in zip(ours[2], want[2])):
+                bad.append((i, who, "fp biases", ours[2], want[2]))
+                continue
+            for name, got, w in (("cal", ours[0], want[0]), ("eval", ours[1], want[1])):
+                tol = 1e-6 * max(float(np.abs(w).max()), 1e-30)
+                err = float(np.abs(got.astype(np.float64) - w).max()) if got.shape == w.shape else float("inf")
+                if err > tol:
+                    bad.append((i, who, name, meta["kind"], meta["args"], meta["rm"], "max err", err, "tol", tol))
+    assert not bad, bad
+
+
+def test_uninstall_restores_the_reference(ref):
+    import fp8_quantization_b200.dropin as b200
+    before = (ref.QCustomLinearTorch.approx_multiply, ref.QCustomBNConv2dTorch.run_forward)
+    b200.install()
+    assert ref.QCustomLinearTorch.approx_multiply is not before[0]
+    b200.uninstall()
+    assert (ref.QCustomLinearTorch.approx_multiply, ref.QCustomBNConv2dTorch.run_forward) == before
+
+
+@pytest.mark.parametrize("K,N", [(768, 768), (768, 3072), (3072, 768)])
+def test_vit_shaped_linear_vs_gpu_eager_reference(ref, K, N):
+    """BASELINE configs[3] shapes (ViT-B/16, 16 images: 3152 token rows, E3M4): the patched reference
+    QCustomLinearTorch against the unpatched one on this GPU, on a 16-column sample (the reference's per-column loop
+    makes columns independent).  The summation is exact in this regime (quant_btw_mult_accu): bit equality."""
+    import fp8_quantization_b200.dropin as b200
+    import vit_cases as vc
+    x, w, b = vc.operands(K, N)
+    meta = dict(ap=vc.approx_params(), rm=vc.RUN_APPROX)
+    outs = []
+    for patched in (False, True):
+        layer = ref.QCustomLinearTorch(K, vc.COLS, bias=True, **_qparams(meta))
+        with torch.no_grad():
+            layer.weight.copy_(w[:vc.COLS])
+            layer.bias.copy_(b[:vc.COLS])
+        layer.cuda().eval()
+        if patched:
+            b200.install()
+        try:
+            outs.append(_protocol(layer, x.cuda(), (x * 0.9).cuda()))
+        finally:
+            b200.uninstall()
+    for a, c in zip(outs[0][2], outs[1][2]):
+        assert np.array_equal(a, c)
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])

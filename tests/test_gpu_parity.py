@@ -207,6 +207,18 @@ def test_fakequant_fixture(fq):
         assert same_bits(y.cpu().numpy(), z[f"y{i}"]), i
 
 
+def test_fakequant_special_values(fq):
+    """NaN propagates (torch.min / torch.max do), +-Inf clamps to +-maxval, fp32 sub-normals, signed zeros: outputs of
+    the unmodified reference (tests/golden/make_fakequant_special.py), stand-alone kernel and fused GEMM prologue."""
+    z = np.load(os.path.join(GOLD, "fakequant_special.npz"))
+    for i, (mbits, sbits) in enumerate(z["cfgs"]):
+        y, b = fq.quantize_to_fp8_ste_MM(dev(z["x"]), 8, dev(z[f"mv{i}"]), torch.tensor([float(mbits)]), int(sbits))
+        assert np.array_equal(b.cpu().numpy().reshape(-1), z[f"b{i}"].reshape(-1)), i
+        got, want = y.cpu().numpy(), z[f"y{i}"]
+        ok = (got.view(np.uint32) == want.view(np.uint32)) | ((got == 0) & (want == 0)) | (np.isnan(got) & np.isnan(want))
+        assert ok.all(), (i, got, want)
+
+
 @pytest.mark.parametrize("mbits", [2, 3, 4, 5])
 def test_fakequant_large_vs_oracle(fq, mbits):
     """16 M elements (> L2 is not needed for parity): per tensor and per channel, values straddling

@@ -92,6 +92,21 @@ def test_fakequant_fixture():
         assert same_bits(y, z[f"y{i}"]), i
 
 
+def same_bits_or_nan(a, b):
+    a, b = np.asarray(a, np.float32), np.asarray(b, np.float32)
+    return bool(np.all((a.view(np.uint32) == b.view(np.uint32)) | ((a == 0) & (b == 0)) | (np.isnan(a) & np.isnan(b))))
+
+
+def test_fakequant_special_values():
+    """NaN propagates (torch.min / torch.max), +-Inf clamps to +-maxval, sub-normals and signed zeros: reference outputs."""
+    z = np.load(os.path.join(GOLD, "fakequant_special.npz"))
+    for i, (mbits, sbits) in enumerate(z["cfgs"]):
+        y, b = orc.fp8_fakequant(z["x"], z[f"mv{i}"], 8, float(mbits), int(sbits))
+        assert np.array_equal(b.reshape(-1), z[f"b{i}"].reshape(-1)), i
+        assert same_bits_or_nan(y, z[f"y{i}"]), (i, y, z[f"y{i}"])
+    assert np.isnan(z["y0"]).sum() > 0
+
+
 def test_codec_fixture():
     z = np.load(os.path.join(GOLD, "codec.npz"))
     for i, (E, M, bias, clip) in enumerate(z["cfgs"]):

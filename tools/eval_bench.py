@@ -37,7 +37,8 @@ def main():
     import torch.distributed as dist
     import model_bench as mb
     import model_cases as mc
-    from fp8_quantization_b200 import eval_harness as eh
+    from fp8_quantization_b200 import eval_harness as eh, ops
+    ops.set_autotune(True)
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -56,7 +57,7 @@ def main():
     x_cal = mk(a.per_gpu_batch, 1).to(dev)          # replicated calibration batch
     x = mk(n, 2).to(dev)                            # every rank holds the batch, evaluates its slice
     eh.calibrate(model, x_cal)
-    fwd = eh.GraphedForward(model) if a.graph else None
+    fwd = eh.GraphedForward(model, gather_total=n if world > 1 else None) if a.graph else None
     for _ in range(max(a.warmup, 3)):
         logits, _ = eh.evaluate(model, x, forward=fwd)
     if world > 1:
@@ -77,13 +78,13 @@ def main():
     if a.check and rank == 0 and world > 1:
         with torch.inference_mode():
             whole = model(x)
-        same = bool(torch.equal(whole, logits))
+        same = bool(torch.equal(whole, logits))      # `logits`: the last timed step's gathered result
     if rank == 0:
         print(json.dumps({"metric": f"{a.model}_approx_sim_images_per_s", "value": round(n / ms_step * 1e3, 1),
                           "unit": "images/s", "n_gpus": world, "steps": a.steps, "ms_per_step": round(ms_step, 3),
                           "scaling": "weak", "cuda_graph": bool(a.graph), "per_gpu_batch": a.per_gpu_batch, "global_batch": n,
                           "format": f"E{7 - M}M{M}", "approx_gmacs": round(n * mb.MACS_PER_IMAGE[a.model] / ms_step / 1e6, 1),
-                          "collective": "one all_gather of logits per step" if world > 1 else None,
+                          "collective": ("one all_gather of logits per step" + (", captured in the CUDA graph" if fwd is not None and fwd.collective_in_graph else "")) if world > 1 else None,
                           "sharded_equals_single_gpu": same, "logits_checksum": float(logits.double().sum())}),
               flush=True)
     if world > 1:
