@@ -178,7 +178,11 @@ def time_reference_layer(args, device):
     layer = reference_layer(ac, M, ncols, w, b, device)
     x = x.to(device)
     sync = torch.cuda.synchronize if device != "cpu" else (lambda: None)
-    with torch.inference_mode(), contextlib.redirect_stdout(io.StringIO()):   # the Linear variant prints whole tensors
+    # On the GPU the reference runs under a default-device context: it builds scalar tensors without a device
+    # (approx_matmul_whole_v9.py:275), which torch 2.4 -- its pinned version -- let mix with CUDA operands and
+    # torch 2.11 does not.  The reference's files stay unmodified.
+    ctx = torch.device(device) if device != "cpu" else contextlib.nullcontext()
+    with ctx, torch.inference_mode(), contextlib.redirect_stdout(io.StringIO()):   # the Linear variant prints whole tensors
         layer.quantized()
         layer.estimate_ranges()
         layer(x)

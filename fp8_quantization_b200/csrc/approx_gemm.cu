@@ -89,6 +89,44 @@ __global__ void lut_build_kernel(LutGeom g, const signed char* __restrict__ T, i
     lut[idx] = out;
 }
 
+// Pair table of the v5 integer-add GEMM (ofuf_mode 1; lut.cuh make_lut_geom_v5): the addend is
+// sign(a) * sign(b) * dec(t) with t = (eA + eB - c) * 2^M + mA + mB + comp[mA, mB] followed by the adder's
+// overflow / underflow simulation (approx_matmul_whole_v5.py:155-182) -- a function of (eA + eB - c, mA, mB), i.e.
+// the same additive index structure as the approx_v9 table with the CODE exponents in place of floor(log2).
+// Cells are in units of u (result bias 1 - M makes u == 1), bf16; every cell has <= M + 1 significant bits.
+__global__ void lut_build_v5_kernel(LutGeom g, const signed char* __restrict__ T, int sim, int of_opt, int uf_opt,
+                                    uint16_t* __restrict__ lut, LutFlags* __restrict__ flags)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= g.total_entries) return;
+    uint16_t out = 0;
+    if (idx < g.zeroA_off) {
+        const int M = g.M, ms = 1 << M, mod = 1 << (g.E + M);
+        const int mB = idx & (ms - 1);
+        const int row = idx >> M;
+        const int r = row % g.NT;
+        const int q = row / g.NT;
+        const int mA = q & (ms - 1);
+        const int sa = (q >> M) & 1;
+        if (r > g.RA) {
+            const int esum = r - (g.v5_lo + g.RA + 1);               // eA + eB - (bA + bB - bR)
+            int t = esum * ms + mA + mB + (T ? (int)T[mA * ms + mB] : 0);
+            if (sim) {
+                const bool of = t > mod - 1, uf = t < 0;
+                t = ((t % mod) + mod) % mod;
+                if (of_opt && of) t = mod - 1;
+                if (uf_opt && uf) t = t % ms;
+            }
+            const FmtParam pR = make_param(g.E, M, 1 - M, false);   // unit space
+            const float v = fpany_decode(pR, sa ? -1.0f : 1.0f, t >> M, t & (ms - 1));
+            const uint32_t bits = __float_as_uint(v);
+            if ((bits & 0xFFFFu) || !(fabsf(v) < INFINITY)) atomicAdd(&flags->unrepresentable, 1);
+            out = (uint16_t)(bits >> 16);
+        }
+    }
+    lut[idx] = out;
+}
+
 // Pair table of the quantize_after_mult_and_add mode (approx_calculation.py:959-967): the addend is
 // Q(a * b) with Q = quantize_to_fp8_ste_MM(., n_bits, maxval, mantissa_bits, sign_bits); for operands on
 // the FP8 grid that is sb * u * F(sa, t, mA, mB) with the SAME index geometry as the approx table
@@ -191,6 +229,53 @@ __device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int b
     return (mult << 16) | boff;
 }
 
+// v5 flavour (ofuf_mode 1): operands enter through their CODES (float_to_fpany_absint with clip_OF, v5 :246-281).
+// On-grid values only -- exact mantissa, not above the top binade -- anything else raises `off` and the arithmetic
+// kernel (which rounds and clips like the reference) recomputes.  A zero is the ordinary code (0, 0) with sign +1
+// (sign(v) = v < 0 ? -1 : 1, v5 :106-107): its product is NOT zero in v5.
+__device__ __forceinline__ bool v5_code(float v, int M, int E, int bias, int& e, int& m, uint32_t& neg)
+{
+    const uint32_t bits = __float_as_uint(v);
+    const uint32_t mag = bits & 0x7FFFFFFFu;
+    e = 0; m = 0; neg = 0;
+    if (mag == 0) return true;
+    neg = bits >> 31;
+    const int ef = (int)(mag >> 23);
+    if (ef == 0 || ef == 255) return false;
+    const int L = ef - 127, Lmin = 1 - bias;
+    const uint32_t frac = mag & 0x7FFFFFu;
+    if (L >= Lmin) {
+        e = L + bias;
+        m = (int)(frac >> (23 - M));
+        return (frac & ((1u << (23 - M)) - 1u)) == 0 && e <= (1 << E) - 1;
+    }
+    const int sh = Lmin - L;                       // sub-normal: |v| = m * 2^(1 - bias - M)
+    if (sh > M) return false;
+    const uint32_t sig = (1u << 23) | frac;
+    m = (int)(sig >> (23 - M + sh));
+    return (sig & ((1u << (23 - M + sh)) - 1u)) == 0;
+}
+
+__device__ __forceinline__ uint32_t predecode_a_v5(const LutGeom& g, float v, int bA, int& off)
+{
+    int e, m;
+    uint32_t neg;
+    if (!v5_code(v, g.M, g.E, bA, e, m, neg)) { off = 1; return 2u * (uint32_t)g.zeroA_off; }
+    return 2u * (uint32_t)(g.row_entries * (e + g.NT * (m + (int)(neg << g.M))));
+}
+
+__device__ __forceinline__ uint32_t predecode_b_v5(const LutGeom& g, float v, int bA, int bB, int bR, int& off)
+{
+    int e, m;
+    uint32_t neg;
+    const uint32_t pad = kBf16One << 16;           // row 0: all zero against every A row
+    if (!v5_code(v, g.M, g.E, bB, e, m, neg)) { off = 1; return pad; }
+    const int tB = e - (bA + bB - bR);
+    if (tB < -g.v5_lo || tB > (1 << g.E) + 3) { off = 1; return pad; }
+    const uint32_t boff = 2u * ((uint32_t)m + (uint32_t)(g.row_entries * (tB + g.v5_lo + g.RA + 1)));
+    return ((neg ? kBf16MinusOne : kBf16One) << 16) | boff;
+}
+
 // 32x32 tile transpose: reads along k (SRC_K_CONTIG) or along rows, writes along rows.
 template <bool IS_B, bool SRC_K_CONTIG>
 __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom g)
@@ -208,7 +293,8 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
             uint32_t w = IS_B ? (g.sidx ? 0u : (kBf16One << 16)) : 2u * (uint32_t)g.zeroA_off;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
-                w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax) : predecode_a(g, v, bA, off, tmax);
+                w = IS_B ? (g.v5 ? predecode_b_v5(g, v, bA, a.bias.B(r), bR, off) : predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax))
+                         : (g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax));
                 if (!IS_B) zeros += (v == 0.0f);
             }
             tile[tx][ty + i * 8] = w;   // [k][r]
@@ -226,7 +312,8 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
             uint32_t w = IS_B ? (g.sidx ? 0u : (kBf16One << 16)) : 2u * (uint32_t)g.zeroA_off;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
-                w = IS_B ? predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax) : predecode_a(g, v, bA, off, tmax);
+                w = IS_B ? (g.v5 ? predecode_b_v5(g, v, bA, a.bias.B(r), bR, off) : predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax))
+                         : (g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax));
                 if (!IS_B) zeros += (v == 0.0f);
             }
             if (k < a.Kpad && r < a.Rpad) a.dst[k * a.Rpad + r] = w;
@@ -287,7 +374,7 @@ __global__ void __launch_bounds__(PC_ROWS) predecode_conv_kernel(PredecodeArgs a
             const int h = h0 + ky * s.dh, wi = w0 + kx * s.dw;
             float v = 0.0f;                                              // F.pad zeros (:727)
             if (h >= 0 && h < s.H && wi >= 0 && wi < s.W) v = s.fq(__ldg(base + ((int64_t)c * s.H + h) * s.W + wi));
-            w = predecode_a(g, v, bA, off, tmax);
+            w = g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax);
             zeros += (v == 0.0f);
         }
         dst[(int64_t)kk * a.Rpad] = w;
@@ -939,7 +1026,7 @@ struct ApproxPairOp {
     __device__ __forceinline__ Col column(int64_t n) const { return make_param(cfg.E, cfg.M, bias.B(n), cfg.quirk); }
     __device__ __forceinline__ float pair(float a, float b, const Col& pB) const
     {
-        return T ? pair_generic(cfg, pA, pB, pR, T, a, b) : pair_generic<signed char>(cfg, pA, pB, pR, nullptr, a, b);
+        return T ? pair_any(cfg, pA, pB, pR, T, a, b) : pair_any<signed char>(cfg, pA, pB, pR, nullptr, a, b);
     }
     __device__ __forceinline__ float finish(float acc, const Col&) const { return acc; }
 };
@@ -979,19 +1066,27 @@ int device_table(const signed char* host, int M, const signed char** dev_out)
 }
 
 // Builds (once per configuration and device) the pair table of lut.cuh.  First use synchronises.
+struct V5Flags {
+    int on, sim, of_opt, uf_opt;
+};
+
 static int build_lut(int E, int M, const signed char* dev_table, int with_approx, int clip_OF, bool sidx, bool quirk,
-                     LutEntry* e)
+                     LutEntry* e, const V5Flags* v5 = nullptr)
 {
-    e->geom = make_lut_geom(E, M, sidx);
+    e->geom = (v5 && v5->on) ? make_lut_geom_v5(E, M) : make_lut_geom(E, M, sidx);
     e->lut_bytes = (int)round_up((int64_t)e->geom.total_entries * 2, 16);
     LutFlags* d_flags = nullptr;
     B200_CUDA_TRY(cudaMalloc(&e->d_lut, e->lut_bytes));
     B200_CUDA_TRY(cudaMalloc(&d_flags, sizeof(LutFlags)));
     B200_CUDA_TRY(cudaMemset(e->d_lut, 0, e->lut_bytes));
     B200_CUDA_TRY(cudaMemset(d_flags, 0, sizeof(LutFlags)));
-    lut_build_kernel<<<(int)ceil_div(e->geom.total_entries, 256), 256>>>(e->geom, dev_table, dev_table != nullptr,
-                                                                        with_approx, clip_OF, quirk ? 1 : 0, e->d_lut,
-                                                                        d_flags);
+    if (v5 && v5->on)
+        lut_build_v5_kernel<<<(int)ceil_div(e->geom.total_entries, 256), 256>>>(e->geom, dev_table, v5->sim, v5->of_opt,
+                                                                               v5->uf_opt, e->d_lut, d_flags);
+    else
+        lut_build_kernel<<<(int)ceil_div(e->geom.total_entries, 256), 256>>>(e->geom, dev_table, dev_table != nullptr,
+                                                                            with_approx, clip_OF, quirk ? 1 : 0, e->d_lut,
+                                                                            d_flags);
     B200_LAUNCH_CHECK("lut_build_kernel");
     B200_CUDA_TRY(cudaMemcpy(&e->flags, d_flags, sizeof(LutFlags), cudaMemcpyDeviceToHost));
     cudaFree(d_flags);
@@ -999,17 +1094,19 @@ static int build_lut(int E, int M, const signed char* dev_table, int with_approx
 }
 
 static int get_lut(int E, int M, const signed char* host_table, const signed char* dev_table, int with_approx,
-                   int clip_OF, const LutEntry** out, bool quirk = false)
+                   int clip_OF, const LutEntry** out, bool quirk = false, const V5Flags* v5 = nullptr)
 {
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lk(g_cache_mu);
-    auto key = std::make_tuple(dev, E, M, (const void*)host_table, with_approx, clip_OF + (quirk ? 2 : 0));
+    const bool is_v5 = v5 && v5->on;
+    const int mode = is_v5 ? (4 + 8 * v5->sim + 16 * v5->of_opt + 32 * v5->uf_opt) : (clip_OF + (quirk ? 2 : 0));
+    auto key = std::make_tuple(dev, E, M, (const void*)host_table, is_v5 ? 0 : with_approx, mode);
     auto it = g_luts.find(key);
     if (it == g_luts.end()) {
         LutEntry e;
-        if (int rc = build_lut(E, M, dev_table, with_approx, clip_OF, quirk, quirk, &e)) return rc;
-        if (!quirk && e.flags.sign_quirk && !e.flags.unrepresentable) {
+        if (int rc = build_lut(E, M, dev_table, with_approx, clip_OF, quirk, quirk, &e, v5)) return rc;
+        if (!is_v5 && !quirk && e.flags.sign_quirk && !e.flags.unrepresentable) {
             // not odd in the operand signs: rebuild with both signs in the index (lut.cuh)
             cudaFree(e.d_lut);
             e = LutEntry();
@@ -1124,7 +1221,8 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     pa.tmax = partial ? flag + 4 : nullptr;
     pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
     pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
-    pa.zero_count = reinterpret_cast<unsigned long long*>(flag + 2);
+    // v5 flavour: a zero operand is an ordinary code (its product is not zero), so there is nothing to skip
+    pa.zero_count = geom.v5 ? nullptr : reinterpret_cast<unsigned long long*>(flag + 2);
     // Conv form: decode the input once and let the GEMM gather (needs 16-byte-aligned images and the extra
     // workspace b200_approx_conv2d_workspace_bytes reserves); else write the im2col plane from the NCHW tensor
     // (contiguous along the output pixel, i.e. along rows: read and write row-fastest).
@@ -1141,7 +1239,9 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         const char* e = getenv("B200_CONV_GATHER");   // experiments / tests: 0 = never, 1 = heuristic, 2 = whenever possible
         const int mode = e ? atoi(e) : 1;
         const bool pays = mode >= 2 || (A.kh * A.kw >= 4 && N <= 256);
-        gather = mode != 0 && pays && conv_ws && conv_ws_bytes >= need && img % 4 == 0 && total < ((int64_t)1 << 31) &&
+        // (v5 flavour: padding taps are REAL zeros of the reference's im2col matrix and must decode as the code
+        // (0, 0), which the gather's shared "zero word" cannot tell from k / row padding: im2col plane only)
+        gather = !geom.v5 && mode != 0 && pays && conv_ws && conv_ws_bytes >= need && img % 4 == 0 && total < ((int64_t)1 << 31) &&
                  ((uintptr_t)A.p & 15) == 0 && A.H < 16384 && A.W < 16384 && nB * A.Ho * A.Wo == Mrows;
         if (gather) {
             uint32_t* Pw = reinterpret_cast<uint32_t*>(conv_ws);
@@ -1327,13 +1427,16 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     if (int rc = check_device()) return rc;
     if (!p || Mrows < 0 || K < 0 || N < 0) { set_error("b200_approx_gemm: bad argument"); return B200_ERR_ARGUMENT; }
     const int E = p->expo_width, M = p->mant_width;
+    const bool v5 = p->ofuf_mode == 1;
     const signed char* host_table = nullptr;
     if (p->custom_table) {
         if (E < 1 || M < 1 || M > 5 || E + M > 7) { set_error("Invalid combination of expo_width and mant_width"); return B200_ERR_INVALID_FORMAT; }
         host_table = intern_table(reinterpret_cast<const signed char*>(p->custom_table), M);
-    } else if (int rc = select_table(E, M, p->withComp, p->dnsmp_factor, p->allow_unpinned_format, &host_table)) {
+    } else if (int rc = v5 ? select_table_v5(E, M, p->withComp, p->dnsmp_factor, &host_table)
+                           : select_table(E, M, p->withComp, p->dnsmp_factor, p->allow_unpinned_format, &host_table)) {
         return rc;
     }
+    if (p->ofuf_mode > 1) { set_error("b200_approx_gemm: unknown ofuf_mode"); return B200_ERR_ARGUMENT; }
     if (Mrows == 0 || N == 0) return B200_OK;
     if ((K > 0 && (!A.p || !B)) || !C || (!bias.iB && !bias.fB)) { set_error("b200_approx_gemm: NULL operand"); return B200_ERR_ARGUMENT; }
     cudaStream_t st = (cudaStream_t)stream;
@@ -1349,20 +1452,29 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     op.cfg.qbma = p->quant_btw_mult_accu != 0;
     op.cfg.quirk = p->single_column_quirk != 0;
     op.T = op.cfg.with_approx ? dev_table : nullptr;
+    V5Flags vf{v5 ? 1 : 0, p->sim_hw_add_OFUF != 0, p->with_OF_opt != 0, p->with_UF_opt != 0};
+    if (v5) {   // the v5 GEMM knows none of approx_v9's refinements and has no tensor-bias branch
+        op.cfg.v5 = true;
+        op.cfg.sim_ofuf = vf.sim != 0; op.cfg.of_opt = vf.of_opt != 0; op.cfg.uf_opt = vf.uf_opt != 0;
+        op.cfg.quirk = false;
+        op.T = dev_table;
+    }
     const BSrc bsrc{B, sb_k, sb_n};
     const dim3 ggrid = pair_gemm_grid(Mrows, N);
 
-    const bool lut_mode = !p->force_generic && p->with_s2nn2s_opt && p->quant_btw_mult_accu && !p->single_column_quirk && K > 0;
+    const bool lut_mode = !p->force_generic && K > 0 &&
+                          (v5 || (p->with_s2nn2s_opt && p->quant_btw_mult_accu && !p->single_column_quirk));
     const LutEntry* lut = nullptr;
     if (lut_mode) {
-        if (int rc = get_lut(E, M, p->with_approx ? host_table : nullptr, p->with_approx ? dev_table : nullptr,
-                             p->with_approx != 0, p->golden_clip_OF != 0, &lut))
+        if (int rc = v5 ? get_lut(E, M, host_table, dev_table, 0, 0, &lut, false, &vf)
+                        : get_lut(E, M, p->with_approx ? host_table : nullptr, p->with_approx ? dev_table : nullptr,
+                                  p->with_approx != 0, p->golden_clip_OF != 0, &lut))
             return rc;
     }
     if (!lut || lut->flags.sign_quirk || lut->flags.unrepresentable) {
         pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, nullptr, 0);
         B200_LAUNCH_CHECK("pair_gemm_kernel<ApproxPairOp>");
-        set_path("generic");
+        set_path(v5 ? "generic-v5" : "generic");
         return B200_OK;
     }
 
@@ -1378,8 +1490,10 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 32, st));
 
     // split-K partial sums: only if the caller's workspace has the room b200_approx_gemm_workspace_bytes asks for
+    // (not in the v5 flavour: without sim_hw_add_OFUF its cells need not be integers of u, and the exactness
+    // certificate below is stated for approx_v9's table)
     const size_t pbytes = splitk_partial_bytes(Mrows, N);
-    float* partial = (pbytes && workspace_bytes >= words + pbytes) ? reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + words) : nullptr;
+    float* partial = (!v5 && pbytes && workspace_bytes >= words + pbytes) ? reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + words) : nullptr;
     // whatever the caller provides beyond the GEMM-form workspace holds the decoded conv plane
     void* conv_ws = workspace_bytes > words + pbytes ? reinterpret_cast<char*>(workspace) + words + pbytes : nullptr;
     const size_t conv_ws_bytes = conv_ws ? workspace_bytes - words - pbytes : 0;
@@ -1389,6 +1503,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     // runs only if the predecode found an off-grid operand
     pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<ApproxPairOp>(conditional)");
+    if (v5) { set_path("lut-v5"); return B200_OK; }
     set_path(lut->geom.sidx ? "lut-signed" : (g_last_splits > 1 ? "lut-splitk" : (g_last_splits == 0 ? "lut-streamk" : "lut")));
     return B200_OK;
 }

@@ -66,8 +66,8 @@ __global__ void __launch_bounds__(256) approx_dw_kernel(DwArgs d, const int* __r
             for (int k = 0; k < d.Kg; ++k) {
                 const float av = a.load(m, k);
                 const float bv = __ldg(wg + k);
-                acc += d.T ? pair_generic(d.cfg, pA, pB, pR, d.T, av, bv)
-                           : pair_generic<signed char>(d.cfg, pA, pB, pR, nullptr, av, bv);
+                acc += d.T ? pair_any(d.cfg, pA, pB, pR, d.T, av, bv)
+                           : pair_any<signed char>(d.cfg, pA, pB, pR, nullptr, av, bv);
             }
         }
         tile[gl][tx] = acc;
@@ -417,11 +417,13 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
     // N == 1 per group: the reference's tensor-bias branch (approx_calculation.py:800-809)
     if (aq) { set_error("b200_approx_conv2d_fbias_fq: the fused input quantizer is not available for depthwise groups"); return B200_ERR_ARGUMENT; }
     const int E = p->expo_width, M = p->mant_width;
+    const bool v5 = p->ofuf_mode == 1;      // v5 integer-add semantics (no tensor-bias branch exists in v5)
     const signed char* host_table = nullptr;
     if (p->custom_table) {
         if (E < 1 || M < 1 || M > 5 || E + M > 7) { set_error("Invalid combination of expo_width and mant_width"); return B200_ERR_INVALID_FORMAT; }
         host_table = intern_table(reinterpret_cast<const signed char*>(p->custom_table), M);
-    } else if (int rc = select_table(E, M, p->withComp, p->dnsmp_factor, p->allow_unpinned_format, &host_table)) {
+    } else if (int rc = v5 ? select_table_v5(E, M, p->withComp, p->dnsmp_factor, &host_table)
+                           : select_table(E, M, p->withComp, p->dnsmp_factor, p->allow_unpinned_format, &host_table)) {
         return rc;
     }
     if (d.rows == 0) return B200_OK;
@@ -439,10 +441,15 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
     a.cfg.qbma = p->quant_btw_mult_accu != 0;
     a.cfg.quirk = true;
     a.T = a.cfg.with_approx ? dev_table : nullptr;
+    if (v5) {
+        a.cfg.v5 = true; a.cfg.quirk = false;
+        a.cfg.sim_ofuf = p->sim_hw_add_OFUF != 0; a.cfg.of_opt = p->with_OF_opt != 0; a.cfg.uf_opt = p->with_UF_opt != 0;
+        a.T = dev_table;
+    }
     const dim3 grid((unsigned)ceil_div(d.rows, 32), (unsigned)ceil_div(g->groups, 32));
     cudaStream_t st = (cudaStream_t)stream;
     // table path: main mode only; needs 256 B of workspace for the device-side fallback flag
-    const bool lut_mode = !p->force_generic && p->with_s2nn2s_opt && p->quant_btw_mult_accu && !p->golden_clip_OF &&
+    const bool lut_mode = !v5 && !p->force_generic && p->with_s2nn2s_opt && p->quant_btw_mult_accu && !p->golden_clip_OF &&
                           workspace && workspace_bytes >= 256;
     if (lut_mode) {
         DwLutArgs la;
@@ -482,6 +489,6 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
     }
     approx_dw_kernel<<<grid, 256, 0, st>>>(a, nullptr, 0);
     B200_LAUNCH_CHECK("approx_dw_kernel");
-    set_path("single-column");
+    set_path(v5 ? "single-column-v5" : "single-column");
     return B200_OK;
 }

@@ -37,6 +37,8 @@ struct LutGeom {
     int total_entries;
     int sidx;        // 1: "signed index" layout for tables that are not odd in the operand signs
     int s_stride;    // entries per sign region: a_stride * 2^M
+    int v5;          // 1: table of the v5 integer-add GEMM (ofuf_mode 1), indexed by code exponents
+    int v5_lo;       // v5: most negative supported eB - (bA + bB - bR)
 };
 
 // Signed-index layout (sidx): the addend depends on the signs only through s = [a<0] xor [b<0], but for
@@ -60,6 +62,33 @@ __host__ __device__ inline LutGeom make_lut_geom(int E, int M, bool sidx = false
     g.s_stride = g.a_stride << M;
     g.zeroA_off = g.s_stride * (sidx ? 3 : 2);
     g.total_entries = g.zeroA_off + g.NTB * g.row_entries;
+    g.v5 = 0;
+    g.v5_lo = 0;
+    return g;
+}
+
+// v5 flavour: same entry layout [sa][mA][row][mB], row = tA_idx + tB_idx with
+//   tA_idx = eA                               in [0, RA],  RA = 2^E - 1   (code exponent of a)
+//   tB_idx = eB - (bA + bB - bR) + lo + RA + 1   in [RA + 1, NTB - 1]      (code exponent of b, re-biased per column)
+//   row - (lo + RA + 1) = eA + eB - (bA + bB - bR), the exponent part of the product code t (v5 :159)
+// tB_idx = 0 is reserved for padding: rows <= RA are all zero.  Exponent sums outside [-lo, 2^E + 3] + [0, RA]
+// (never met with calibrated biases) raise the off-grid flag instead.
+__host__ __device__ inline LutGeom make_lut_geom_v5(int E, int M)
+{
+    LutGeom g;
+    g.E = E;
+    g.M = M;
+    g.RA = (1 << E) - 1;
+    g.v5_lo = (1 << E) + 8;
+    g.NTB = g.RA + 1 + g.v5_lo + (1 << E) + 4;
+    g.NT = g.RA + g.NTB;
+    g.row_entries = 1 << M;
+    g.a_stride = g.NT * g.row_entries;
+    g.sidx = 0;
+    g.s_stride = g.a_stride << M;
+    g.zeroA_off = g.s_stride * 2;
+    g.total_entries = g.zeroA_off + g.NTB * g.row_entries;
+    g.v5 = 1;
     return g;
 }
 

@@ -114,6 +114,8 @@ __host__ __device__ inline float allnorm_decode(int M, int bias, float sign, int
 struct PairCfg {
     int E, M;
     bool with_approx, s2nn2s, clip_OF, qbma, quirk;
+    // ofuf_mode 1: the v5 integer-add GEMM (pair_v5 below) with its live overflow / underflow flags
+    bool v5 = false, sim_ofuf = false, of_opt = false, uf_opt = false;
 };
 
 // mult_result_mant, approx/approx_matmul_whole_v9.py:178-184 (negative indices wrap like python)
@@ -166,6 +168,37 @@ __host__ __device__ inline float pair_generic(const PairCfg& c, const FmtParam& 
 __host__ __device__ __forceinline__ float clamp_nan(float x, float mn, float mx)
 {
     return (x != x) ? x : fminf(fmaxf(x, mn), mx);
+}
+
+// One operand pair of the v5 GEMM (opt-in): custom_matmul_vectorize of
+// approx/approx_matmul_whole_v5.py:10-152 with approx_mult_new :155-182.  T: v5 comp table or nullptr (zeros).
+// One custom_bias in v5; per-operand biases enter as B_neg = -((bA + bB - bR) << M) (approx_v9's exponent formula).
+template <typename TabT>
+__host__ __device__ inline float pair_v5(const PairCfg& c, const FmtParam& pA, const FmtParam& pB, const FmtParam& pR,
+                                         const TabT* T, float a, float b)
+{
+    int eA, mA, eB, mB;
+    fpany_encode(pA, a, true, eA, mA);                          // :26-37, clip_OF = True (:22)
+    fpany_encode(pB, b, true, eB, mB);                          // :39-50
+    const int ms = 1 << c.M, mod = 1 << (c.E + c.M);
+    int t = (eA * ms + mA) + (eB * ms + mB) - (pA.bias + pB.bias - pR.bias) * ms;   // :52-59, :159
+    if (T) t += (int)T[mA * ms + mB];                           // :159 comp_table_NN[x_mant, y_mant]
+    if (c.sim_ofuf) {                                           // :162-176
+        const bool of = t > mod - 1, uf = t < 0;
+        t = ((t % mod) + mod) % mod;                            // floor-mod
+        if (c.of_opt && of) t = mod - 1;
+        if (c.uf_opt && uf) t = t % ms;
+    }
+    const int expo = t >> c.M, mant = t & (ms - 1);             // :298-299 (floor division, non-negative remainder)
+    const float sign = ((a < 0.0f) ? -1.0f : 1.0f) * ((b < 0.0f) ? -1.0f : 1.0f);   // :106-108
+    return fpany_decode(pR, sign, expo, mant);                  // :111-114
+}
+
+template <typename TabT>
+__host__ __device__ inline float pair_any(const PairCfg& c, const FmtParam& pA, const FmtParam& pB, const FmtParam& pR,
+                                          const TabT* T, float a, float b)
+{
+    return c.v5 ? pair_v5(c, pA, pB, pR, T, a, b) : pair_generic(c, pA, pB, pR, T, a, b);
 }
 
 // quantize_to_fp8_ste_MM element body, quantization/quantizers/fp8_quantizer.py:119-154

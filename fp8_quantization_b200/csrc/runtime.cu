@@ -6,7 +6,13 @@
 
 #include "common.cuh"
 #include "comp_tables.inc"
+#include "comp_tables_v5.inc"
 #include "tables.h"
+
+#include <cstddef>
+static_assert(sizeof(b200_approx_params) == 40 && offsetof(b200_approx_params, ofuf_mode) == 24 &&
+                  offsetof(b200_approx_params, custom_table) == 32,
+              "b200_approx_params layout is part of the C ABI (fp8_quantization_b200/_lib.py mirrors it)");
 
 namespace b200 {
 
@@ -80,6 +86,28 @@ int select_table(int E, int M, int withComp, int dnsmp, int allow_unpinned, cons
     return B200_ERR_INVALID_FORMAT;
 }
 
+// get_comp_table_NN of the v5 integer-add multiplier (approx/approx_matmul_whole_v5.py:516-542); nullptr = zeros
+// (without withComp v5 assigns a zero table and then raises: the opt-in mode uses the zero table).
+int select_table_v5(int E, int M, int withComp, int dnsmp, const signed char** out)
+{
+    *out = nullptr;
+    const bool known = (E == 4 && M == 3) || (E == 3 && M == 4) || (E == 2 && M == 5);
+    if (!known) { set_error("Invalid combination of expo_width and mant_width"); return B200_ERR_INVALID_FORMAT; }
+    if (!withComp) return B200_OK;
+    if (E == 4) { *out = kCompV5Table0; return B200_OK; }
+    if (E == 3) {
+        if (dnsmp == 3) *out = kCompV5Table1;
+        else if (dnsmp >= 4) *out = kCompV5Table2;
+        else { set_error("UnboundLocalError: comp_table_NN (E3M4, withComp, dnsmp_factor < 3)"); return B200_ERR_UNBOUND_TABLE; }
+        return B200_OK;
+    }
+    if (dnsmp == 3) *out = kCompV5Table3;
+    else if (dnsmp == 4) *out = kCompV5Table4;
+    else if (dnsmp >= 5) *out = kCompV5Table5;
+    else { set_error("UnboundLocalError: comp_table_NN (E2M5, withComp, dnsmp_factor < 3)"); return B200_ERR_UNBOUND_TABLE; }
+    return B200_OK;
+}
+
 const signed char* intern_table(const signed char* host, int M)
 {
     static std::mutex mu;
@@ -108,6 +136,18 @@ extern "C" const char* b200_last_error(void)
 
 extern "C" uint64_t b200_kernel_launches(void) { return g_launches.load(); }
 extern "C" const char* b200_last_path(void) { return g_path; }
+
+extern "C" int b200_comp_table_v5(int E, int M, int withComp, int dnsmp, int8_t* host_out)
+{
+    const signed char* t = nullptr;
+    int rc = select_table_v5(E, M, withComp, dnsmp, &t);
+    if (rc != B200_OK) return rc;
+    if (!host_out) { set_error("b200_comp_table_v5: host_out is NULL"); return B200_ERR_ARGUMENT; }
+    const int n = (1 << M) * (1 << M);
+    if (t) memcpy(host_out, t, n);
+    else memset(host_out, 0, n);
+    return B200_OK;
+}
 
 extern "C" int b200_error_table(int E, int M, int withComp, int dnsmp, int allow_unpinned, int8_t* host_out)
 {

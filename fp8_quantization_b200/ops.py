@@ -63,10 +63,13 @@ def _workspace(device, nbytes):
 
 
 def make_params(custom_approx_params=None, *, single_column_quirk=False, allow_unpinned_format=False,
-                force_generic=False, **overrides):
+                force_generic=False, ofuf_mode=None, **overrides):
     """Builds the POD struct from the reference's `custom_approx_params` dict (13 keys,
     utils/click_options.py:589-606); missing keys take the defaults of custom_matmul_vectorize's
-    signature (approx/approx_matmul_whole_v9.py:10-18)."""
+    signature (approx/approx_matmul_whole_v9.py:10-18).
+    ofuf_mode: 0 = approx_v9 (sim_hw_add_OFUF / with_OF_opt / with_UF_opt ignored, the reference's behaviour);
+    1 or "v5" = the v5 integer-add GEMM in which those flags are live.  Opt-in only: taken
+    from the argument, else from an extra `ofuf_mode` key of the dict (not one of the reference's 13 keys)."""
     d = dict(expo_width=4, mant_width=3, dnsmp_factor=3, withComp=True, with_approx=True,
              with_s2nn2s_opt=False, sim_hw_add_OFUF=False, with_OF_opt=False, with_UF_opt=False,
              golden_clip_OF=False, quant_btw_mult_accu=True, debug_mode=False, self_check_mode=False)
@@ -81,6 +84,9 @@ def make_params(custom_approx_params=None, *, single_column_quirk=False, allow_u
     p.single_column_quirk = 1 if single_column_quirk else 0
     p.allow_unpinned_format = 1 if allow_unpinned_format else 0
     p.force_generic = 1 if force_generic else 0
+    if ofuf_mode is None:
+        ofuf_mode = (custom_approx_params or {}).get("ofuf_mode", 0)
+    p.ofuf_mode = 1 if ofuf_mode in (1, True, "v5") else 0
     p.custom_table = None
     return p
 
@@ -92,6 +98,16 @@ def error_table(expo_width, mant_width, withComp, dnsmp_factor, allow_unpinned_f
     out = torch.zeros((n, n), dtype=torch.int8)
     _lib.check(lib.b200_error_table(expo_width, mant_width, int(bool(withComp)), int(dnsmp_factor),
                                     int(allow_unpinned_format), ctypes.c_void_p(out.data_ptr())))
+    return out
+
+
+def comp_table_v5(expo_width, mant_width, withComp, dnsmp_factor):
+    """get_comp_table_NN of the v5 integer-add multiplier (approx/approx_matmul_whole_v5.py:516-542), host int8."""
+    lib = _lib.load()
+    n = 2 ** mant_width if 0 < mant_width <= 5 else 1
+    out = torch.zeros((n, n), dtype=torch.int8)
+    _lib.check(lib.b200_comp_table_v5(expo_width, mant_width, int(bool(withComp)), int(dnsmp_factor),
+                                      ctypes.c_void_p(out.data_ptr())))
     return out
 
 

@@ -40,8 +40,9 @@ extern "C" {
 #define B200_ERR_NO_DEVICE (-7)      /* no sm_100 device: there is NO CPU fallback */
 
 /* custom_approx_params, utils/click_options.py:589-606 (13 keys) + run-mode bits.
- * sim_hw_add_OFUF / with_OF_opt / with_UF_opt are accepted and IGNORED exactly like approx_v9 does
- * (approx_matmul_whole_v9.py:15 vs :20-169).  */
+ * With ofuf_mode == 0 (the default) sim_hw_add_OFUF / with_OF_opt / with_UF_opt are accepted and IGNORED exactly
+ * like approx_v9 does (approx_matmul_whole_v9.py:15 vs :20-169).  ofuf_mode == 1 opts into the last LIVE definition
+ * of those flags, the v5 integer-add GEMM (see b200_approx_gemm below). */
 typedef struct b200_approx_params {
     int32_t expo_width;
     int32_t mant_width;
@@ -58,6 +59,8 @@ typedef struct b200_approx_params {
     uint8_t single_column_quirk; /* 1: int32-tensor-bias numerics of the N==1 branch, approx_calculation.py:801-809 */
     uint8_t allow_unpinned_format; /* 1: accept (E,M) outside {(4,3),(3,4),(2,5)} with an all-zero table (no reference answer) */
     uint8_t force_generic;       /* 1: skip the table kernel, use the per-pair arithmetic kernel (tests) */
+    uint8_t ofuf_mode;           /* 0: approx_v9 (OF/UF flags ignored).  1: the v5 integer-add GEMM with the simulated
+                                    hardware-adder overflow / underflow, approx_matmul_whole_v5.py:10-182 */
     const int8_t *custom_table;  /* HOST pointer or NULL.  Non-NULL: use this 2^M x 2^M int8 table (the
                                     error_table_NN argument of custom_matmul_vectorize,
                                     approx_matmul_whole_v9.py:12) instead of selecting by withComp/dnsmp_factor */
@@ -86,6 +89,11 @@ uint64_t b200_autotune_runs(void);
 int b200_error_table(int expo_width, int mant_width, int withComp, int dnsmp_factor,
                      int allow_unpinned_format, int8_t *host_out);
 
+/* get_comp_table_NN of the v5 integer-add multiplier, approx/approx_matmul_whole_v5.py:516-542 (used when
+ * ofuf_mode == 1): 2^M * 2^M int8 to HOST memory; without withComp the all-zero table the reference assigns before
+ * it raises. */
+int b200_comp_table_v5(int expo_width, int mant_width, int withComp, int dnsmp_factor, int8_t *host_out);
+
 /* ---- A8: quantize_to_fp8_ste_MM, quantization/quantizers/fp8_quantizer.py:97-173 ------------- */
 /* maxval: device [n_channels]; n_channels == 1 -> per tensor, else channel = (i / inner) % n_channels
  * (maxval viewed as [C,1,...,1], :114-115).  bias_out: device [n_channels] fp32 (integer valued),
@@ -108,12 +116,13 @@ int b200_fpany_quant(const float *v, int64_t n, int expo_width, int mant_width, 
                      int tensor_bias_quirk, int clip_OF, float *out, void *stream);
 
 /* ---- A7: hardware adder overflow / underflow clipping (only live in v5) ------------------------ */
+/* Inside the GEMM / conv: b200_approx_params.ofuf_mode = 1 (above).  Elementwise, on integer codes: */
 /* approx_mult_new, approx/approx_matmul_whole_v5.py:155-182, elementwise on the integer code domain:
  *   t = x_int + y_int + B_neg + table[x_mant, y_mant];
  *   sim_hw_add_OFUF: of = t > 2^(E+M)-1, uf = t < 0; t = t mod 2^(E+M) (floor-mod);
  *   with_OF_opt: t = of ? 2^(E+M)-1 : t;   with_UF_opt: t = uf ? t mod 2^M : t.
  * approx_v9 accepts these three flags and never reads them (approx_matmul_whole_v9.py:15 vs :20-169), so
- * b200_approx_gemm ignores them too; this entry point is the opt-in v5 semantics.  x_mant / y_mant may
+ * b200_approx_gemm ignores them too unless ofuf_mode == 1; this entry point is the same clip on raw codes.  x_mant / y_mant may
  * be NULL (-> x_int mod 2^M); table_dev: DEVICE int8 [2^M, 2^M] or NULL (zeros).  (The with_OF_opt line of
  * the reference names an undefined tensor, :173; its evident meaning is implemented -- see
  * tests/golden/make_v5_ofuf.py.) */
@@ -130,7 +139,19 @@ int b200_approx_mult_v5(const int32_t *x_int, const int32_t *y_int, const int32_
  *   B  : [K, N] fp32, element (k,n) at B[k*sb_k + n*sb_n]          (weight.t(): sb_k=1, sb_n=ldw)
  *   C  : [Mrows, N] fp32, element (m,n) at C[m*ldc + n]
  *   bB : device int32 [N], per-column weight exponent bias (y_bias[i], :952); bA,bR scalars.
- * C[m,n] = sum_{k ascending, fp32} addend(A[m,k], B[k,n]).                                       */
+ * C[m,n] = sum_{k ascending, fp32} addend(A[m,k], B[k,n]).
+ *
+ * p->ofuf_mode == 1 (opt-in): the addend is the v5 GEMM's, custom_matmul_vectorize of
+ * approx/approx_matmul_whole_v5.py:10-152 with approx_mult_new (:155-182):
+ *   (eA,mA) = enc(a), (eB,mB) = enc(b)  [clip_OF = True];   t = (eA*2^M+mA) + (eB*2^M+mB) + B_neg + comp[mA,mB];
+ *   sim_hw_add_OFUF: of = t > 2^(E+M)-1, uf = t < 0, t = t mod 2^(E+M); with_OF_opt: of -> 2^(E+M)-1;
+ *   with_UF_opt: uf -> t mod 2^M;   addend = dec(t) * sign(a) * sign(b);   fp32 sum, k ascending.
+ * v5 has ONE custom_bias; with the layers' per-operand biases B_neg = -((bA + bB[n] - bR) << M) (approx_v9's exponent
+ * formula, v9 :66-67) and the result decodes with bR -- equal biases reproduce v5 bit for bit (tests/golden/
+ * v5_gemm.npz).  comp = p->custom_table, else v5's own table choice (:516-542; all zero without withComp).  A zero
+ * operand is an ordinary code in v5 (its product is NOT zero); with_approx / with_s2nn2s_opt / quant_btw_mult_accu /
+ * golden_clip_OF / single_column_quirk do not exist in v5 and are ignored in this mode.  Operands on the format's grid
+ * run on the table kernel (a second pair-table flavour), anything else on the arithmetic kernel. */
 size_t b200_approx_gemm_workspace_bytes(int64_t Mrows, int64_t K, int64_t N);
 int b200_approx_gemm(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n,
                      float *C, int64_t ldc, int64_t Mrows, int64_t K, int64_t N, int bA,

@@ -403,6 +403,61 @@ void orc_v5_ofuf_array(const int32_t *x_int, const int32_t *y_int, const int32_t
     }
 }
 
+/*
+ * The v5 GEMM, custom_matmul_vectorize of approx/approx_matmul_whole_v5.py:10-152 -- the last version whose
+ * sim_hw_add_OFUF / with_OF_opt / with_UF_opt are live (approx_v9 ignores them):
+ *   (eA,mA) = enc(a), (eB,mB) = enc(b) with clip_OF = True (:22,:26-50; python-number param_prepare :204-243);
+ *   t = (eA*2^M + mA) + (eB*2^M + mB) + B_neg + comp[mA,mB]  (:52-85,:159), then the adder simulation (:162-176);
+ *   r = dec(t) * sign(a) * sign(b), sign(v) = v < 0 ? -1 : 1  (:106-116, :285-313: expo = t // 2^M floor, mant = t mod 2^M);
+ *   C = sum_k r in fp32 (:131).
+ * v5 has ONE custom_bias for all three formats; with per-operand biases (the layers have them) the code offset
+ * is B_neg = -((bA + bB[n] - bR) << M) -- approx_v9's exponent formula (v9 :66-67) -- and the result decodes with bR;
+ * bA == bB == bR reproduces v5 exactly.  A zero operand is NOT special in v5: its code (0,0) takes part in the add.
+ */
+static float orc_v5_pair(int E, int M, const orc_param *pA, const orc_param *pB, const orc_param *pR,
+                         const int32_t *comp, int sim, int of_opt, int uf_opt, float a, float b)
+{
+    int32_t eA, mA, eB, mB;
+    orc_encode(pA, a, 1, &eA, &mA);
+    orc_encode(pB, b, 1, &eB, &mB);
+    const int32_t mant_scale = 1 << M, mod = 1 << (E + M), max_norm_int = mod - 1;
+    const int32_t B_neg = -((pA->fp_bias + pB->fp_bias - pR->fp_bias) * mant_scale);
+    int32_t t = (eA * mant_scale + mA) + (eB * mant_scale + mB) + B_neg + (comp ? comp[mA * mant_scale + mB] : 0);
+    if (sim) {
+        int of = t > max_norm_int, uf = t < 0;
+        t = ((t % mod) + mod) % mod;
+        if (of_opt && of) t = max_norm_int;
+        if (uf_opt && uf) t = t % mant_scale;
+    }
+    int32_t expo = (t >= 0) ? t / mant_scale : -((-t + mant_scale - 1) / mant_scale);   /* floor division */
+    int32_t mant = t - expo * mant_scale;
+    const float sign = ((a < 0.0f) ? -1.0f : 1.0f) * ((b < 0.0f) ? -1.0f : 1.0f);
+    return orc_decode(pR, sign, expo, mant);
+}
+
+void orc_v5_matmul(int E, int M, const int32_t *comp, const float *A, int64_t sa0, int64_t sa1, const float *B,
+                   int64_t sb0, int64_t sb1, float *C, int64_t sc0, int64_t sc1, int64_t Mrows, int64_t K, int64_t N,
+                   int bA, const int32_t *bB, int bB_stride, int bR, int sim, int of_opt, int uf_opt, int sum_mode)
+{
+    orc_param pA = orc_param_prepare(E, M, bA, 0);
+    orc_param pR = orc_param_prepare(E, M, bR, 0);
+#pragma omp parallel for collapse(2) schedule(static)
+    for (int64_t n = 0; n < N; ++n) {
+        for (int64_t m = 0; m < Mrows; ++m) {
+            orc_param pB = orc_param_prepare(E, M, bB[n * bB_stride], 0);
+            float accf = 0.0f;
+            double accd = 0.0;
+            for (int64_t k = 0; k < K; ++k) {
+                float r = orc_v5_pair(E, M, &pA, &pB, &pR, comp, sim, of_opt, uf_opt, A[m * sa0 + k * sa1],
+                                      B[k * sb0 + n * sb1]);
+                accf += r;
+                accd += (double)r;
+            }
+            C[m * sc0 + n * sc1] = sum_mode ? (float)accd : accf;
+        }
+    }
+}
+
 /* ------------------------------------------------------------------------------------------ */
 /* im2col, approx/approx_calculation.py:724-747: [B,C,H,W] -> [B*Ho*Wo, C*kh*kw], K order (c,ky,kx) */
 /* ------------------------------------------------------------------------------------------ */

@@ -220,6 +220,51 @@ def v5_ofuf(x_int, y_int, comp, B_neg, E, M, sim_hw_add_OFUF, with_OF_opt, with_
     return out
 
 
+_V5_TABLES = None
+
+
+def v5_comp_table(E, M, withComp, dnsmp_factor):
+    """get_comp_table_NN of approx/approx_matmul_whole_v5.py:516-542; without compensation the reference assigns an
+    all-zero table and then raises ValueError -- the zero table is what the opt-in mode uses there."""
+    global _V5_TABLES
+    if _V5_TABLES is None:
+        z = np.load(os.path.join(_HERE, "..", "tests", "golden", "comp_tables_v5.npz"))
+        _V5_TABLES = [z[f"t{i}"].astype(np.int32) for i in range(6)]
+    L = _V5_TABLES
+    if not withComp:
+        return np.zeros((2 ** M, 2 ** M), np.int32)
+    if (E, M) == (4, 3):
+        return L[0]
+    if (E, M) == (3, 4):
+        if dnsmp_factor == 3:
+            return L[1]
+        if dnsmp_factor >= 4:
+            return L[2]
+        raise UnboundLocalError("comp_table_NN")
+    if (E, M) == (2, 5):
+        if dnsmp_factor in (3, 4):
+            return L[dnsmp_factor]
+        if dnsmp_factor >= 5:
+            return L[5]
+        raise UnboundLocalError("comp_table_NN")
+    raise ValueError("Invalid combination of expo_width and mant_width")
+
+
+def v5_matmul(A, B, comp, E, M, bA, bB, bR, sim_hw_add_OFUF=False, with_OF_opt=False, with_UF_opt=False, sum_mode=0):
+    """custom_matmul_vectorize of approx/approx_matmul_whole_v5.py:10-152 (see orc_v5_matmul)."""
+    A = _f32(A)
+    B = _f32(B)
+    Mr, K = A.shape
+    N = B.shape[1]
+    comp = np.ascontiguousarray(comp, np.int32) if comp is not None else None
+    bBv = np.ascontiguousarray(np.broadcast_to(np.asarray(bB, np.int32).reshape(-1), (N,)), np.int32)
+    C = np.zeros((Mr, N), np.float32)
+    lib().orc_v5_matmul(int(E), int(M), _p(comp), _p(A), i64(K), i64(1), _p(B), i64(N), i64(1), _p(C), i64(N), i64(1),
+                        i64(Mr), i64(K), i64(N), int(bA), _p(bBv), 1, int(bR), int(sim_hw_add_OFUF), int(with_OF_opt),
+                        int(with_UF_opt), int(sum_mode))
+    return C
+
+
 def im2col(x, kh, kw, stride, padding, dilation):
     x = _f32(x)
     B, C, H, W = x.shape

@@ -61,8 +61,13 @@ def _build(ref, z, i, meta):
     return layer.cuda().eval()
 
 
-def _protocol(layer, x_cal, x_eval):
-    with torch.inference_mode(), contextlib.redirect_stdout(io.StringIO()):   # the Linear variant prints tensors
+def _protocol(layer, x_cal, x_eval, eager=False):
+    # The unpatched reference builds scalar tensors without a device (e.g. approx_matmul_whole_v9.py:275,
+    # torch.tensor(mant_width)); torch 2.4 (its pinned version) let such 0-dim CPU tensors mix with CUDA operands in
+    # ldexp, torch 2.11 does not.  Running it under a default-device context puts them on the GPU -- the reference
+    # itself stays unmodified.  The patched classes need no such context.
+    ctx = torch.device("cuda") if eager else contextlib.nullcontext()
+    with ctx, torch.inference_mode(), contextlib.redirect_stdout(io.StringIO()):   # the Linear variant prints tensors
         layer.quantized()
         layer.estimate_ranges()
         y_cal = layer(x_cal)
@@ -83,7 +88,7 @@ def test_reference_classes_with_dropin(ref, level):
     bad = []
     for i, meta in enumerate(metas):
         x_cal, x_eval = torch.from_numpy(z[f"xcal{i}"]).cuda(), torch.from_numpy(z[f"xeval{i}"]).cuda()
-        eager = _protocol(_build(ref, z, i, meta), x_cal, x_eval)         # unpatched reference, GPU eager
+        eager = _protocol(_build(ref, z, i, meta), x_cal, x_eval, eager=True)   # unpatched reference, GPU eager
         b200.install(level=level)
         try:
             l0 = ops.kernel_launches()
@@ -132,7 +137,7 @@ def test_vit_shaped_linear_vs_gpu_eager_reference(ref, K, N):
         if patched:
             b200.install()
         try:
-            outs.append(_protocol(layer, x.cuda(), (x * 0.9).cuda()))
+            outs.append(_protocol(layer, x.cuda(), (x * 0.9).cuda(), eager=not patched))
         finally:
             b200.uninstall()
     for a, c in zip(outs[0][2], outs[1][2]):

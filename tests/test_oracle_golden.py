@@ -144,3 +144,37 @@ def test_v5_ofuf_fixture():
         comp = T[x % (2 ** M), y % (2 ** M)]
         got = orc.v5_ofuf(x, y, comp, int(B_neg), int(E), int(M), int(sim), int(of), int(uf))
         assert np.array_equal(got, z[f"r{i}"]), (i, E, M, sim, of, uf)
+
+
+def test_v5_gemm_fixture():
+    """Oracle restatement of the v5 GEMM (approx/approx_matmul_whole_v5.py:10-182, the live OF/UF flags) against
+    outputs of the unmodified reference function (tests/golden/make_v5_gemm.py): bit exact with sim_hw_add_OFUF
+    (addends are bounded multiples of u: the fp32 sum is order independent), 1e-6 norm-wise otherwise."""
+    z = np.load(os.path.join(GOLD, "v5_gemm.npz"))
+    nexact = 0
+    for i, (E, M, bias, ongrid, wc, sim, of, uf, g) in enumerate(z["cfgs"].tolist()):
+        T = orc.v5_comp_table(E, M, bool(wc), 3)
+        A, B = z[f"A{g}"], z[f"B{g}"]
+        got = orc.v5_matmul(A, B, T, E, M, bias, bias, bias, sim, of, uf)
+        want = z[f"r{i}"]
+        if same_bits(got, want):
+            nexact += 1
+            continue
+        assert not sim, (i, "not bit exact with sim_hw_add_OFUF")
+        mag = np.abs(orc.v5_matmul(np.abs(A), np.abs(B), T, E, M, bias, bias, bias, sim, of, uf, sum_mode=1)).astype(np.float64)
+        assert np.all(np.abs(got.astype(np.float64) - want) <= 1e-6 * mag + 1e-30), i
+    assert nexact >= len(z["cfgs"]) * 3 // 4
+
+
+def test_v5_comp_tables_match_reference():
+    import fp8_quantization_b200 as pkg
+    z = np.load(os.path.join(GOLD, "comp_tables_v5.npz"))
+    want = {(4, 3, 3): 0, (3, 4, 3): 1, (3, 4, 4): 2, (3, 4, 5): 2, (2, 5, 3): 3, (2, 5, 4): 4, (2, 5, 5): 5, (2, 5, 7): 5}
+    for (E, M, d), idx in want.items():
+        assert np.array_equal(pkg.ops.comp_table_v5(E, M, True, d).numpy(), z[f"t{idx}"]), (E, M, d)
+        assert np.array_equal(orc.v5_comp_table(E, M, True, d), z[f"t{idx}"])
+        assert not pkg.ops.comp_table_v5(E, M, False, d).any()
+    with pytest.raises(UnboundLocalError):
+        pkg.ops.comp_table_v5(3, 4, True, 2)
+    with pytest.raises(ValueError):
+        pkg.ops.comp_table_v5(5, 2, True, 3)
