@@ -93,25 +93,33 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.t0 = index, [], None, None
 
     def start(self):
+        """Spawns the sampler (nvidia-smi needs a few hundred ms before its first row: start it before the warm-up)."""
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "25", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def mark(self):
+        """Start of the timed region: only rows sampled from here to stop() are reported."""
+        self.t0 = time.time()
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        t1 = time.time()
+        time.sleep(0.05)
         self.proc.terminate()
+        rows = [r for t, r in self.rows if (self.t0 is None or t >= self.t0) and t <= t1 + 0.03]
+        self.rows = rows
         sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
         mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -453,18 +461,19 @@ def run_ours(args):
         def step():
             ops.approx_matmul(xq, wq.t(), bA, bB, bR, params, out=out)
 
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
         for _ in range(max(args.warmup, 3)):
             step()
         torch.cuda.synchronize()
         path = ops.last_path()
         macs = rows * K_DIM * N_DIM
 
-        sampler = ClockSampler(local)
-        if rank == 0:
-            sampler.start()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+        sampler.mark()
         l0 = ops.kernel_launches()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()

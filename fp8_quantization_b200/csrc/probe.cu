@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(256) lds_peak_kernel(int iters, uint32_t seed,
 #define B200_LDS_PROBE(U)                                                                   \
         {                                                                                   \
             uint32_t v;                                                                     \
-            asm volatile("ld.shared.u16 %0, [%1+%2];" : "=r"(v) : "r"(base), "n"(128 * (U))); \
+            asm volatile("ld.volatile.shared.u16 %0, [%1+%2];" : "=r"(v) : "r"(base), "n"(128 * (U))); \
             acc[(U) & 3] ^= v;                                                              \
         }
         B200_LDS_PROBE(0) B200_LDS_PROBE(1) B200_LDS_PROBE(2) B200_LDS_PROBE(3) B200_LDS_PROBE(4) B200_LDS_PROBE(5)

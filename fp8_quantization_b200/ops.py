@@ -41,6 +41,8 @@ def _mbits(t):
         return float(t)
     if not t.is_cuda:
         return float(t.item())
+    if t.is_inference():   # tensors made under torch.inference_mode() keep no version counter: read, do not cache
+        return float(t.item())
     key = (t.data_ptr(), t._version, t.device)
     v = _MBITS.get(key)
     if v is None:

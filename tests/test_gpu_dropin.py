@@ -85,10 +85,19 @@ def test_reference_classes_with_dropin(ref, level):
     from fp8_quantization_b200 import ops
     z = np.load(os.path.join(GOLD, "layers.npz"))
     metas = json.loads(bytes(z["meta"]).decode())
-    bad = []
+    bad, no_eager = [], []
     for i, meta in enumerate(metas):
         x_cal, x_eval = torch.from_numpy(z[f"xcal{i}"]).cuda(), torch.from_numpy(z[f"xeval{i}"]).cuda()
-        eager = _protocol(_build(ref, z, i, meta), x_cal, x_eval, eager=True)   # unpatched reference, GPU eager
+        try:
+            eager = _protocol(_build(ref, z, i, meta), x_cal, x_eval, eager=True)   # unpatched reference, GPU eager
+        except RuntimeError as e:
+            # quantize_after_mult_and_add: the unpatched reference hands res_quantizer.quantizer.maxval -- a plain CPU
+            # attribute that only FPQuantizer.forward would move (fp8_quantizer.py:236-237) -- straight to
+            # quantize_to_fp8_ste_MM with CUDA operands (approx_calculation.py:962 / :790) and raises on a GPU.  There is
+            # no GPU-eager answer for these cases; the CPU reference run (layers.npz) remains the judge.
+            assert meta["rm"].get("quantize_after_mult_and_add") and "same device" in str(e), (i, meta["rm"], e)
+            eager = None
+            no_eager.append(i)
         b200.install(level=level)
         try:
             l0 = ops.kernel_launches()
@@ -98,6 +107,8 @@ def test_reference_classes_with_dropin(ref, level):
             b200.uninstall()
         gold = (z[f"ycal{i}"], z[f"yeval{i}"], (z[f"bias_a{i}"], z[f"bias_w{i}"], z[f"bias_r{i}"]))
         for who, want in (("cpu-reference", gold), ("gpu-eager-reference", eager)):
+            if want is None:
+                continue
             if not all(np.array_equal(a, b) for a, b in zip(ours[2], want[2])):
                 bad.append((i, who, "fp biases", ours[2], want[2]))
                 continue
@@ -107,6 +118,7 @@ def test_reference_classes_with_dropin(ref, level):
                 if err > tol:
                     bad.append((i, who, name, meta["kind"], meta["args"], meta["rm"], "max err", err, "tol", tol))
     assert not bad, bad
+    assert len(no_eager) < len(metas) // 2, no_eager
 
 
 def test_uninstall_restores_the_reference(ref):

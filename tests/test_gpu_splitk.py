@@ -31,7 +31,8 @@ def grid_values(E, M, bias, shape, seed, top_frac=1.0):
 
 
 def flags(fq):
-    ws = fq.ops._WORKSPACES[torch.cuda.current_device()]
+    dev = torch.cuda.current_device()
+    ws = fq.ops._WORKSPACES[(dev, torch.cuda.current_stream(dev).cuda_stream)]
     return ws[:32].view(torch.int32).cpu().tolist()
 
 
