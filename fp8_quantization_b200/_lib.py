@@ -82,6 +82,9 @@ SIGNATURES = {
     "b200_qamaa_gemm_workspace_bytes": (c_sz, [c_i64, c_i64, c_i64]),
     "b200_qamaa_gemm_fbias": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_int,
                                       c_f32, c_int, c_vp, c_vp, c_i64, c_vp, c_sz, c_vp]),
+    "b200_static_scratch_bytes": (c_sz, []),
+    "b200_qamaa_gemm_fbias_static": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp,
+                                             c_int, c_f32, c_int, c_vp, c_vp, c_i64, c_vp]),
     "b200_qamaa_conv2d_workspace_bytes": (c_sz, [ctypes.POINTER(ConvGeom)]),
     "b200_qamaa_conv2d_fbias": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_int, c_f32, c_int, c_vp,
                                         c_vp, c_i64, c_vp, c_sz, c_vp]),

@@ -1647,3 +1647,77 @@ extern "C" int b200_profile_end(double* total_ms, int* launches)
     if (launches) *launches = n;
     return B200_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of b200_qamaa_gemm_fbias (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops).
+// The scratch the table kernel needs (flags, both decoded operand planes, the pair table rebuilt from `maxval`,
+// the split-K partial sums) lives in ONE file-scope device array instead of a caller workspace.  Every GPU that
+// loads the library holds these B200_STATIC_SCRATCH_BYTES until the process exits.
+//   * In host code `g_static_scratch` is only a stand-in for the symbol: its device address is looked up once
+//     per device (with that device current) through cudaGetSymbolAddress and that pointer goes to the kernels.
+//   * All calls on a device share the array and it keeps the previous call's contents: the flag words are
+//     cleared at the start of every call (qamaa_gemm_impl: cudaMemsetAsync(flag, 0, 32)), planes, table and
+//     partial sums are fully rewritten before they are read.  Calls that overlap on the GPU (two streams, two
+//     host threads) RACE on it -- serialise them.
+//   * No cudaMalloc / cudaFree / allocating library routine on this path.
+// ------------------------------------------------------------------------------------------------
+constexpr size_t kStaticScratchBytes = (size_t)64 << 20;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+namespace {
+std::mutex g_static_mu;
+void* g_static_ptr[b200::PerDeviceOnce::kMaxDev] = {};
+
+// device address of g_static_scratch on the CURRENT device (looked up once per device)
+int static_scratch_ptr(void** out)
+{
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= b200::PerDeviceOnce::kMaxDev) { set_error("device index out of range"); return B200_ERR_ARGUMENT; }
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_static_scratch)");
+        if (!p || ((uintptr_t)p & 255) != 0) { set_error("b200_qamaa_gemm_fbias_static: bad scratch address"); return B200_ERR_CUDA; }
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return B200_OK;
+}
+}  // namespace
+
+extern "C" size_t b200_static_scratch_bytes(void) { return kStaticScratchBytes; }
+
+extern "C" int b200_qamaa_gemm_fbias_static(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n,
+                                            float* C, int64_t ldc, int64_t Mrows, int64_t K, int64_t N,
+                                            const float* maxval_dev, int n_bits, float mantissa_bits, int sign_bits,
+                                            const float* bA_dev, const float* bB_dev, int64_t bB_stride, void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (Mrows < 0 || K < 0 || N < 0 || !maxval_dev || !bB_dev) {
+        set_error("b200_qamaa_gemm_fbias_static: bad argument (the operand biases are required)");
+        return B200_ERR_ARGUMENT;
+    }
+    if (Mrows == 0 || N == 0) return B200_OK;
+    if (!A || !B || !C) { set_error("b200_qamaa_gemm_fbias_static: NULL operand"); return B200_ERR_ARGUMENT; }
+    const size_t need = b200_qamaa_gemm_workspace_bytes(Mrows, K, N);
+    if (need == 0 || need > kStaticScratchBytes) {
+        char msg[256];
+        snprintf(msg, sizeof msg,
+                 "b200_qamaa_gemm_fbias_static: problem %lld x %lld x %lld needs %zu bytes of scratch, the static array holds "
+                 "%zu (use b200_qamaa_gemm_fbias with a caller workspace)",
+                 (long long)Mrows, (long long)K, (long long)N, need, kStaticScratchBytes);
+        set_error(msg);
+        return B200_ERR_WORKSPACE;
+    }
+    void* scratch = nullptr;
+    if (int rc = static_scratch_ptr(&scratch)) return rc;
+    const int E = n_bits - sign_bits - (int)rintf(mantissa_bits);
+    const int dflt = 1 << (E > 0 ? E - 1 : 0);
+    BiasSrc hint{dflt, dflt, bA_dev, nullptr, nullptr, bB_dev, bB_stride};
+    // exactly the workspace size the allocating entry point is given: same tile / split-K choice, same bits
+    return qamaa_gemm_impl(make_gemm_asrc(A, lda), B, sb_k, sb_n, C, ldc, Mrows, K, N, maxval_dev, n_bits, mantissa_bits,
+                           sign_bits, &hint, scratch, need, stream);
+}

@@ -187,6 +187,25 @@ int b200_qamaa_gemm_fbias(const float *A, int64_t lda, const float *B, int64_t s
                           float mantissa_bits, int sign_bits, const float *bA_dev, const float *bB_dev,
                           int64_t bB_stride, void *workspace, size_t workspace_bytes, void *stream);
 
+/* Allocation-free variant of b200_qamaa_gemm_fbias.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it).  The scratch (flags, decoded operand planes, pair table, split-K partial sums) is a
+ * file-scope `static __device__` array of b200_static_scratch_bytes() = 64 MiB inside the library -- every GPU that
+ * loads the library holds it until the process exits -- so there is no workspace argument and the call performs no
+ * cudaMalloc / cudaFree / allocating library routine.  Same arguments, same results (bit for bit) as
+ * b200_qamaa_gemm_fbias given a workspace of b200_qamaa_gemm_workspace_bytes(Mrows, K, N); bB_dev is required.
+ * Limit: b200_qamaa_gemm_workspace_bytes(Mrows, K, N) <= b200_static_scratch_bytes() (roughly
+ * round_up(K,32) * (round_up(Mrows,256) + round_up(N,128)) <= 5.9 M words, e.g. 1024 x 1024 x 1024 or
+ * 3152 x 768 x 768); larger problems return B200_ERR_WORKSPACE with a message naming both sizes.
+ * All calls on a device share the one array, which keeps the previous call's contents: what must start at zero is
+ * cleared on the stream at the start of each call, everything else is rewritten before it is read.  Calls that
+ * OVERLAP on the GPU (different streams, or host threads) race on it: serialise them. */
+size_t b200_static_scratch_bytes(void);
+int b200_qamaa_gemm_fbias_static(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n, float *C,
+                                 int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *maxval_dev, int n_bits,
+                                 float mantissa_bits, int sign_bits, const float *bA_dev, const float *bB_dev,
+                                 int64_t bB_stride, void *stream);
+
 /* ---- K3: the non-approx matmul on the tensor cores (tcgen05) ---------------------------------- */
 /* C = A @ B (+ bias) for FAKE-QUANTIZED operands; replaces `x @ y[:, i:i+1]` per column
  * (approx/approx_calculation.py:968-969 Linear, :796-797 BN-conv, :996 / :811 single column) and
