@@ -442,6 +442,8 @@ def run_ours(args):
     M, rows = args.mant_width, args.rows
     lib = pkg._lib.load()
     ops.set_autotune(True)       # measured tile choice: opt-in (the C ABI's default is "no host sync ever")
+    from fp8_quantization_b200 import quantization as _Q
+    _Q.enable_fusions(True)      # opt-in fused forward (input quantizer, fixed-weight cache, GEMM epilogue): same bits
 
     x_host, w_host, b_host = host_inputs(rows, M)
     layer = build_layer(M, dev, w_host, b_host)

@@ -44,6 +44,13 @@ class ActQuant(ctypes.Structure):
                 ("n_bits", ctypes.c_int32), ("sign_bits", ctypes.c_int32)]
 
 
+class Epilogue(ctypes.Structure):
+    """struct b200_epilogue (include/fp8approx_b200.h): fused +bias -> eval BN -> activation -> store."""
+    _fields_ = [("bias", ctypes.c_void_p), ("bn_mean", ctypes.c_void_p), ("bn_var", ctypes.c_void_p),
+                ("bn_gamma", ctypes.c_void_p), ("bn_beta", ctypes.c_void_p), ("bn_eps", ctypes.c_float),
+                ("act", ctypes.c_int32)]
+
+
 class ConvGeom(ctypes.Structure):
     """struct b200_conv_geom (conv geometry of QCustomBNConv2dTorch.run_forward, approx_calculation.py:822-857)."""
     _fields_ = [("batch", ctypes.c_int64), ("C_in", ctypes.c_int32), ("H", ctypes.c_int32), ("W", ctypes.c_int32),
@@ -77,6 +84,12 @@ SIGNATURES = {
                                           c_vp]),
     "b200_approx_conv2d_fbias_fq": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_vp, c_i64, c_vp,
                                             ctypes.POINTER(ApproxParams), ctypes.POINTER(ActQuant), c_vp, c_sz, c_vp]),
+    "b200_approx_gemm_fbias_ep": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp,
+                                          c_i64, c_vp, ctypes.POINTER(ApproxParams), ctypes.POINTER(ActQuant),
+                                          ctypes.POINTER(Epilogue), c_vp, c_sz, c_vp]),
+    "b200_approx_conv2d_fbias_ep": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_vp, c_i64, c_vp,
+                                            ctypes.POINTER(ApproxParams), ctypes.POINTER(ActQuant),
+                                            ctypes.POINTER(Epilogue), c_vp, c_sz, c_vp]),
     "b200_qamaa_gemm": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_int, c_f32,
                                 c_int, c_vp]),
     "b200_qamaa_gemm_workspace_bytes": (c_sz, [c_i64, c_i64, c_i64]),

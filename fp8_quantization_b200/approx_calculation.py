@@ -35,7 +35,8 @@ class _ApproxMixin:
         if y.shape[1] != 1:
             if self.approx_flag:
                 return ops.approx_matmul(x, y, x_bias, y_bias, res_bias, _ApproxMixin._params(self, False),
-                                         act_quant=self.__dict__.pop("_b200_act_quant", None))
+                                         act_quant=self.__dict__.pop("_b200_act_quant", None),
+                                         epilogue=self.__dict__.pop("_b200_ep_args", None))
             if self.quantize_after_mult_and_add:
                 q = self.res_quantizer.quantizer
                 return ops.qamaa_matmul(x, y, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits, x_bias=x_bias,
@@ -63,6 +64,10 @@ class QCustomLinearTorch(_ApproxMixin, QuantizationHijacker, nn.Linear):
         weight = weight.contiguous()
         lead = x.shape[:-1]
         x2 = x.reshape(-1, x.shape[-1]) if x.dim() != 2 else x
+        if self.approx_flag and weight.shape[0] != 1 and "_b200_epilogue" in self.__dict__:
+            # opt-in fused epilogue (quantization.FUSED_GEMM_EPILOGUE): `+ bias` and the activation inside the GEMM
+            self.__dict__["_b200_ep_args"] = dict(self.__dict__.pop("_b200_epilogue"), bias=bias)
+            bias = None
         output = self.approx_multiply(x2.detach(), weight.detach().t(), self.get_acts_fp_bias(),
                                       self.get_weights_fp_bias(), self.get_res_fp_bias())
         if bias is not None:
@@ -95,9 +100,13 @@ class _ConvMixin(_ApproxMixin):
         Ho, Wo = _conv_out_hw(H, W, kh, kw, self.stride, self.padding, self.dilation)
         Ng = Cout // self.groups
         if use_approx and self.approx_flag:
+            ep = self.__dict__.pop("_b200_epilogue", None)        # opt-in fused epilogue: the call returns final NCHW
             out = ops.approx_conv2d(x, weight, self.get_acts_fp_bias(), self.get_weights_fp_bias(),
                                     self.get_res_fp_bias(), _ApproxMixin._params(self, Ng == 1), self.stride, self.padding,
-                                    self.dilation, self.groups, act_quant=self.__dict__.pop("_b200_act_quant", None))
+                                    self.dilation, self.groups, act_quant=self.__dict__.pop("_b200_act_quant", None),
+                                    epilogue=dict(ep, bias=bias) if ep is not None else None)
+            if ep is not None:
+                return out
         elif use_approx and self.quantize_after_mult_and_add and Ng != 1:
             q = self.res_quantizer.quantizer
             out = ops.qamaa_conv2d(x, weight, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits, self.stride,

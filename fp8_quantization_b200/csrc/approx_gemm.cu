@@ -30,6 +30,7 @@
 #include "pair_math.cuh"
 #include "qamaa_op.cuh"
 #include "tables.h"
+#include "epilogue.cuh"
 #include "gemm_impl.cuh"
 
 namespace b200 {
@@ -563,6 +564,7 @@ struct LutGemmArgs {
     // exactness certificate as split-K (`splits` = upper bound of segments per tile).
     int sk_ctas, sk_tiles_n;
     int64_t sk_tiles;
+    Epilogue ep;          // fused +bias -> BN -> activation -> (NCHW) store, epilogue.cuh; ep.on == 0: plain store
 };
 
 // KT: k-tile depth (8 where a large table leaves little shared memory for the operand ring).
@@ -794,6 +796,66 @@ approx_gemm_lut_kernel(LutGemmArgs a)
             for (int j = 0; j < CPL; ++j) acc[i][j] = q.quant(acc[i][j] * unit) / unit;   // stored below as acc * unit
     }
     const int64_t n = n0 + lane * CPL;
+    if (a.ep.on) {
+        // fused epilogue (epilogue.cuh): the lane owns CPL fixed columns = output channels, so their bias / BN
+        // constants live in registers; the final values are computed here
+        Epilogue::Col ec[CPL];
+#pragma unroll
+        for (int j = 0; j < CPL; ++j) ec[j] = a.ep.column(n + j < a.N ? n + j : a.N - 1);
+#pragma unroll
+        for (int i = 0; i < RPW; ++i)
+#pragma unroll
+            for (int j = 0; j < CPL; ++j) acc[i][j] = a.ep.apply(acc[i][j] * unit, ec[j]);
+        if (a.ep.HW > 0) {
+            // NCHW store.  A warp holds RPW consecutive rows (pixels) of 32 * CPL channels: transposed through a
+            // warp-private patch of the (now idle) operand ring, one column of every lane per pass, so that a
+            // store instruction writes runs of RPW consecutive pixels (RPW * 4 contiguous bytes per channel).
+            static_assert(RPW == 16 || RPW == 32, "the transposing store assumes 16 or 32 rows per warp");
+            static_assert((size_t)ST * KT * (BM + BN) * 4 >= (size_t)WARPS * 32 * (RPW + 1) * 4, "staging patch fits the operand ring");
+            __syncthreads();   // every warp is done reading operand stages (no cp.async is in flight: wait<0> above)
+            float* patch = reinterpret_cast<float*>(As) + warp * (32 * (RPW + 1));
+            const int row = lane % RPW, cgrp = lane / RPW;           // this lane's row in the store phase
+            constexpr int CPI = 32 / RPW;                            // channels per store instruction
+            const int64_t m = m0 + warp * RPW + row;
+            const int64_t bimg = m / a.ep.HW, pix = m - bimg * a.ep.HW;
+            float* obase = a.C + (bimg * a.ep.Ctot + a.ep.c0) * a.ep.HW + pix;
+#pragma unroll
+            for (int j = 0; j < CPL; ++j) {
+#pragma unroll
+                for (int i = 0; i < RPW; ++i) patch[lane * (RPW + 1) + i] = acc[i][j];
+                __syncwarp();
+                if (m < a.Mrows) {
+#pragma unroll 4
+                    for (int c = cgrp; c < 32; c += CPI) {
+                        const int64_t nn = n0 + c * CPL + j;
+                        if (nn < a.N) obase[nn * a.ep.HW] = patch[c * (RPW + 1) + row];
+                    }
+                }
+                __syncwarp();
+            }
+            if (streamk) __syncthreads();   // the next segment's prologue overwrites the ring
+            continue;
+        }
+        // row-major: the plain store below, with the scaling already applied
+        const bool vec = ((a.ldc & (CPL - 1)) == 0) && ((reinterpret_cast<uintptr_t>(a.C) & (4 * CPL - 1)) == 0) &&
+                         (n + CPL - 1 < a.N);
+#pragma unroll
+        for (int i = 0; i < RPW; ++i) {
+            const int64_t m = m0 + warp * RPW + i;
+            if (m >= a.Mrows) break;
+            float* crow = a.C + m * a.ldc;
+            if (vec && CPL == 4) {
+                *reinterpret_cast<float4*>(crow + n) = make_float4(acc[i][0], acc[i][1], acc[i][CPL - 2], acc[i][CPL - 1]);
+            } else if (vec) {
+                *reinterpret_cast<float2*>(crow + n) = make_float2(acc[i][0], acc[i][1]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < CPL; ++j)
+                    if (n + j < a.N) crow[n + j] = acc[i][j];
+            }
+        }
+        continue;
+    }
     const bool vec = ((a.ldc & (CPL - 1)) == 0) && ((reinterpret_cast<uintptr_t>(a.C) & (4 * CPL - 1)) == 0) &&
                      (n + CPL - 1 < a.N);
 #pragma unroll
@@ -821,7 +883,7 @@ __global__ void __launch_bounds__(256) streamk_fixup_kernel(const float* __restr
                                                             int nk_all, int BM, int BN, float* __restrict__ C, int64_t ldc,
                                                             int64_t Mrows, int64_t N, BiasSrc bias, int M, int qamaa,
                                                             QamaaOp qop, const int* __restrict__ inexact,
-                                                            const int* __restrict__ offgrid)
+                                                            const int* __restrict__ offgrid, Epilogue ep)
 {
     if (*inexact != 0 || *offgrid != 0) return;
     const int64_t U = tiles * nk_all, tile = blockIdx.x;
@@ -847,7 +909,7 @@ __global__ void __launch_bounds__(256) streamk_fixup_kernel(const float* __restr
         }
         s *= unit;
         if (qamaa) s = qop.quant(s);
-        C[(m0 + r) * ldc + n0 + c] = s;
+        ep.store(C, ldc, m0 + r, n0 + c, s);
     }
 }
 
@@ -855,7 +917,7 @@ __global__ void __launch_bounds__(256) streamk_fixup_kernel(const float* __restr
 __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ P, int splits, float* __restrict__ C,
                                                             int64_t ldc, int64_t Mrows, int64_t N, BiasSrc bias, int M,
                                                             int qamaa, QamaaOp qop, const int* __restrict__ inexact,
-                                                            const int* __restrict__ offgrid)
+                                                            const int* __restrict__ offgrid, Epilogue ep)
 {
     if (*inexact != 0 || *offgrid != 0) return;
     const float unit = pow2f_i(1 - bias.R() - M);
@@ -867,7 +929,51 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
         s *= unit;
         if (qamaa) s = qop.quant(s);
         const int64_t m = i / N;
-        C[m * ldc + (i - m * N)] = s;
+        ep.store(C, ldc, m, i - m * N, s);
+    }
+}
+
+// Same, for a fused epilogue with an NCHW store (epilogue.cuh): 32 rows x 32 columns per CTA, slices read with lanes
+// along the columns (contiguous in the partial sums), transposed through shared memory, stored with lanes along the
+// rows (= pixels, contiguous in NCHW).  grid (ceil(Mrows / 32), ceil(N / 32)), 256 threads.
+__global__ void __launch_bounds__(256) splitk_reduce_nchw_kernel(const float* __restrict__ P, int splits, float* __restrict__ C,
+                                                                 int64_t Mrows, int64_t N, BiasSrc bias, int M, int qamaa,
+                                                                 QamaaOp qop, const int* __restrict__ inexact,
+                                                                 const int* __restrict__ offgrid, Epilogue ep)
+{
+    if (*inexact != 0 || *offgrid != 0) return;
+    __shared__ float tile[32][33];
+    const float unit = pow2f_i(1 - bias.R() - M);
+    if (qamaa) qop.begin();
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int64_t m0 = (int64_t)blockIdx.x * 32, n0 = (int64_t)blockIdx.y * 32, total = Mrows * N;
+    const int64_t n = n0 + tx;
+    const Epilogue::Col ec = ep.column(n < N ? n : N - 1);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = ty + 8 * i;
+        const int64_t m = m0 + r;
+        float s = 0.0f;
+        if (m < Mrows && n < N) {
+            const int64_t e = m * N + n;
+            s = P[e];
+            for (int z = 1; z < splits; ++z) s += P[(int64_t)z * total + e];
+            s *= unit;
+            if (qamaa) s = qop.quant(s);
+            s = ep.apply(s, ec);
+        }
+        tile[r][tx] = s;
+    }
+    __syncthreads();
+    const int64_t m = m0 + tx;
+    if (m < Mrows) {
+        const int64_t bimg = m / ep.HW, pix = m - bimg * ep.HW;
+        float* obase = C + (bimg * ep.Ctot + ep.c0) * ep.HW + pix;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int c = ty + 8 * i;
+            if (n0 + c < N) obase[(n0 + c) * ep.HW] = tile[tx][c];
+        }
     }
 }
 
@@ -1196,7 +1302,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
                         int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const LutGeom& geom,
                         const uint16_t* d_lut, int lut_bytes, int* flag, uint32_t* Aw, uint32_t* Bw, int64_t Mpad,
                         int64_t Npad, int64_t Kpad, const QamaaOp* qop, float* partial, void* conv_ws, size_t conv_ws_bytes,
-                        cudaStream_t st)
+                        cudaStream_t st, const Epilogue& ep = Epilogue{})
 {
     const int M = geom.M;
     static PerDeviceOnce once;
@@ -1280,6 +1386,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     if (qop) la.qop = *qop; else la.qop = QamaaOp{};
     la.partial = partial; la.inexact = flag + 6; la.tmax = flag + 4; la.t_bias = geom.RA + M + 2;
     la.cp = cp;
+    la.ep = ep;
     // one (tile, split) configuration: the GEMM, and for split-K the ordered reduction plus the gated unsplit kernel
     auto launch = [&](const LutTileCfg* cfg, int splits) -> int {
         LutGemmArgs l = la;
@@ -1295,15 +1402,19 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
             B200_LAUNCH_CHECK("approx_gemm_lut_kernel(stream-K)");
             streamk_fixup_kernel<<<(unsigned)tiles, 256, 0, st>>>(partial, (int)G, tiles, (int)tgrid.y, (int)nk_all, cfg->BM(),
                                                                   cfg->BN(), C, ldc, Mrows, N, bias, M, l.qamaa, l.qop,
-                                                                  flag + 6, flag);
+                                                                  flag + 6, flag, ep);
             B200_LAUNCH_CHECK("streamk_fixup_kernel");
         } else {
             (gather ? cfg->conv_kernel : cfg->kernel)<<<tgrid, 32 * cfg->warps, cfg->smem(lut_bytes), st>>>(l);
         }
         if (splits > 1) {
             B200_LAUNCH_CHECK("approx_gemm_lut_kernel(split-K)");
-            splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(Mrows * N, 256), 4 * sms), 256, 0, st>>>(
-                partial, splits, C, ldc, Mrows, N, bias, M, l.qamaa, l.qop, flag + 6, flag);
+            if (ep.on && ep.HW > 0)
+                splitk_reduce_nchw_kernel<<<dim3((unsigned)ceil_div(Mrows, 32), (unsigned)ceil_div(N, 32)), 256, 0, st>>>(
+                    partial, splits, C, Mrows, N, bias, M, l.qamaa, l.qop, flag + 6, flag, ep);
+            else
+                splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(Mrows * N, 256), 4 * sms), 256, 0, st>>>(
+                    partial, splits, C, ldc, Mrows, N, bias, M, l.qamaa, l.qop, flag + 6, flag, ep);
             B200_LAUNCH_CHECK("splitk_reduce_kernel");
         }
         if (splits != 1) {
@@ -1422,8 +1533,9 @@ size_t b200::conv_gather_workspace_bytes(int64_t nB, int64_t Cg, int64_t H, int6
 // implicit-im2col view of an NCHW tensor.
 int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc,
                            int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const b200_approx_params* p,
-                           void* workspace, size_t workspace_bytes, void* stream)
+                           void* workspace, size_t workspace_bytes, void* stream, const Epilogue* epp)
 {
+    const Epilogue ep = epp ? *epp : Epilogue{};
     if (int rc = check_device()) return rc;
     if (!p || Mrows < 0 || K < 0 || N < 0) { set_error("b200_approx_gemm: bad argument"); return B200_ERR_ARGUMENT; }
     const int E = p->expo_width, M = p->mant_width;
@@ -1472,7 +1584,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
             return rc;
     }
     if (!lut || lut->flags.sign_quirk || lut->flags.unrepresentable) {
-        pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, nullptr, 0);
+        pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, nullptr, 0, ep);
         B200_LAUNCH_CHECK("pair_gemm_kernel<ApproxPairOp>");
         set_path(v5 ? "generic-v5" : "generic");
         return B200_OK;
@@ -1498,10 +1610,10 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     void* conv_ws = workspace_bytes > words + pbytes ? reinterpret_cast<char*>(workspace) + words + pbytes : nullptr;
     const size_t conv_ws_bytes = conv_ws ? workspace_bytes - words - pbytes : 0;
     if (int rc = run_lut_gemm(A, B, sb_k, sb_n, C, ldc, Mrows, K, N, bias, lut->geom, lut->d_lut, lut->lut_bytes, flag,
-                              Aw, Bw, Mpad, Npad, Kpad, nullptr, partial, conv_ws, conv_ws_bytes, st))
+                              Aw, Bw, Mpad, Npad, Kpad, nullptr, partial, conv_ws, conv_ws_bytes, st, ep))
         return rc;
     // runs only if the predecode found an off-grid operand
-    pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
+    pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1, ep);
     B200_LAUNCH_CHECK("pair_gemm_kernel<ApproxPairOp>(conditional)");
     if (v5) { set_path("lut-v5"); return B200_OK; }
     set_path(lut->geom.sidx ? "lut-signed" : (g_last_splits > 1 ? "lut-splitk" : (g_last_splits == 0 ? "lut-streamk" : "lut")));
@@ -1604,6 +1716,37 @@ extern "C" int b200_approx_gemm_fbias_fq(const float* A, int64_t lda, const floa
     ASrc a = make_gemm_asrc(A, lda);
     if (int rc = apply_act_quant(&a, aq)) return rc;
     return approx_gemm_impl(a, B, sb_k, sb_n, C, ldc, Mrows, K, N, b, p, workspace, workspace_bytes, stream);
+}
+
+int b200::make_epilogue(const b200_epilogue* e, Epilogue* out)
+{
+    *out = Epilogue{};
+    if (!e) return B200_OK;
+    if (e->act < 0 || e->act > 2) { set_error("b200_epilogue: act must be 0 (none), 1 (ReLU) or 2 (ReLU6)"); return B200_ERR_ARGUMENT; }
+    if (e->bn_mean && !e->bn_var) { set_error("b200_epilogue: bn_mean without bn_var"); return B200_ERR_ARGUMENT; }
+    out->on = 1;
+    out->bias = e->bias;
+    out->mean = e->bn_mean; out->var = e->bn_var; out->gamma = e->bn_gamma; out->beta = e->bn_beta;
+    out->eps = e->bn_eps;
+    out->act = e->act;
+    return B200_OK;
+}
+
+extern "C" int b200_approx_gemm_fbias_ep(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n,
+                                         float* C, int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float* bA_dev,
+                                         const float* bB_dev, int64_t bB_stride, const float* bR_dev,
+                                         const b200_approx_params* p, const b200_act_quant* aq, const b200_epilogue* ep,
+                                         void* workspace, size_t workspace_bytes, void* stream)
+{
+    if (!p) { set_error("b200_approx_gemm_fbias_ep: params is NULL"); return B200_ERR_ARGUMENT; }
+    const int dflt = 1 << (p->expo_width > 0 ? p->expo_width - 1 : 0);
+    BiasSrc b{dflt, dflt, bA_dev, bR_dev, nullptr, bB_dev, bB_stride};
+    ASrc a = make_gemm_asrc(A, lda);
+    if (int rc = apply_act_quant(&a, aq)) return rc;
+    Epilogue e;
+    if (int rc = make_epilogue(ep, &e)) return rc;
+    e.Ctot = (int)N;    // row-major store: channel == column
+    return approx_gemm_impl(a, B, sb_k, sb_n, C, ldc, Mrows, K, N, b, p, workspace, workspace_bytes, stream, ep ? &e : nullptr);
 }
 
 extern "C" int b200_approx_gemm_fbias(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n,

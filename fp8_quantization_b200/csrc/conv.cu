@@ -43,6 +43,7 @@ struct DwArgs {
     BiasSrc bias;
     PairCfg cfg;
     const signed char* T;
+    Epilogue ep;         // fused +bias -> BN -> activation -> NCHW store (epilogue.cuh); on == 0: plain [rows, groups]
 };
 
 __global__ void __launch_bounds__(256) approx_dw_kernel(DwArgs d, const int* __restrict__ gate, int gate_run_if_nonzero)
@@ -78,7 +79,7 @@ __global__ void __launch_bounds__(256) approx_dw_kernel(DwArgs d, const int* __r
         const int ml = ty + 8 * i;
         const int64_t mm = (int64_t)blockIdx.x * 32 + ml;
         const int g = blockIdx.y * 32 + tx;
-        if (mm < d.rows && g < d.groups) d.out[mm * d.groups + g] = tile[tx][ml];
+        if (mm < d.rows && g < d.groups) d.ep.store(d.out, d.groups, mm, g, tile[tx][ml]);
     }
 }
 
@@ -100,6 +101,7 @@ struct DwLutArgs {
     const uint16_t* lut;
     int lut_bytes;
     int* flag;
+    Epilogue ep;         // as in DwArgs; the NCHW store needs no transposition here (rows run across lanes)
 };
 
 // Weight fields are decoded once per (group, k) of a tile into `wpart` (they are the same for every row), the
@@ -171,6 +173,12 @@ __global__ void __launch_bounds__(256, 3) approx_dw_lut_kernel(DwLutArgs d)
             }
             wpart[i] = wp;
         }
+        const bool ep_nchw = d.ep.on && d.ep.HW > 0;
+        Epilogue::Col* ecol = reinterpret_cast<Epilogue::Col*>(&tile[0][0]);   // the transposition tile is idle then
+        if (ep_nchw && threadIdx.x < 32) {
+            const int grp = gt * 32 + threadIdx.x;
+            ecol[threadIdx.x] = d.ep.column(grp < d.groups ? grp : d.groups - 1);
+        }
         __syncthreads();
         const int64_t m = rt * 32 + tx;
         int wo, ho;
@@ -235,15 +243,22 @@ __global__ void __launch_bounds__(256, 3) approx_dw_lut_kernel(DwLutArgs d)
                     }
                 }
             }
-            tile[gl][tx] = acc * unit;
+            if (ep_nchw) {
+                // rows (= pixels) run across the lanes: the NCHW store is coalesced as it stands
+                if (grp < d.groups && m < d.rows)
+                    d.out[((b * d.ep.Ctot + d.ep.c0 + grp) * (int64_t)s.Ho + ho) * s.Wo + wo] = d.ep.apply(acc * unit, ecol[gl]);
+            } else {
+                tile[gl][tx] = acc * unit;
+            }
         }
+        if (ep_nchw) continue;
         __syncthreads();
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int ml = ty + 8 * i;
             const int64_t mm = rt * 32 + ml;
             const int grp = gt * 32 + tx;
-            if (mm < d.rows && grp < d.groups) d.out[mm * d.groups + grp] = tile[tx][ml];
+            if (mm < d.rows && grp < d.groups) d.ep.store(d.out, d.groups, mm, grp, tile[tx][ml]);
         }
     }
     if (off) *d.flag = 1;
@@ -372,7 +387,16 @@ extern "C" size_t b200_approx_conv2d_workspace_bytes(const b200_conv_geom* g)
 
 static int approx_conv2d_impl(const float* x, const float* w, float* out, const b200_conv_geom* g, const float* bA_dev,
                               const float* bB_dev, int64_t bB_stride, const float* bR_dev, const b200_approx_params* p,
-                              const b200_act_quant* aq, void* workspace, size_t workspace_bytes, void* stream);
+                              const b200_act_quant* aq, void* workspace, size_t workspace_bytes, void* stream,
+                              const b200_epilogue* ep = nullptr);
+
+extern "C" int b200_approx_conv2d_fbias_ep(const float* x, const float* w, float* out, const b200_conv_geom* g,
+                                           const float* bA_dev, const float* bB_dev, int64_t bB_stride,
+                                           const float* bR_dev, const b200_approx_params* p, const b200_act_quant* aq,
+                                           const b200_epilogue* ep, void* workspace, size_t workspace_bytes, void* stream)
+{
+    return approx_conv2d_impl(x, w, out, g, bA_dev, bB_dev, bB_stride, bR_dev, p, aq, workspace, workspace_bytes, stream, ep);
+}
 
 extern "C" int b200_approx_conv2d_fbias(const float* x, const float* w, float* out, const b200_conv_geom* g,
                                         const float* bA_dev, const float* bB_dev, int64_t bB_stride,
@@ -392,13 +416,21 @@ extern "C" int b200_approx_conv2d_fbias_fq(const float* x, const float* w, float
 
 static int approx_conv2d_impl(const float* x, const float* w, float* out, const b200_conv_geom* g, const float* bA_dev,
                               const float* bB_dev, int64_t bB_stride, const float* bR_dev, const b200_approx_params* p,
-                              const b200_act_quant* aq, void* workspace, size_t workspace_bytes, void* stream)
+                              const b200_act_quant* aq, void* workspace, size_t workspace_bytes, void* stream,
+                              const b200_epilogue* epp)
 {
     if (int rc = check_device()) return rc;
     ConvDims d;
     if (int rc = conv_dims(g, &d)) return rc;
     if (!p) { set_error("b200_approx_conv2d: params is NULL"); return B200_ERR_ARGUMENT; }
     const int dflt = 1 << (p->expo_width > 0 ? p->expo_width - 1 : 0);   // approx_calculation.py:766-767
+    Epilogue ep;
+    if (int rc = make_epilogue(epp, &ep)) return rc;
+    if (ep.on) {          // conv form: the output is the final NCHW tensor
+        ep.HW = (int64_t)d.Ho * d.Wo;
+        ep.Ctot = g->C_out;
+        if (ep.HW <= 0) return B200_OK;
+    }
     if (d.Ng != 1) {
         b200_approx_params pp = *p;
         pp.single_column_quirk = 0;
@@ -408,8 +440,10 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
             const float* wg = w + (int64_t)grp * d.Ng * d.Kg;
             ASrc av = make_conv_asrc(x, g, d, grp);
             if (int rc = apply_act_quant(&av, aq)) return rc;
-            if (int rc = approx_gemm_impl(av, wg, 1, d.Kg, out + (int64_t)grp * d.Ng,
-                                          g->C_out, d.rows, d.Kg, d.Ng, b, &pp, workspace, workspace_bytes, stream))
+            ep.c0 = grp * d.Ng;
+            if (int rc = approx_gemm_impl(av, wg, 1, d.Kg, ep.on ? out : out + (int64_t)grp * d.Ng,
+                                          g->C_out, d.rows, d.Kg, d.Ng, b, &pp, workspace, workspace_bytes, stream,
+                                          ep.on ? &ep : nullptr))
                 return rc;
         }
         return B200_OK;
@@ -441,6 +475,7 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
     a.cfg.qbma = p->quant_btw_mult_accu != 0;
     a.cfg.quirk = true;
     a.T = a.cfg.with_approx ? dev_table : nullptr;
+    a.ep = ep;           // c0 = 0: group == output channel
     if (v5) {
         a.cfg.v5 = true; a.cfg.quirk = false;
         a.cfg.sim_ofuf = p->sim_hw_add_OFUF != 0; a.cfg.of_opt = p->with_OF_opt != 0; a.cfg.uf_opt = p->with_UF_opt != 0;
@@ -473,6 +508,7 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
             la.a = a.a; la.w = w; la.out = out; la.rows = d.rows; la.groups = g->groups; la.Kg = d.Kg; la.Cg = d.Cg;
             la.n_row_tiles = ceil_div(d.rows, 32); la.n_grp_tiles = (int)ceil_div(g->groups, 32);
             la.bias = a.bias; la.flag = reinterpret_cast<int*>(workspace);
+            la.ep = ep;
             B200_CUDA_TRY(cudaMemsetAsync(la.flag, 0, 4, st));
             const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (227 * 1024) / (smem + 1024)));
             const int64_t tiles = la.n_row_tiles * la.n_grp_tiles;

@@ -1,6 +1,7 @@
 // gemm_impl.cuh -- internal interface between the C-ABI entry points (approx_gemm.cu, conv.cu).
 #pragma once
 #include "common.cuh"
+#include "epilogue.cuh"
 #include "lut.cuh"
 #include "pair_gemm.cuh"
 
@@ -33,7 +34,10 @@ int get_quirk_lut(int E, int M, const signed char* host_table, const signed char
 
 int approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_n, float* C, int64_t ldc,
                      int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const b200_approx_params* p,
-                     void* workspace, size_t workspace_bytes, void* stream);
+                     void* workspace, size_t workspace_bytes, void* stream, const Epilogue* ep = nullptr);
+
+// b200_epilogue (C ABI) -> Epilogue; HW / Ctot / c0 are set by the caller (conv form).  B200_OK or an argument error.
+int make_epilogue(const b200_epilogue* e, Epilogue* out);
 
 // extra workspace (beyond the GEMM-form bytes) with which the conv form decodes the input once and lets the
 // table GEMM do the im2col gather (approx_gemm.cu)

@@ -13,6 +13,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "epilogue.cuh"
 #include "pair_math.cuh"
 
 namespace b200 {
@@ -84,7 +85,8 @@ constexpr int PG_BM = 64, PG_BN = 64, PG_KT = 16, PG_LD = 68;
 template <class Op>
 __global__ void __launch_bounds__(256) pair_gemm_kernel(ASrc A, BSrc B, float* __restrict__ C, int64_t ldc,
                                                         int64_t Mrows, int64_t K, int64_t N, Op op,
-                                                        const int* __restrict__ gate, int gate_run_if_nonzero)
+                                                        const int* __restrict__ gate, int gate_run_if_nonzero,
+                                                        Epilogue ep = Epilogue{})
 {
     if (gate) {
         const int g = *gate;
@@ -156,7 +158,7 @@ __global__ void __launch_bounds__(256) pair_gemm_kernel(ASrc A, BSrc B, float* _
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int64_t n = n0 + tx * 4 + j;
-            if (n < N) C[m * ldc + n] = op.finish(acc[i][j], col[j]);
+            if (n < N) ep.store(C, ldc, m, n, op.finish(acc[i][j], col[j]));
         }
     }
 }

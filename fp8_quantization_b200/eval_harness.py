@@ -145,14 +145,25 @@ class GraphedForward:
                     y_static = self.model(x_static)
                     dist.all_gather_into_tensor(gathered, y_static.float().contiguous(), group=self.group)
                 self.collective_in_graph = True
-                return g, x_static, y_static, gathered, dict(ops._WORKSPACES)
+                return g, x_static, y_static, gathered, self._keepalive(ops)
             except Exception:    # the collective is not capturable on this stack: graph the forward only
                 self.collective_in_graph = False
                 torch.cuda.synchronize(x.device)
         g = torch.cuda.CUDAGraph()
         with torch.inference_mode(), torch.cuda.graph(g):
             y_static = self.model(x_static)
-        return g, x_static, y_static, None, dict(ops._WORKSPACES)
+        return g, x_static, y_static, None, self._keepalive(ops)
+
+    def _keepalive(self, ops):
+        """What the captured kernels read by address and nobody else is guaranteed to keep: the package's workspaces and
+        the layers' cached quantized weights (quantization.CACHE_FIXED_WEIGHTS; a later forward with another setting, or
+        a weight update, drops the cache entry -- the graph must still own the tensors it was captured with)."""
+        cached = [m.__dict__["_b200_wcache"] for m in self.model.modules() if "_b200_wcache" in m.__dict__]
+        # ... and the quantizers' range / exponent-bias tensors: plain attributes that a later eager forward REPLACES
+        # (FPQuantizer.forward assigns a fresh custom_bias on every call, fp8_quantizer.py:244)
+        for m in self.model.modules():
+            cached += [t for t in (getattr(m, "custom_bias", None), getattr(m, "maxval", None)) if torch.is_tensor(t)]
+        return dict(ops._WORKSPACES), cached
 
 
 _N_CLASSES = {}

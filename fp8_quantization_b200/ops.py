@@ -124,7 +124,31 @@ def _act_quant_struct(act_quant, device):
     return aq, (mv, bs)
 
 
-def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out=None, act_quant=None):
+def _epilogue_struct(epilogue, n_channels, device):
+    """dict(bias=, bn=(mean, var, gamma, beta, eps), act=0|1|2) -> (struct b200_epilogue, tensors kept alive).
+    Every per-channel tensor must have n_channels elements."""
+    keep = []
+
+    def vec(t):
+        if t is None:
+            return None
+        t = t.detach().to(device=device, dtype=torch.float32).reshape(-1).contiguous()
+        if t.numel() != n_channels:
+            raise ValueError(f"epilogue: expected {n_channels} per-channel values, got {t.numel()}")
+        keep.append(t)
+        return t.data_ptr()
+    ep = _lib.Epilogue()
+    ep.bias = vec(epilogue.get("bias"))
+    bn = epilogue.get("bn")
+    if bn is not None:
+        mean, var, gamma, beta, eps = bn
+        ep.bn_mean, ep.bn_var, ep.bn_gamma, ep.bn_beta = vec(mean), vec(var), vec(gamma), vec(beta)
+        ep.bn_eps = float(eps)
+    ep.act = int(epilogue.get("act", 0))
+    return ep, keep
+
+
+def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out=None, act_quant=None, epilogue=None):
     """C = approx_multiply(x [Mrows,K], y [K,N]) in ONE launch sequence.
 
     Biases, two forms:
@@ -136,6 +160,8 @@ def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out
     `y` may be any strided view (e.g. weight.t()).
     `act_quant` = (maxval, bias, mantissa_bits, n_bits, sign_bits): `x` holds RAW activations and the input
     fake-quantizer runs inside the operand decode pass (b200_approx_gemm_fbias_fq); bit-identical to quantizing first.
+    `epilogue` = dict(bias=[N], bn=(mean, var, gamma, beta, eps), act=0|1|2), all optional (opt-in):
+    `+ bias`, eval batch norm and ReLU / ReLU6 evaluated in the GEMM's epilogue (b200_approx_gemm_fbias_ep).
     """
     lib = _lib.load()
     _require_cuda(x, y)
@@ -158,8 +184,8 @@ def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out
     nbytes = lib.b200_approx_gemm_workspace_bytes(Mrows, K, N)
     ws = _workspace(x.device, nbytes)
     int_path = isinstance(x_bias, int) and isinstance(res_bias, int)
-    if act_quant is not None and int_path:
-        raise ValueError("the fused input quantizer needs the device-bias form of the call")
+    if (act_quant is not None or epilogue is not None) and int_path:
+        raise ValueError("the fused input quantizer / epilogue need the device-bias form of the call")
     with torch.cuda.device(x.device):
         if int_path:
             if isinstance(y_bias, int):
@@ -189,7 +215,14 @@ def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out
                 if fb.numel() < N:
                     raise IndexError("index out of range: y_bias has fewer entries than output columns")
                 sB = fb.stride(0)
-            if act_quant is not None:
+            if epilogue is not None:
+                aq, alive = _act_quant_struct(act_quant, x.device) if act_quant is not None else (None, None)
+                ep, alive2 = _epilogue_struct(epilogue, N, x.device)
+                rc = lib.b200_approx_gemm_fbias_ep(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out),
+                                                   out.stride(0), Mrows, K, N, _ptr(fa), _ptr(fb), sB, _ptr(fr),
+                                                   ctypes.byref(params), ctypes.byref(aq) if aq is not None else None,
+                                                   ctypes.byref(ep), _ptr(ws), ws.numel(), _stream())
+            elif act_quant is not None:
                 aq, alive = _act_quant_struct(act_quant, x.device)
                 rc = lib.b200_approx_gemm_fbias_fq(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out),
                                                    out.stride(0), Mrows, K, N, _ptr(fa), _ptr(fb), sB, _ptr(fr),
@@ -333,17 +366,23 @@ def exact_grouped_conv2d(x, weight, stride, padding, dilation, groups):
     return out
 
 
-def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, dilation, groups, act_quant=None):
+def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, dilation, groups, act_quant=None,
+                  epilogue=None):
     """im2col + group loop + approx_multiply of QCustomBNConv2dTorch.run_forward
     (approx/approx_calculation.py:846-906) in one C-ABI call.  Returns [B*Ho*Wo, C_out] fp32.
-    Biases are the fake-quantizers' fp32 tensors (or None -> 2^(E-1)); read on the device."""
+    Biases are the fake-quantizers' fp32 tensors (or None -> 2^(E-1)); read on the device.
+    `epilogue` (opt-in, see approx_matmul): the call then returns the FINAL tensor, contiguous NCHW
+    [B, C_out, Ho, Wo] = act(bn(conv + bias)) (b200_approx_conv2d_fbias_ep)."""
     lib = _lib.load()
     _require_cuda(x, weight)
     x = x.float().contiguous()
     weight = weight.float().contiguous()
     g = conv_geom(x.shape, weight.shape, stride, padding, dilation, groups)
-    rows, _, _, _, _ = conv_out_shape(g)
-    out = torch.empty((rows, g.C_out), dtype=torch.float32, device=x.device)
+    rows, ho, wo, _, _ = conv_out_shape(g)
+    if epilogue is not None:
+        out = torch.empty((g.batch, g.C_out, ho, wo), dtype=torch.float32, device=x.device)
+    else:
+        out = torch.empty((rows, g.C_out), dtype=torch.float32, device=x.device)
     fa, fr = _dev_scalar(x_bias, x.device), _dev_scalar(res_bias, x.device)
     fb = w_bias if torch.is_tensor(w_bias) else torch.tensor([float(w_bias if w_bias is not None else
                                                                     2 ** (params.expo_width - 1))])
@@ -357,7 +396,14 @@ def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, 
     nbytes = lib.b200_approx_conv2d_workspace_bytes(ctypes.byref(g))
     ws = _workspace(x.device, nbytes) if nbytes else None
     with torch.cuda.device(x.device):
-        if act_quant is not None:
+        if epilogue is not None:
+            aq, alive = _act_quant_struct(act_quant, x.device) if act_quant is not None else (None, None)
+            ep, alive2 = _epilogue_struct(epilogue, g.C_out, x.device)
+            rc = lib.b200_approx_conv2d_fbias_ep(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(fa), _ptr(fb), sB,
+                                                 _ptr(fr), ctypes.byref(params),
+                                                 ctypes.byref(aq) if aq is not None else None, ctypes.byref(ep), _ptr(ws),
+                                                 ws.numel() if ws is not None else 0, _stream())
+        elif act_quant is not None:
             aq, alive = _act_quant_struct(act_quant, x.device)
             rc = lib.b200_approx_conv2d_fbias_fq(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(fa), _ptr(fb), sB,
                                                  _ptr(fr), ctypes.byref(params), ctypes.byref(aq), _ptr(ws),

@@ -239,6 +239,32 @@ int b200_approx_gemm_fbias_fq(const float *A, int64_t lda, const float *B, int64
                               const b200_approx_params *p, const b200_act_quant *aq, void *workspace,
                               size_t workspace_bytes, void *stream);
 
+/* ---- N2: fused epilogue (OPT-IN: the entry points above keep the reference's pass structure) --- */
+/* What the reference does to a layer's product sums before the next layer reads them, evaluated in the epilogue of
+ * the GEMM / conv kernels instead of as separate passes over the output, in the reference's operation order
+ * (bit-identical to the unfused sequence):
+ *   v = acc;  v += bias[c]           `output += bias`, approx/approx_calculation.py:1020-1021 (Linear), :911-912 (conv)
+ *   v = fma(v, alpha[c], beta'[c])   F.batch_norm(eval), quantization/quantized_folded_bn.py:66-72, op order of ATen's CPU
+ *                                    kernel: invstd = 1/sqrt(var+eps), alpha = gamma*invstd, beta' = fma(-mean, alpha, beta)
+ *                                    (== b200_bn_act below)
+ *   v = relu / relu6 (v)             quantized_folded_bn.py:74-75, quantization/hijacker.py:108-109
+ *   store                            GEMM form: C[m*ldc + n];  conv form: contiguous NCHW [batch, C_out, Ho, Wo] (the
+ *                                    view + permute of approx_calculation.py:909-910 made real)
+ * All pointers are DEVICE pointers to [N] (GEMM) / [C_out] (conv) fp32 arrays, or NULL: bias NULL = no bias;
+ * bn_mean NULL = no batch norm (bn_var then ignored); bn_gamma / bn_beta NULL = 1 / 0. */
+typedef struct b200_epilogue {
+    const float *bias;
+    const float *bn_mean, *bn_var, *bn_gamma, *bn_beta;
+    float bn_eps;
+    int32_t act; /* 0 none, 1 ReLU, 2 ReLU6 */
+} b200_epilogue;
+/* b200_approx_gemm_fbias_fq with the epilogue (aq and ep may each be NULL) */
+int b200_approx_gemm_fbias_ep(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n, float *C,
+                              int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *bA_dev,
+                              const float *bB_dev, int64_t bB_stride, const float *bR_dev,
+                              const b200_approx_params *p, const b200_act_quant *aq, const b200_epilogue *ep,
+                              void *workspace, size_t workspace_bytes, void *stream);
+
 /* ---- A9: conv form, QCustomBNConv2dTorch.run_forward, approx/approx_calculation.py:822-917 -------- */
 typedef struct b200_conv_geom {
     int64_t batch;
@@ -273,6 +299,13 @@ int b200_approx_conv2d_fbias_fq(const float *x, const float *w, float *out, cons
                                 const float *bA_dev, const float *bB_dev, int64_t bB_stride,
                                 const float *bR_dev, const b200_approx_params *p, const b200_act_quant *aq,
                                 void *workspace, size_t workspace_bytes, void *stream);
+/* b200_approx_conv2d_fbias_fq with the fused epilogue (b200_epilogue above; aq and ep may each be NULL).  With
+ * ep != NULL `out` is the FINAL tensor: contiguous NCHW [batch, C_out, Ho, Wo] holding act(bn(conv + bias)); depthwise
+ * groups are supported (aq must then be NULL).  With ep == NULL: [rows, C_out] row-major as above. */
+int b200_approx_conv2d_fbias_ep(const float *x, const float *w, float *out, const b200_conv_geom *g,
+                                const float *bA_dev, const float *bB_dev, int64_t bB_stride,
+                                const float *bR_dev, const b200_approx_params *p, const b200_act_quant *aq,
+                                const b200_epilogue *ep, void *workspace, size_t workspace_bytes, void *stream);
 /* quantize_after_mult_and_add conv (:787-795); groups with one output channel are refused
  * (B200_ERR_ARGUMENT): the reference computes those exactly (:810-811). */
 int b200_qamaa_conv2d(const float *x, const float *w, float *out, const b200_conv_geom *g,

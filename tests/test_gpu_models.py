@@ -41,8 +41,19 @@ def build(kind, size, E, M):
     return model.cuda().eval()
 
 
+@pytest.fixture(params=[False, True], ids=["reference-passes", "fused"])
+def fused(request):
+    """The forward with the reference's pass structure (default) and with every opt-in fusion on
+    (quantization.enable_fusions: input quantizer in the operand decode, cached fixed weights, +bias -> BN ->
+    activation -> NCHW store in the GEMM / conv epilogue): the goldens must hold for both."""
+    from fp8_quantization_b200 import quantization as Q
+    prev = Q.enable_fusions(request.param)
+    yield request.param
+    Q.enable_fusions(True, *prev)
+
+
 @pytest.mark.parametrize("case", mc.MODEL_CASES, ids=[c[0] for c in mc.MODEL_CASES])
-def test_model_against_reference(case):
+def test_model_against_reference(case, fused):
     name, kind, size, batch, (E, M) = case
     z = np.load(GOLD)
     if f"{name}_yeval" not in z.files:
@@ -126,10 +137,11 @@ def test_vit_tiny_table_vs_arithmetic():
     assert float(outs[0][1].abs().max()) > 0
 
 
-def test_graphed_forward_equals_eager():
+def test_graphed_forward_equals_eager(fused):
     """eval_harness.GraphedForward: the calibrated ResNet-18 forward replayed as a CUDA graph returns the bits
-    of the eager forward, for two different batches through the same graph and for a second input shape."""
-    from fp8_quantization_b200 import eval_harness as eh
+    of the eager forward, for two different batches through the same graph and for a second input shape; and the
+    fused forward returns the bits of the forward with the reference's pass structure."""
+    from fp8_quantization_b200 import eval_harness as eh, quantization as Q
     res = 64
     model = build("resnet18", res, 4, 3)
     eh.calibrate(model, mc.images(4, res, 1).cuda())
@@ -138,6 +150,12 @@ def test_graphed_forward_equals_eager():
         x = mc.images(n, res, seed).cuda()
         with torch.inference_mode():
             want = model(x)
+            prev = Q.enable_fusions(False)
+            try:
+                plain = model(x)
+            finally:
+                Q.enable_fusions(True, *prev)
         got = fwd(x)
         assert torch.equal(got, want), (seed, n)
+        assert torch.equal(plain, want), (seed, n, "fused != reference passes")
     assert len(fwd._graphs) == 2

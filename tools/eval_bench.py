@@ -39,6 +39,8 @@ def main():
     import model_cases as mc
     from fp8_quantization_b200 import eval_harness as eh, ops
     ops.set_autotune(True)
+    from fp8_quantization_b200 import quantization as _Q
+    _Q.enable_fusions(True)      # opt-in fused forward (input quantizer, fixed-weight cache, GEMM epilogue): same bits
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))

@@ -47,6 +47,8 @@ def images_per_s(model_name="resnet18", batch=8, steps=10, warmup=3, E=4, M=3, g
     from fp8_quantization_b200 import eval_harness as eh, ops
     device = device or torch.device("cuda", torch.cuda.current_device())
     ops.set_autotune(True)
+    from fp8_quantization_b200 import quantization as _Q
+    _Q.enable_fusions(True)      # opt-in fused forward (input quantizer, fixed-weight cache, GEMM epilogue): same bits
     model = build(model_name, E, M, device)
     if model_name == "bert_base":
         ids = lambda n, seed: torch.randint(0, 30522, (n, 128), generator=torch.Generator().manual_seed(seed))
