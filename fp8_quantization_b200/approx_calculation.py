@@ -125,7 +125,14 @@ class _ConvMixin(_ApproxMixin):
 
 class QCustomBNConv2dTorch(_ConvMixin, BNFusedHijacker, nn.Conv2d):
     def _fusable_input_quant(self, x):
-        return x.dim() == 4 and self.out_channels // self.groups != 1     # depthwise groups read x_q directly
+        if x.dim() != 4:
+            return False
+        if self.out_channels // self.groups != 1:
+            return True
+        # depthwise groups: the input is quantized while it is decoded into the table kernel's word plane (main mode)
+        cap = self.custom_approx_params or {}
+        return bool(cap.get("with_s2nn2s_opt")) and bool(cap.get("quant_btw_mult_accu", True)) and \
+            not cap.get("golden_clip_OF") and not cap.get("ofuf_mode")
 
     def run_forward(self, x, weight, bias, offsets=None):
         """approx_calculation.py:822-917."""

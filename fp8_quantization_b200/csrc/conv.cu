@@ -264,6 +264,225 @@ __global__ void __launch_bounds__(256, 3) approx_dw_lut_kernel(DwLutArgs d)
     if (off) *d.flag = 1;
 }
 
+// ---- single-column groups, table driven, over a PRE-DECODED input plane ----------------------------------------
+// approx_dw_lut_kernel above extracts and validates the fields of `a` for every MAC (52 instructions per MAC measured,
+// profiles/r1e_approx_dw_lut_full.txt) although every input element is used by up to kh*kw outputs.  Here the input is
+// decoded ONCE (dw_plane_kernel: optional fused input fake-quantizer, field extraction, validity test -> one 32-bit
+// word per element = byte offset of its (sign, tA, mA) part of the table index, same NCHW layout), and the MAC is
+//     LDG word -> address = min(word + weight part, zero cell) -> LDS.U16 -> fp32 add          (k ascending)
+// A zero / padded / invalid input carries a huge word, which the min() sends to the all-zero cell.
+constexpr uint32_t kDwPlaneSkip = 0x40000000u;
+
+struct DwPlaneArgs {
+    ASrc a;               // geometry + the raw input (fq fields set: quantize while decoding)
+    uint32_t* plane;      // [B][C][H][W] words
+    int64_t total;        // B * C * H * W
+    BiasSrc bias;
+    LutGeom g;
+    int* flag;
+};
+
+__device__ __forceinline__ uint32_t dw_plane_word(float v, uint32_t frac_mask, uint32_t mmask, uint32_t ea_lo, uint32_t RA,
+                                                  uint32_t s_stride2, uint32_t a_stride2, uint32_t row2, int mshift, int& off)
+{
+    const uint32_t ab = __float_as_uint(v);
+    const uint32_t amag = ab & 0x7FFFFFFFu;
+    if (amag == 0u) return kDwPlaneSkip;                       // zero product: addend 0 (v9 :81)
+    const uint32_t tA = (amag >> 23) - ea_lo;                  // wraps for values below the sub-normal range
+    if ((amag & frac_mask) || tA > RA) { off = 1; return kDwPlaneSkip; }
+    const uint32_t mA = (amag >> mshift) & mmask;
+    return s_stride2 * (ab >> 31) + a_stride2 * mA + row2 * tA;
+}
+
+__global__ void __launch_bounds__(256) dw_plane_kernel(DwPlaneArgs d)
+{
+    const ASrc& s = d.a;
+    const LutGeom& g = d.g;
+    const int M = g.M, bA = d.bias.A(), bR = d.bias.R();
+    int off = (bA < 2 || bR < 2 || bA >= 64 || bR >= 64) ? 1 : 0;
+    const uint32_t frac_mask = (1u << (23 - M)) - 1u, mmask = (1u << M) - 1u;
+    const uint32_t ea_lo = (uint32_t)(127 + 1 - bA - M), RA = (uint32_t)g.RA;
+    const uint32_t s2 = 2u * (uint32_t)g.s_stride, a2 = 2u * (uint32_t)g.a_stride, r2 = 2u * (uint32_t)g.row_entries;
+    const int mshift = 23 - M;
+    // fused input fake-quantizer: constants read once per thread
+    const bool fq = s.fq_maxval != nullptr;
+    const float mx = fq ? __ldg(s.fq_maxval) : 0.0f, fb = fq ? __ldg(s.fq_bias) : 0.0f;
+    const bool fast = fq && fp8_ste_fast_ok(fb);
+    auto quant = [&](float v) -> float {
+        if (!fq) return v;
+        return fast ? fp8_ste_quant_fast(v, mx, (int)fb, (int)s.fq_Mf, s.fq_sign) : fp8_ste_quant(v, mx, fb, s.fq_Mf, s.fq_sign);
+    };
+    const bool vec = (d.total & 3) == 0 && ((uintptr_t)s.p & 15) == 0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    if (vec) {
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < d.total / 4; i += stride) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(s.p) + i);
+            uint4 w;
+            w.x = dw_plane_word(quant(v.x), frac_mask, mmask, ea_lo, RA, s2, a2, r2, mshift, off);
+            w.y = dw_plane_word(quant(v.y), frac_mask, mmask, ea_lo, RA, s2, a2, r2, mshift, off);
+            w.z = dw_plane_word(quant(v.z), frac_mask, mmask, ea_lo, RA, s2, a2, r2, mshift, off);
+            w.w = dw_plane_word(quant(v.w), frac_mask, mmask, ea_lo, RA, s2, a2, r2, mshift, off);
+            reinterpret_cast<uint4*>(d.plane)[i] = w;
+        }
+    } else {
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < d.total; i += stride)
+            d.plane[i] = dw_plane_word(quant(__ldg(s.p + i)), frac_mask, mmask, ea_lo, RA, s2, a2, r2, mshift, off);
+    }
+    if (off) *d.flag = 1;
+}
+
+struct DwPlaneLutArgs {
+    DwLutArgs l;             // a.p is unused here; everything else as in approx_dw_lut_kernel
+    const uint32_t* plane;   // [B][C][H][W] words written by dw_plane_kernel
+};
+
+// Same tiling as approx_dw_lut_kernel (persistent CTAs over 32 rows x 32 groups, rows across lanes, weight parts decoded
+// once per tile into shared memory).  KG = 9: 3x3 taps unrolled, all nine words loaded first.
+template <int KG>
+__global__ void __launch_bounds__(256, 4) approx_dw_plane_lut_kernel(DwPlaneLutArgs pa)
+{
+    const DwLutArgs& d = pa.l;
+    extern __shared__ __align__(16) unsigned char dw_smem[];
+    const int Kg = KG ? KG : d.Kg;
+    float (*tile)[33] = reinterpret_cast<float (*)[33]>(dw_smem + d.lut_bytes);
+    uint32_t* wpart = reinterpret_cast<uint32_t*>(dw_smem + d.lut_bytes + 32 * 33 * sizeof(float));   // [32][Kg]
+    int2* kinfo = reinterpret_cast<int2*>(wpart + ((32 * Kg + 1) & ~1));                               // [Kg]
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(d.lut);
+        uint4* dst = reinterpret_cast<uint4*>(dw_smem);
+        for (int i = threadIdx.x; i < d.lut_bytes / 16; i += 256) dst[i] = __ldg(src + i);
+    }
+    const ASrc& s = d.a;
+    for (int k = threadIdx.x; k < Kg; k += 256) {   // K order (c, ky, kx), approx_calculation.py:724-747
+        const int kx = k % s.kw, t = k / s.kw, ky = t % s.kh, c = t / s.kh;
+        kinfo[k] = make_int2((c * s.H + ky * s.dh) * s.W + kx * s.dw, (ky * s.dh) | ((kx * s.dw) << 16));
+    }
+    const uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(dw_smem);
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const LutGeom& g = d.g;
+    const int M = g.M;
+    const int bA = d.bias.A(), bR = d.bias.R();
+    int off = (bA < 2 || bR < 2 || bA >= 64 || bR >= 64) ? 1 : 0;
+    const float unit = pow2f_i(1 - bR - M);
+    const uint32_t frac_mask = (1u << (23 - M)) - 1u;
+    const uint32_t zero_addr = lut_base + 2u * (uint32_t)g.zeroA_off;   // an all-zero cell
+    const int mshift = 23 - M;
+    const bool small = d.rows < ((int64_t)1 << 31) && d.n_row_tiles * d.n_grp_tiles < ((int64_t)1 << 31);
+    int2 kreg[KG > 0 ? KG : 1];
+    if (KG > 0) {
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < KG; ++k) kreg[k] = kinfo[k];
+    }
+    for (int64_t t = blockIdx.x; t < d.n_row_tiles * d.n_grp_tiles; t += gridDim.x) {
+        int64_t rt;
+        int gt;
+        if (small) { rt = (uint32_t)t / (uint32_t)d.n_grp_tiles; gt = (int)((uint32_t)t - (uint32_t)rt * (uint32_t)d.n_grp_tiles); }
+        else       { rt = t / d.n_grp_tiles; gt = (int)(t - rt * d.n_grp_tiles); }
+        __syncthreads();                          // previous tile's wpart / tile readers are done; first pass: lut, kinfo
+        for (int i = threadIdx.x; i < 32 * Kg; i += 256) {
+            const int gl = i / Kg, k = i - gl * Kg, grp = gt * 32 + gl;
+            uint32_t wp = kDwPlaneSkip;           // zero weight (v9 :81) or no such group: every tap looks up the zero cell
+            if (grp < d.groups) {
+                const int bB = d.bias.B(grp);
+                if (bB < 2 || bB >= 64) off = 1;
+                const uint32_t wb = __float_as_uint(__ldg(d.w + (int64_t)grp * Kg + k));
+                const uint32_t wmag = wb & 0x7FFFFFFFu;
+                if (wmag != 0u) {
+                    const int LB = (int)(wmag >> 23) - 127;
+                    const int tB = LB + bR - bA + 3 + g.RA;          // no clamp: every row is live here
+                    if ((wmag & frac_mask) || tB < 0 || tB > g.NTB - 1 || LB < 1 - bB - M || (wmag >> 23) == 0 ||
+                        (wmag >> 23) == 255)
+                        off = 1;                  // outside the table's domain: the arithmetic kernel recomputes
+                    else
+                        wp = lut_base + 2u * ((uint32_t)g.s_stride * (wb >> 31) + (uint32_t)g.row_entries * (uint32_t)tB +
+                                              ((wmag & 0x7FFFFFu) >> mshift));
+                }
+            }
+            wpart[i] = wp;
+        }
+        const bool ep_nchw = d.ep.on && d.ep.HW > 0;
+        Epilogue::Col* ecol = reinterpret_cast<Epilogue::Col*>(&tile[0][0]);
+        if (ep_nchw && threadIdx.x < 32) {
+            const int grp = gt * 32 + threadIdx.x;
+            ecol[threadIdx.x] = d.ep.column(grp < d.groups ? grp : d.groups - 1);
+        }
+        __syncthreads();
+        const int64_t m = rt * 32 + tx;
+        int wo, ho;
+        int64_t b;
+        if (small) {
+            const uint32_t mm = (uint32_t)m, t2 = mm / (uint32_t)s.Wo;
+            wo = (int)(mm - t2 * (uint32_t)s.Wo);
+            b = t2 / (uint32_t)s.Ho;
+            ho = (int)(t2 - (uint32_t)b * (uint32_t)s.Ho);
+        } else {
+            wo = (int)(m % s.Wo);
+            const int64_t t2 = m / s.Wo;
+            ho = (int)(t2 % s.Ho);
+            b = t2 / s.Ho;
+        }
+        const int h0 = ho * s.sh - s.ph, w0 = wo * s.sw - s.pw;
+        // tap validity (F.pad zeros, :727) once per output pixel, as a bit mask over k
+        uint32_t inb = 0u;
+        if (KG > 0) {
+#pragma unroll
+            for (int k = 0; k < KG; ++k) {
+                const int h = h0 + (kreg[k].y & 0xFFFF), wi = w0 + (kreg[k].y >> 16);
+                inb |= ((unsigned)h < (unsigned)s.H && (unsigned)wi < (unsigned)s.W) ? (1u << k) : 0u;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int gl = ty + 8 * i;
+            const int grp = gt * 32 + gl;
+            float acc = 0.0f;
+            if (grp < d.groups && m < d.rows) {
+                const uint32_t* p0 = pa.plane + ((b * s.C + (int64_t)grp * d.Cg) * s.H + h0) * (int64_t)s.W + w0;
+                const uint32_t* wrow = wpart + gl * Kg;
+                if (KG > 0) {
+                    uint32_t aw[KG > 0 ? KG : 1];
+#pragma unroll
+                    for (int k = 0; k < KG; ++k) aw[k] = ((inb >> k) & 1u) ? __ldg(p0 + kreg[k].x) : kDwPlaneSkip;
+#pragma unroll
+                    for (int k = 0; k < KG; ++k) {
+                        const uint32_t addr = min(aw[k] + wrow[k], zero_addr);   // skip words overshoot: zero cell
+                        unsigned short e;
+                        asm("ld.shared.u16 %0, [%1];" : "=h"(e) : "r"(addr));
+                        acc += __uint_as_float((uint32_t)e << 16);
+                    }
+                } else {
+                    for (int k = 0; k < Kg; ++k) {
+                        const int2 ki = kinfo[k];
+                        const int h = h0 + (ki.y & 0xFFFF), wi = w0 + (ki.y >> 16);
+                        if ((unsigned)h >= (unsigned)s.H || (unsigned)wi >= (unsigned)s.W) continue;   // F.pad zeros (:727)
+                        const uint32_t addr = min(__ldg(p0 + ki.x) + wrow[k], zero_addr);
+                        unsigned short e;
+                        asm("ld.shared.u16 %0, [%1];" : "=h"(e) : "r"(addr));
+                        acc += __uint_as_float((uint32_t)e << 16);
+                    }
+                }
+            }
+            if (ep_nchw) {
+                if (grp < d.groups && m < d.rows)
+                    d.out[((b * d.ep.Ctot + d.ep.c0 + grp) * (int64_t)s.Ho + ho) * s.Wo + wo] = d.ep.apply(acc * unit, ecol[gl]);
+            } else {
+                tile[gl][tx] = acc * unit;
+            }
+        }
+        if (ep_nchw) continue;
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int ml = ty + 8 * i;
+            const int64_t mm = rt * 32 + ml;
+            const int grp = gt * 32 + tx;
+            if (mm < d.rows && grp < d.groups) d.ep.store(d.out, d.groups, mm, grp, tile[tx][ml]);
+        }
+    }
+    if (off) *d.flag = 1;
+}
+
 // ---- exact grouped conv (non-approx configuration, groups > 1) ---------------------------------------
 // out[m, n] = sum_{k < Kg, ascending} col[m, grp(n)*Kg + k] * w[n, k]: the reference's exact branch of the
 // group loop (`input_col_group @ weight_group.T`, approx/approx_calculation.py:810-811, :796-797) for every
@@ -381,7 +600,8 @@ extern "C" size_t b200_approx_conv2d_workspace_bytes(const b200_conv_geom* g)
 {
     ConvDims d;
     if (conv_dims(g, &d) != B200_OK) return 0;
-    if (d.Ng == 1) return 256;   // device-side fallback flag of the single-column table kernel
+    // single-column groups: device-side fallback flag + the decoded input plane of approx_dw_plane_lut_kernel
+    if (d.Ng == 1) return 256 + (size_t)round_up((int64_t)g->batch * g->C_in * g->H * g->W * 4, 256);
     return b200_approx_gemm_workspace_bytes(d.rows, d.Kg, d.Ng) + conv_gather_workspace_bytes(g->batch, d.Cg, g->H, g->W, d.Kg);
 }
 
@@ -449,7 +669,10 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
         return B200_OK;
     }
     // N == 1 per group: the reference's tensor-bias branch (approx_calculation.py:800-809)
-    if (aq) { set_error("b200_approx_conv2d_fbias_fq: the fused input quantizer is not available for depthwise groups"); return B200_ERR_ARGUMENT; }
+    const int64_t in_total = (int64_t)g->batch * g->C_in * g->H * g->W;
+    const bool plane_room = workspace && workspace_bytes >= 256 + (size_t)in_total * 4 && ((uintptr_t)workspace & 15) == 0;
+    // (a fused input quantizer is honoured by the decoded-plane table kernel and by the arithmetic kernel, whose operand
+    // view quantizes on load; the per-MAC decoding table kernel reads the raw tensor and is skipped then)
     const int E = p->expo_width, M = p->mant_width;
     const bool v5 = p->ofuf_mode == 1;      // v5 integer-add semantics (no tensor-bias branch exists in v5)
     const signed char* host_table = nullptr;
@@ -466,6 +689,7 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
     if (int rc = device_table(host_table, M, &dev_table)) return rc;
     DwArgs a;
     a.a = make_conv_asrc(x, g, d, 0);
+    if (int rc = apply_act_quant(&a.a, aq)) return rc;     // ASrc::load quantizes: the arithmetic kernel honours it too
     a.w = w; a.out = out; a.rows = d.rows; a.groups = g->groups; a.Kg = d.Kg; a.Cg = d.Cg;
     a.bias = BiasSrc{dflt, dflt, bA_dev, bR_dev, nullptr, bB_dev, bB_stride};
     a.cfg.E = E; a.cfg.M = M;
@@ -502,6 +726,8 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
             if (int rc = once.get(&sms, []() -> int {
                     B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_lut_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
                     B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_lut_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                    B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_plane_lut_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                    B200_CUDA_TRY(cudaFuncSetAttribute(approx_dw_plane_lut_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
                     return B200_OK;
                 }))
                 return rc;
@@ -513,14 +739,34 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
             const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (227 * 1024) / (smem + 1024)));
             const int64_t tiles = la.n_row_tiles * la.n_grp_tiles;
             const unsigned blocks = (unsigned)std::min<int64_t>(tiles, (int64_t)sms * per_sm);
-            if (d.Kg == 9) approx_dw_lut_kernel<9><<<blocks, 256, smem, st>>>(la);
-            else           approx_dw_lut_kernel<0><<<blocks, 256, smem, st>>>(la);
-            B200_LAUNCH_CHECK("approx_dw_lut_kernel");
-            // runs only if the table kernel met an operand / bias outside its domain
-            approx_dw_kernel<<<grid, 256, 0, st>>>(a, la.flag, 1);
-            B200_LAUNCH_CHECK("approx_dw_kernel(conditional)");
-            set_path("single-column-lut");
-            return B200_OK;
+            const char* pe = getenv("B200_DW_PLANE");     // experiments / tests: 0 = the per-MAC decoding kernel
+            if (plane_room && in_total < ((int64_t)1 << 31) && !(pe && atoi(pe) == 0)) {
+                // decode the input once (with the input fake-quantizer, if fused), then the lookup kernel
+                DwPlaneArgs dp;
+                dp.a = a.a; dp.plane = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(workspace) + 256);
+                dp.total = in_total; dp.bias = a.bias; dp.g = la.g; dp.flag = la.flag;
+                const unsigned pblocks = (unsigned)std::min<int64_t>(ceil_div(ceil_div(in_total, 4), 256), (int64_t)sms * 16);
+                dw_plane_kernel<<<pblocks, 256, 0, st>>>(dp);
+                B200_LAUNCH_CHECK("dw_plane_kernel");
+                DwPlaneLutArgs pl{la, dp.plane};
+                if (d.Kg == 9) approx_dw_plane_lut_kernel<9><<<blocks, 256, smem, st>>>(pl);
+                else           approx_dw_plane_lut_kernel<0><<<blocks, 256, smem, st>>>(pl);
+                B200_LAUNCH_CHECK("approx_dw_plane_lut_kernel");
+                approx_dw_kernel<<<grid, 256, 0, st>>>(a, la.flag, 1);
+                B200_LAUNCH_CHECK("approx_dw_kernel(conditional)");
+                set_path("single-column-lut-plane");
+                return B200_OK;
+            }
+            if (!aq) {
+                if (d.Kg == 9) approx_dw_lut_kernel<9><<<blocks, 256, smem, st>>>(la);
+                else           approx_dw_lut_kernel<0><<<blocks, 256, smem, st>>>(la);
+                B200_LAUNCH_CHECK("approx_dw_lut_kernel");
+                // runs only if the table kernel met an operand / bias outside its domain
+                approx_dw_kernel<<<grid, 256, 0, st>>>(a, la.flag, 1);
+                B200_LAUNCH_CHECK("approx_dw_kernel(conditional)");
+                set_path("single-column-lut");
+                return B200_OK;
+            }
         }
     }
     approx_dw_kernel<<<grid, 256, 0, st>>>(a, nullptr, 0);

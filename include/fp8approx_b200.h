@@ -225,7 +225,8 @@ int b200_fq_gemm_tc(const float *A, int64_t lda, const float *B, int64_t sb_k, i
  * GEMM / conv instead of as a separate pass over the activations.  A / x then hold the RAW activations;
  * maxval_dev is the quantizer's per-tensor range, bias_dev the exponent bias the stand-alone quantizer derived
  * from it (FPQuantizer.custom_bias; also what bA_dev must point at).  Results are bit-identical to
- * quantizing first.  Not available for single-output-channel (depthwise) groups. */
+ * quantizing first.  Single-output-channel (depthwise) groups quantize while the input is decoded into the word plane
+ * of their table kernel. */
 typedef struct b200_act_quant {
     const float *maxval_dev; /* device [1] */
     const float *bias_dev;   /* device [1] */
@@ -294,7 +295,7 @@ int b200_approx_conv2d_fbias(const float *x, const float *w, float *out, const b
                              const float *bA_dev, const float *bB_dev, int64_t bB_stride,
                              const float *bR_dev, const b200_approx_params *p, void *workspace,
                              size_t workspace_bytes, void *stream);
-/* same, with the input fake-quantizer fused (b200_act_quant above); refuses depthwise groups */
+/* same, with the input fake-quantizer fused (b200_act_quant above) */
 int b200_approx_conv2d_fbias_fq(const float *x, const float *w, float *out, const b200_conv_geom *g,
                                 const float *bA_dev, const float *bB_dev, int64_t bB_stride,
                                 const float *bR_dev, const b200_approx_params *p, const b200_act_quant *aq,

@@ -274,9 +274,17 @@ def test_v5_ofuf_fixture(fq):
             assert np.array_equal(got.cpu().numpy(), z[f"r{i}"])
 
 
+@pytest.fixture(params=["1", "0"], ids=["decoded-plane", "per-mac-decode"])
+def dw_kernel(request):
+    """Both single-column table kernels: the decoded-plane one (default) and the older per-MAC decoding one."""
+    os.environ["B200_DW_PLANE"] = request.param
+    yield "single-column-lut-plane" if request.param == "1" else "single-column-lut"
+    os.environ.pop("B200_DW_PLANE", None)
+
+
 @pytest.mark.parametrize("fmt", [(4, 3, 3), (3, 4, 3), (2, 5, 3), (2, 5, 5)])
 @pytest.mark.parametrize("geom", [(3, 40, 17, 19, 3, 1, 1), (2, 33, 16, 16, 3, 2, 1), (1, 8, 9, 9, 5, 1, 2)])
-def test_depthwise_table_kernel_vs_arithmetic(fq, fmt, geom):
+def test_depthwise_table_kernel_vs_arithmetic(fq, fmt, geom, dw_kernel):
     """Single-column groups (every depthwise conv): the table kernel against the arithmetic kernel that the
     layer fixtures pin to the reference's tensor-bias branch (approx_calculation.py:800-809): bit exact.
     Also: biases < 2 and off-grid operands must fall back on the device."""
@@ -293,7 +301,7 @@ def test_depthwise_table_kernel_vs_arithmetic(fq, fmt, geom):
     args = (dev(x), dev(w), torch.tensor([float(bA)]).cuda(), dev(bW), torch.tensor([float(bR)]).cuda())
     conv = ((stride, stride), (pad, pad), (1, 1), C)
     got = fq.ops.approx_conv2d(*args, fq.ops.make_params(kw, single_column_quirk=True), *conv)
-    assert fq.ops.last_path() == "single-column-lut"
+    assert fq.ops.last_path() == dw_kernel
     want = fq.ops.approx_conv2d(*args, fq.ops.make_params(kw, single_column_quirk=True, force_generic=True), *conv)
     assert fq.ops.last_path() == "single-column"
     assert same_bits(got.cpu().numpy(), want.cpu().numpy())
