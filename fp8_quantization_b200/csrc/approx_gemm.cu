@@ -16,8 +16,11 @@
 // Accumulation: fp32, k ascending, one thread owns an output element for the whole K loop -- the
 // same order as the oracle, hence bit-identical to it; identical to the reference whenever fp32
 // summation is exact (always, in the calibrated quant_btw_mult_accu regime: DESIGN.md).
+#include <cuda.h>
+
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 #include <type_traits>
 #include <map>
 #include <mutex>
@@ -402,6 +405,71 @@ __global__ void __launch_bounds__(PC_ROWS) predecode_conv_kernel(PredecodeArgs a
     }
 }
 
+// Conv form, 1x1 taps with unit stride and no padding (every pointwise conv): im2col is the identity up to the layout
+// change NCHW -> [k = channel][row = (b, pixel)], so the pass is elementwise.  One thread converts 4 consecutive pixels
+// of one channel (128-bit load, 128-bit store), the fake-quantizer's constants are read once per thread, nothing divides
+// per element (predecode_conv_kernel spends ~115 instructions per element on its generic tap arithmetic:
+// profiles/r2b_mbv2_predecode_dw_full.txt).  Needs H*W % 4 == 0 and a 16-byte aligned input.
+// grid (ceil(Rpad / 4 / 256), Kpad).
+__global__ void __launch_bounds__(256) predecode_1x1_kernel(PredecodeArgs a, LutGeom g)
+{
+    const ASrc& s = a.asrc;
+    const int64_t q = (int64_t)blockIdx.x * 256 + threadIdx.x, r = q * 4;
+    const int k = blockIdx.y;
+    int off = 0, zeros = 0, tmax = 0;
+    const int bA = a.bias.A(), bR = a.bias.R();
+    if (bA <= -64 || bA >= 64 || bR <= -64 || bR >= 64) off = 1;
+    const uint32_t zero_word = 2u * (uint32_t)g.zeroA_off;
+    const bool live = r < a.rows && k < a.K;
+    if (r < a.Rpad) {
+        uint4 w = make_uint4(zero_word, zero_word, zero_word, zero_word);
+        if (live) {
+            const int64_t HW = (int64_t)s.H * s.W;
+            int64_t b, p;
+            if (a.rows < ((int64_t)1 << 31)) { b = (uint32_t)r / (uint32_t)HW; p = r - b * HW; }
+            else                             { b = r / HW; p = r - b * HW; }
+            float4 v = __ldg(reinterpret_cast<const float4*>(s.p + ((b * s.C + s.c0 + k) * HW + p)));
+            if (s.fq_maxval) {
+                const float mx = __ldg(s.fq_maxval), fb = __ldg(s.fq_bias);
+                if (fp8_ste_fast_ok(fb)) {
+                    const int bi = (int)fb, Mi = (int)s.fq_Mf;
+                    v.x = fp8_ste_quant_fast(v.x, mx, bi, Mi, s.fq_sign); v.y = fp8_ste_quant_fast(v.y, mx, bi, Mi, s.fq_sign);
+                    v.z = fp8_ste_quant_fast(v.z, mx, bi, Mi, s.fq_sign); v.w = fp8_ste_quant_fast(v.w, mx, bi, Mi, s.fq_sign);
+                } else {
+                    v.x = fp8_ste_quant(v.x, mx, fb, s.fq_Mf, s.fq_sign); v.y = fp8_ste_quant(v.y, mx, fb, s.fq_Mf, s.fq_sign);
+                    v.z = fp8_ste_quant(v.z, mx, fb, s.fq_Mf, s.fq_sign); v.w = fp8_ste_quant(v.w, mx, fb, s.fq_Mf, s.fq_sign);
+                }
+            }
+            if (g.v5) {
+                w.x = predecode_a_v5(g, v.x, bA, off); w.y = predecode_a_v5(g, v.y, bA, off);
+                w.z = predecode_a_v5(g, v.z, bA, off); w.w = predecode_a_v5(g, v.w, bA, off);
+            } else {
+                w.x = predecode_a(g, v.x, bA, off, tmax); w.y = predecode_a(g, v.y, bA, off, tmax);
+                w.z = predecode_a(g, v.z, bA, off, tmax); w.w = predecode_a(g, v.w, bA, off, tmax);
+            }
+            zeros = (v.x == 0.0f) + (v.y == 0.0f) + (v.z == 0.0f) + (v.w == 0.0f);
+        }
+        *reinterpret_cast<uint4*>(a.dst + (int64_t)k * a.Rpad + r) = w;
+    }
+    if (off) *a.offgrid = 1;
+    if (a.tmax) {
+        tmax = __reduce_max_sync(0xFFFFFFFFu, tmax);
+        if ((threadIdx.x & 31) == 0 && tmax > *(volatile int*)a.tmax) atomicMax(a.tmax, tmax);
+    }
+    if (a.zero_count && (blockIdx.x & 7) == 0 && (blockIdx.y & 3) == 0) {   // sampled zero statistics
+        __shared__ int s_zeros;
+        if (threadIdx.x == 0) s_zeros = 0;
+        __syncthreads();
+        zeros = __reduce_add_sync(0xFFFFFFFFu, zeros);
+        if ((threadIdx.x & 31) == 0 && zeros) atomicAdd(&s_zeros, zeros);
+        __syncthreads();
+        if (threadIdx.x == 0 && k < a.K) {
+            const int64_t n = min((int64_t)1024, a.rows - (int64_t)blockIdx.x * 1024);
+            if (n > 0) atomicAdd(a.zero_count, (unsigned long long)s_zeros | ((unsigned long long)n << 32));
+        }
+    }
+}
+
 // Conv form, second variant: the group's input channels are decoded ONCE, in place of the kh*kw-times
 // inflated plane above, into words Pw[b][c][h][w]; the GEMM's A-tile loader then does the im2col gather
 // itself (4-byte cp.async from this L2-resident plane).  kinfo[k] = {word offset of tap k = (c, ky, kx)
@@ -530,6 +598,34 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+// TMA operand staging (GEMM form): the k-major planes Aw[Kpad][Mpad] / Bw[Kpad][Npad] are dense 2-D tensors, one
+// cp.async.bulk.tensor.2d per operand and k tile lands a [KT][BM] / [KT][BN] box in shared memory and signals a
+// per-stage mbarrier with the byte count; issued by ONE thread, no address arithmetic or LDGSTS in the other 255.
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "LUT_WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra LUT_WAIT_DONE;\n\t"
+        "bra LUT_WAIT_LOOP;\n\t"
+        "LUT_WAIT_DONE:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+
 struct LutGemmArgs {
     const uint32_t* Aw;   // [Kpad][Mpad]
     const uint32_t* Bw;   // [Kpad][Npad]
@@ -565,6 +661,9 @@ struct LutGemmArgs {
     int sk_ctas, sk_tiles_n;
     int64_t sk_tiles;
     Epilogue ep;          // fused +bias -> BN -> activation -> (NCHW) store, epilogue.cuh; ep.on == 0: plain store
+    int use_tma;          // GEMM form only: operand tiles arrive by TMA (mapA / mapB) instead of the cp.async ring
+    alignas(64) CUtensorMap mapA;   // Aw as a 2-D tensor {Mpad, Kpad}, box {BM, KT}
+    alignas(64) CUtensorMap mapB;   // Bw as a 2-D tensor {Npad, Kpad}, box {BN, KT}
 };
 
 // KT: k-tile depth (8 where a large table leaves little shared memory for the operand ring).
@@ -573,17 +672,19 @@ struct LutGemmArgs {
 // SK: stream-K instantiation (persistent CTAs over (tile, k-tile) ranges, see LutGemmArgs::sk_ctas).
 template <int WARPS, int RPW, int CPL, int KT, bool SIDX, bool CONV, bool SK>
 __global__ void __launch_bounds__(32 * WARPS, (WARPS >= 16) ? 1 : ((RPW * CPL >= 64) ? 16 / WARPS : 24 / WARPS))
-approx_gemm_lut_kernel(LutGemmArgs a)
+approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
 {
     constexpr int BM = RPW * WARPS, BN = 32 * CPL, ST = LUT_STAGES, NTHR = 32 * WARPS;
     static_assert(CPL == 4 || CPL == 2, "a lane owns 2 or 4 consecutive columns");
     static_assert(RPW % 4 == 0, "A words are read 4 at a time");
     if (*a.offgrid != 0) return;   // some operand is off the FP8 grid: the generic kernel takes over
     if (a.gate && *a.gate == 0) return;
-    extern __shared__ __align__(16) unsigned char smem[];
-    uint32_t* As = reinterpret_cast<uint32_t*>(smem + a.lut_bytes);   // [ST][KT][BM]
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t full_bar[ST];                    // TMA: "stage s has landed"
+    uint32_t* As = reinterpret_cast<uint32_t*>(smem + ((a.lut_bytes + 127) & ~127));   // [ST][KT][BM], 128-byte aligned (TMA)
     uint32_t* Bs = As + ST * KT * BM;                                 // [ST][KT][BN]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool tma = !CONV && a.use_tma != 0;
     int64_t m0 = (int64_t)blockIdx.x * BM, n0 = (int64_t)blockIdx.y * BN;
 
     // pair table -> shared memory
@@ -594,6 +695,15 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     }
     const uint32_t lut_base = smem_u32(smem);
     const uint32_t As_u = smem_u32(As), Bs_u = smem_u32(Bs);
+    const uint32_t bar_u = smem_u32(full_bar);
+    if (tma) {
+        if (tid == 0) {
+#pragma unroll
+            for (int s = 0; s < ST; ++s) mbar_init(bar_u + 8u * s, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();   // nobody polls a barrier before it is initialised
+    }
 
     // CONV: this thread gathers row (tid % BM) of every A tile, k = tid / BM + j * (NTHR / BM)
     static_assert(NTHR % BM == 0 && (KT * BM) % NTHR == 0, "A-tile gather mapping");
@@ -612,6 +722,17 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     };
     if (CONV) conv_row_setup();
     auto load_tile = [&](int kt, int stage) {
+        if (tma) {
+            if (tid == 0) {
+                // the stage was last read through the generic proxy (LDS) before the __syncthreads that precedes this call
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                const uint32_t bar = bar_u + 8u * stage;
+                mbar_expect_tx(bar, (uint32_t)(KT * (BM + BN) * 4));
+                tma_load_2d(As_u + 4u * (uint32_t)(stage * KT * BM), &a.mapA, bar, (int)m0, kt * KT);
+                tma_load_2d(Bs_u + 4u * (uint32_t)(stage * KT * BN), &a.mapB, bar, (int)n0, kt * KT);
+            }
+            return;
+        }
         const uint32_t* gb = a.Bw + (int64_t)kt * KT * a.Npad + n0;
         if (CONV) {
             const int2* ki = a.cp.kinfo + kt * KT + tid / BM;
@@ -660,6 +781,7 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     int64_t sk_u = streamk ? (int64_t)blockIdx.x * sk_units / a.sk_ctas : 0;
     const int64_t sk_end = streamk ? (int64_t)(blockIdx.x + 1) * sk_units / a.sk_ctas : 1;
     bool sk_first = true;
+    uint32_t it_base = 0;   // TMA: tiles issued so far by this CTA (stage = it % ST, barrier parity = (it / ST) & 1)
   for (; sk_u < sk_end; sk_first = false) {
     if (streamk) {
         const int64_t tile = sk_u / nk_all;
@@ -680,7 +802,7 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     }
 #pragma unroll
     for (int s = 0; s < ST - 1; ++s) {
-        if (s < nk) load_tile(kt0 + s, s);
+        if (s < nk) load_tile(kt0 + s, tma ? (int)((it_base + s) % ST) : s);
         cp_async_commit();
     }
     // The k loop exists twice: dense activations use the predicated row (no branches, full ILP across
@@ -688,12 +810,15 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     auto mainloop = [&](auto branchy) {
         constexpr bool BRANCHY = decltype(branchy)::value;
         for (int kt = 0; kt < nk; ++kt) {
-            cp_async_wait<ST - 2>();
+            const uint32_t it = it_base + (uint32_t)kt;
+            const int stage = tma ? (int)(it % ST) : kt % ST;
+            if (tma) mbar_wait(bar_u + 8u * stage, (it / ST) & 1u);
+            else     cp_async_wait<ST - 2>();
             __syncthreads();
-            if (kt + ST - 1 < nk) load_tile(kt0 + kt + ST - 1, (kt + ST - 1) % ST);
+            if (kt + ST - 1 < nk) load_tile(kt0 + kt + ST - 1, tma ? (int)((it + ST - 1) % ST) : (kt + ST - 1) % ST);
             cp_async_commit();
-            const uint32_t* Asm = As + (kt % ST) * KT * BM + warp * RPW;
-            const uint32_t* Bsm = Bs + (kt % ST) * KT * BN + lane * CPL;
+            const uint32_t* Asm = As + stage * KT * BM + warp * RPW;
+            const uint32_t* Bsm = Bs + stage * KT * BN + lane * CPL;
 #pragma unroll (KT >= 16 ? 4 : 2)
             for (int kk = 0; kk < KT; ++kk) {
                 uint32_t bw[CPL];
@@ -744,6 +869,7 @@ approx_gemm_lut_kernel(LutGemmArgs a)
     if (sparse) mainloop(std::true_type{});
     else            mainloop(std::false_type{});
     cp_async_wait<0>();
+    it_base += (uint32_t)nk;
 
     if (streamk && nk < nk_all) {
         // a partial k range of this tile: certificate as for split-K (see below), then the slot store
@@ -986,7 +1112,7 @@ struct LutTileCfg {
     void (*sk_conv_kernel)(LutGemmArgs);
     int BM() const { return warps * rpw; }
     int BN() const { return 32 * cpl; }
-    size_t smem(int lut_bytes) const { return (size_t)lut_bytes + (size_t)LUT_STAGES * kt * (BM() + BN()) * 4; }
+    size_t smem(int lut_bytes) const { return (size_t)((lut_bytes + 127) & ~127) + (size_t)LUT_STAGES * kt * (BM() + BN()) * 4; }
 };
 #define LUT_TILE(W, R, C, KT, S) \
     {W, R, C, KT, S, approx_gemm_lut_kernel<W, R, C, KT, (S) != 0, false, false>,          \
@@ -1238,6 +1364,37 @@ int get_quirk_lut(int E, int M, const signed char* host_table, const signed char
     return B200_OK;
 }
 
+// 2-D tensor map over a k-major uint32 plane [outer = Kpad][inner = Rpad], box {box_inner, box_outer}, no swizzle
+// (the kernel reads the tile as plain rows).  cuTensorMapEncodeTiled through the runtime's driver entry point: the
+// library does not link libcuda.
+typedef CUresult (*LutEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static int lut_plane_map(CUtensorMap* map, const uint32_t* base, int64_t inner, int64_t outer, int box_inner, int box_outer)
+{
+    static std::mutex mu;
+    static LutEncodeTiledFn fn = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!fn) {
+            void* p = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            B200_CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+            if (!p || q != cudaDriverEntryPointSuccess) { set_error("cuTensorMapEncodeTiled is not available in this driver"); return B200_ERR_CUDA; }
+            fn = reinterpret_cast<LutEncodeTiledFn>(p);
+        }
+    }
+    const cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+    const cuuint64_t gstride[1] = {(cuuint64_t)inner * 4};
+    const cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<uint32_t*>(base), gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (code " + std::to_string((int)r) + ")"); return B200_ERR_CUDA; }
+    return B200_OK;
+}
+
 // Optional per-launch timing of the dominant kernel (bench.py's roofline leg): CUDA events recorded
 // on the launching stream right around the table GEMM.
 static std::mutex g_prof_mu;
@@ -1309,10 +1466,10 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     int sms = 0;
     if (int rc = once.get(&sms, []() -> int {
             for (const LutTileCfg& c : kLutTiles) {
-                B200_CUDA_TRY(cudaFuncSetAttribute(c.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-                B200_CUDA_TRY(cudaFuncSetAttribute(c.conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-                B200_CUDA_TRY(cudaFuncSetAttribute(c.sk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-                B200_CUDA_TRY(cudaFuncSetAttribute(c.sk_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                B200_CUDA_TRY(cudaFuncSetAttribute(c.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+                B200_CUDA_TRY(cudaFuncSetAttribute(c.conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+                B200_CUDA_TRY(cudaFuncSetAttribute(c.sk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+                B200_CUDA_TRY(cudaFuncSetAttribute(c.sk_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
             }
             return B200_OK;
         }))
@@ -1357,6 +1514,10 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
             cp.H = A.H; cp.W = A.W; cp.Ho = A.Ho; cp.Wo = A.Wo; cp.sh = A.sh; cp.sw = A.sw; cp.ph = A.ph; cp.pw = A.pw;
             const int64_t threads = std::max<int64_t>(ceil_div(total, 4), Kpad);
             predecode_plane_kernel<<<(unsigned)ceil_div(threads, 256), 256, 0, st>>>(pa, geom, Pw, kinfo, zsrc, nB, Cg);
+        } else if (A.kh == 1 && A.kw == 1 && A.sh == 1 && A.sw == 1 && A.ph == 0 && A.pw == 0 && ((int64_t)A.H * A.W) % 4 == 0 &&
+                   ((uintptr_t)A.p & 15) == 0 && A.Ho == A.H && A.Wo == A.W && Kpad <= 65535 &&
+                   !(getenv("B200_PREDECODE_1X1") && atoi(getenv("B200_PREDECODE_1X1")) == 0)) {
+            predecode_1x1_kernel<<<dim3((unsigned)ceil_div(Mpad / 4, 256), (unsigned)Kpad), 256, 0, st>>>(pa, geom);
         } else {
             predecode_conv_kernel<<<dim3((unsigned)(Mpad / PC_ROWS), (unsigned)ceil_div(Kpad, PC_KCH)), PC_ROWS, 0, st>>>(pa, geom);
         }
@@ -1387,9 +1548,24 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     la.partial = partial; la.inexact = flag + 6; la.tmax = flag + 4; la.t_bias = geom.RA + M + 2;
     la.cp = cp;
     la.ep = ep;
+    la.use_tma = 0;
+    memset(&la.mapA, 0, sizeof(la.mapA));
+    memset(&la.mapB, 0, sizeof(la.mapB));
     // one (tile, split) configuration: the GEMM, and for split-K the ordered reduction plus the gated unsplit kernel
+    // TMA operand staging for the GEMM-form planes (B200_LUT_TMA=0: the cp.async ring, for before / after measurements)
+    const bool want_tma = !gather && Mpad < ((int64_t)1 << 31) && Npad < ((int64_t)1 << 31) &&
+                          !(getenv("B200_LUT_TMA") && atoi(getenv("B200_LUT_TMA")) == 0);
+    auto set_maps = [&](LutGemmArgs& l, const LutTileCfg* cfg) -> int {
+        l.use_tma = 0;
+        if (!want_tma || cfg->BM() > 256 || cfg->BN() > 256) return B200_OK;
+        if (int rc = lut_plane_map(&l.mapA, Aw, Mpad, Kpad, cfg->BM(), cfg->kt)) return rc;
+        if (int rc = lut_plane_map(&l.mapB, Bw, Npad, Kpad, cfg->BN(), cfg->kt)) return rc;
+        l.use_tma = 1;
+        return B200_OK;
+    };
     auto launch = [&](const LutTileCfg* cfg, int splits) -> int {
         LutGemmArgs l = la;
+        if (int rc = set_maps(l, cfg)) return rc;
         l.splits = splits; l.gate = nullptr;
         l.sk_ctas = 0; l.sk_tiles_n = 0; l.sk_tiles = 0;
         const dim3 tgrid((unsigned)ceil_div(Mrows, cfg->BM()), (unsigned)ceil_div(N, cfg->BN()), (unsigned)std::max(splits, 1));
@@ -1422,6 +1598,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
             int S1 = 1;
             const LutTileCfg* t1 = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, 1, &S1);
             l.splits = 1; l.gate = flag + 6; l.sk_ctas = 0;
+            if (int rc = set_maps(l, t1)) return rc;
             (gather ? t1->conv_kernel : t1->kernel)<<<dim3((unsigned)ceil_div(Mrows, t1->BM()), (unsigned)ceil_div(N, t1->BN())), 32 * t1->warps,
                                                      t1->smem(lut_bytes), st>>>(l);
         }

@@ -125,6 +125,9 @@ CONV_CASES = [
     (2, 16, 10, 10, 32, 3, 1, 1, 1, 4),      # grouped, 8 columns per group
     (4, 64, 7, 7, 128, 3, 1, 1, 1, 1),       # 49-pixel images: image size not a multiple of 4 words per channel
     (1, 5, 7, 9, 6, 3, 1, 1, 1, 1),          # image of 315 words: the gather path must decline (alignment)
+    (3, 24, 6, 6, 40, 1, 1, 0, 1, 1),        # pointwise, 108 rows / K = 24: row and k padding of the 1x1 decode pass
+    (2, 20, 10, 10, 24, 1, 1, 0, 1, 2),      # pointwise, grouped
+    (2, 12, 5, 5, 16, 1, 1, 0, 1, 1),        # pointwise on 25-pixel images: the 1x1 pass must decline (H*W % 4)
 ]
 
 
