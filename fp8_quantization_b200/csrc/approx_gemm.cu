@@ -680,7 +680,7 @@ approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
     if (*a.offgrid != 0) return;   // some operand is off the FP8 grid: the generic kernel takes over
     if (a.gate && *a.gate == 0) return;
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ __align__(8) uint64_t full_bar[ST];                    // TMA: "stage s has landed"
+    __shared__ __align__(8) uint64_t full_bar[2 * ST];                // TMA: [s] "stage s has landed", [ST + s] "every warp has read stage s"
     uint32_t* As = reinterpret_cast<uint32_t*>(smem + ((a.lut_bytes + 127) & ~127));   // [ST][KT][BM], 128-byte aligned (TMA)
     uint32_t* Bs = As + ST * KT * BM;                                 // [ST][KT][BN]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -699,7 +699,7 @@ approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
     if (tma) {
         if (tid == 0) {
 #pragma unroll
-            for (int s = 0; s < ST; ++s) mbar_init(bar_u + 8u * s, 1);
+            for (int s = 0; s < ST; ++s) { mbar_init(bar_u + 8u * s, 1); mbar_init(bar_u + 8u * (ST + s), WARPS); }
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
         __syncthreads();   // nobody polls a barrier before it is initialised
@@ -812,11 +812,20 @@ approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
         for (int kt = 0; kt < nk; ++kt) {
             const uint32_t it = it_base + (uint32_t)kt;
             const int stage = tma ? (int)(it % ST) : kt % ST;
-            if (tma) mbar_wait(bar_u + 8u * stage, (it / ST) & 1u);
-            else     cp_async_wait<ST - 2>();
-            __syncthreads();
-            if (kt + ST - 1 < nk) load_tile(kt0 + kt + ST - 1, tma ? (int)((it + ST - 1) % ST) : (kt + ST - 1) % ST);
-            cp_async_commit();
+            if (tma) {
+                // no CTA-wide barrier per k tile: a warp only waits for its data; warp 0 (whose lane 0 issues the
+                // loads) additionally waits until every warp has released the stage it is about to refill
+                mbar_wait(bar_u + 8u * stage, (it / ST) & 1u);
+                if (warp == 0 && kt + ST - 1 < nk) {
+                    if (it >= 1) mbar_wait(bar_u + 8u * (ST + (it - 1) % ST), ((it - 1) / ST) & 1u);
+                    load_tile(kt0 + kt + ST - 1, (int)((it + ST - 1) % ST));
+                }
+            } else {
+                cp_async_wait<ST - 2>();
+                __syncthreads();
+                if (kt + ST - 1 < nk) load_tile(kt0 + kt + ST - 1, (kt + ST - 1) % ST);
+                cp_async_commit();
+            }
             const uint32_t* Asm = As + stage * KT * BM + warp * RPW;
             const uint32_t* Bsm = Bs + stage * KT * BN + lane * CPL;
 #pragma unroll (KT >= 16 ? 4 : 2)
@@ -863,6 +872,10 @@ approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
                 for (int i = 0; i < RPW; ++i)
 #pragma unroll
                     for (int j = 0; j < CPL; ++j) macc = fmaxf(macc, fabsf(acc[i][j]));
+            }
+            if (tma) {   // this warp is done with the stage
+                __syncwarp();
+                if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_u + 8u * (ST + stage)) : "memory");
             }
         }
     };
