@@ -104,6 +104,10 @@ SIGNATURES = {
     "b200_fq_gemm_tc_workspace_bytes": (c_sz, [c_i64, c_i64, c_i64]),
     "b200_fq_gemm_tc": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_sz,
                                 c_vp]),
+    "b200_fq_gemm_tc_bplane_bytes": (c_sz, [c_i64, c_i64]),
+    "b200_fq_gemm_tc_prepare_b": (c_int, [c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_sz, c_vp]),
+    "b200_fq_gemm_tc_pre": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_sz,
+                                    c_vp]),
     "b200_conv_out_shape": (c_int, [ctypes.POINTER(ConvGeom), ctypes.POINTER(c_i64), ctypes.POINTER(ctypes.c_int32),
                                     ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32),
                                     ctypes.POINTER(ctypes.c_int32)]),

@@ -14,6 +14,7 @@ import torch
 from torch import nn
 
 from . import ops
+from . import quantization as _Q
 from .quantization import BNFusedHijacker, QuantizationHijacker
 
 
@@ -41,7 +42,10 @@ class _ApproxMixin:
                 q = self.res_quantizer.quantizer
                 return ops.qamaa_matmul(x, y, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits, x_bias=x_bias,
                                         y_bias=y_bias)
-            return ops.fq_matmul(x, y)               # `x @ y[:, i]` per column (:968-969): tcgen05
+            # `x @ y[:, i]` per column (:968-969): tcgen05.  Opt-in (quantization.enable_fusions): `+ bias` in the kernel's
+            # epilogue, and the bf16 plane of cached fixed-range weights built once
+            return ops.fq_matmul(x, y, bias=self.__dict__.pop("_b200_plain_bias", None),
+                                 cache_b=self.__dict__.get("_b200_wcache") is not None)
         # single output column (every depthwise group): int32-TENSOR biases in the reference
         # (:985-994) -> integer-pow numerics, no quantize_after_mult_and_add branch
         if self.approx_flag:
@@ -64,6 +68,10 @@ class QCustomLinearTorch(_ApproxMixin, QuantizationHijacker, nn.Linear):
         weight = weight.contiguous()
         lead = x.shape[:-1]
         x2 = x.reshape(-1, x.shape[-1]) if x.dim() != 2 else x
+        if bias is not None and _Q.FUSED_GEMM_EPILOGUE and not self.approx_flag and not self.quantize_after_mult_and_add \
+                and weight.shape[0] != 1 and x2.is_cuda and not self.training:
+            self.__dict__["_b200_plain_bias"] = bias      # plain matmul: the tensor-core kernel adds the bias itself
+            bias = None
         if self.approx_flag and weight.shape[0] != 1 and "_b200_epilogue" in self.__dict__:
             # opt-in fused epilogue (quantization.FUSED_GEMM_EPILOGUE): `+ bias` and the activation inside the GEMM
             self.__dict__["_b200_ep_args"] = dict(self.__dict__.pop("_b200_epilogue"), bias=bias)

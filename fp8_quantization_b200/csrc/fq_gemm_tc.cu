@@ -359,9 +359,48 @@ extern "C" size_t b200_fq_gemm_tc_workspace_bytes(int64_t Mrows, int64_t K, int6
     return kTcFlagBytes + (size_t)round_up((Mrows + N) * Kp * 2, 256) + 256;
 }
 
-extern "C" int b200_fq_gemm_tc(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, float* C,
-                               int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float* bias_dev, void* workspace,
-                               size_t workspace_bytes, void* stream)
+// The right operand (the layer's fake-quantized weights) is the same tensor call after call once the ranges are
+// fixed: b200_fq_gemm_tc_prepare_b converts it ONCE into the bf16 plane the kernel's tensor map reads
+// ([256-byte header: int32 "not exact in bf16" flag][N][Kp] bf16), b200_fq_gemm_tc_pre then skips that convert pass.
+extern "C" size_t b200_fq_gemm_tc_bplane_bytes(int64_t K, int64_t N)
+{
+    if (K < 0 || N < 0) return 0;
+    const int64_t Kp = round_up(K > 0 ? K : 1, TC_BK);
+    return kTcFlagBytes + (size_t)round_up(N * Kp * 2, 256);
+}
+
+static int convert_b(const float* B, int64_t sb_k, int64_t sb_n, int64_t K, int64_t N, int64_t Kp, __nv_bfloat16* Bh, int* flag,
+                     cudaStream_t st)
+{
+    if (sb_k == 1) {
+        const int64_t n = N * (Kp / 8);
+        to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(B, sb_n, 1, Bh, N, K, Kp, flag);
+    } else {
+        to_bf16_kernel<false><<<dim3((unsigned)ceil_div(N, 32), (unsigned)(Kp / 32)), 256, 0, st>>>(B, sb_n, sb_k, Bh, N, K, Kp, flag);
+    }
+    B200_LAUNCH_CHECK("to_bf16_kernel<B>");
+    return B200_OK;
+}
+
+extern "C" int b200_fq_gemm_tc_prepare_b(const float* B, int64_t sb_k, int64_t sb_n, int64_t K, int64_t N, void* bplane,
+                                         size_t bplane_bytes, void* stream)
+{
+    if (int rc = check_device()) return rc;
+    if (K < 1 || N < 1 || !B || !bplane) { set_error("b200_fq_gemm_tc_prepare_b: bad argument"); return B200_ERR_ARGUMENT; }
+    if (bplane_bytes < b200_fq_gemm_tc_bplane_bytes(K, N) || ((uintptr_t)bplane & 255) != 0) {
+        set_error("b200_fq_gemm_tc_prepare_b: plane buffer too small or not 256-byte aligned (see b200_fq_gemm_tc_bplane_bytes)");
+        return B200_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int* flag = reinterpret_cast<int*>(bplane);
+    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
+    return convert_b(B, sb_k, sb_n, K, N, round_up(K, TC_BK), reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(bplane) + kTcFlagBytes),
+                     flag, st);
+}
+
+static int fq_gemm_tc_impl(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, const void* bplane, float* C,
+                           int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float* bias_dev, void* workspace,
+                           size_t workspace_bytes, void* stream)
 {
     if (int rc = check_device()) return rc;
     if (Mrows < 0 || K < 0 || N < 0) { set_error("b200_fq_gemm_tc: bad argument"); return B200_ERR_ARGUMENT; }
@@ -386,20 +425,20 @@ extern "C" int b200_fq_gemm_tc(const float* A, int64_t lda, const float* B, int6
     const int64_t Kp = round_up(K, TC_BK);
     int* flag = reinterpret_cast<int*>(workspace);
     __nv_bfloat16* Ah = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(workspace) + kTcFlagBytes);
-    __nv_bfloat16* Bh = Ah + Mrows * Kp;
-    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
+    const __nv_bfloat16* Bh = Ah + Mrows * Kp;
+    if (bplane) {   // prepared right operand: its plane, and its "inexact" flag as the start value of this call's flag
+        Bh = reinterpret_cast<const __nv_bfloat16*>(reinterpret_cast<const char*>(bplane) + kTcFlagBytes);
+        B200_CUDA_TRY(cudaMemcpyAsync(flag, bplane, 4, cudaMemcpyDeviceToDevice, st));
+    } else {
+        B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
+    }
     {
         const int64_t n = Mrows * (Kp / 8);
         to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(A, lda, 1, Ah, Mrows, K, Kp, flag);
         B200_LAUNCH_CHECK("to_bf16_kernel<A>");
     }
-    if (sb_k == 1) {
-        const int64_t n = N * (Kp / 8);
-        to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(B, sb_n, 1, Bh, N, K, Kp, flag);
-    } else {
-        to_bf16_kernel<false><<<dim3((unsigned)ceil_div(N, 32), (unsigned)(Kp / 32)), 256, 0, st>>>(B, sb_n, sb_k, Bh, N, K, Kp, flag);
-    }
-    B200_LAUNCH_CHECK("to_bf16_kernel<B>");
+    if (!bplane)
+        if (int rc = convert_b(B, sb_k, sb_n, K, N, Kp, Ah + Mrows * Kp, flag, st)) return rc;
 
     const int nkb = (int)(Kp / TC_BK);
     static PerDeviceOnce once;
@@ -429,6 +468,21 @@ extern "C" int b200_fq_gemm_tc(const float* A, int64_t lda, const float* B, int6
     // runs only if the convert pass found an operand that is not exact in bf16
     pair_gemm_kernel<PlainOp><<<pair_gemm_grid(Mrows, N), 256, 0, st>>>(asrc, bsrc, C, ldc, Mrows, K, N, pop, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<PlainOp>(conditional)");
-    set_path("tcgen05");
+    set_path(bplane ? "tcgen05-preB" : "tcgen05");
     return B200_OK;
+}
+
+extern "C" int b200_fq_gemm_tc(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, float* C,
+                               int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float* bias_dev, void* workspace,
+                               size_t workspace_bytes, void* stream)
+{
+    return fq_gemm_tc_impl(A, lda, B, sb_k, sb_n, nullptr, C, ldc, Mrows, K, N, bias_dev, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200_fq_gemm_tc_pre(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, const void* bplane,
+                                   float* C, int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float* bias_dev,
+                                   void* workspace, size_t workspace_bytes, void* stream)
+{
+    if (!bplane || K < 1) { set_error("b200_fq_gemm_tc_pre: needs a prepared plane (b200_fq_gemm_tc_prepare_b) and K >= 1"); return B200_ERR_ARGUMENT; }
+    return fq_gemm_tc_impl(A, lda, B, sb_k, sb_n, bplane, C, ldc, Mrows, K, N, bias_dev, workspace, workspace_bytes, stream);
 }

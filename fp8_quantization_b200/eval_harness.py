@@ -163,7 +163,7 @@ class GraphedForward:
         # (FPQuantizer.forward assigns a fresh custom_bias on every call, fp8_quantizer.py:244)
         for m in self.model.modules():
             cached += [t for t in (getattr(m, "custom_bias", None), getattr(m, "maxval", None)) if torch.is_tensor(t)]
-        return dict(ops._WORKSPACES), cached
+        return dict(ops._WORKSPACES), cached, dict(ops._BPLANES)
 
 
 _N_CLASSES = {}

@@ -291,10 +291,31 @@ def qamaa_matmul(x, y, n_bits, maxval, mantissa_bits, sign_bits, out=None, x_bia
     return out
 
 
-def fq_matmul(x, y, bias=None, out=None):
+_BPLANES = {}
+
+
+def _prepared_b(lib, y, K, N):
+    """bf16 plane of a right operand that stays the same call after call (b200_fq_gemm_tc_prepare_b), built once per
+    (storage, version, view).  The entry holds `y` itself, so its storage cannot be freed and reused under the key."""
+    key = (y.data_ptr(), y._version if not y.is_inference() else -1, tuple(y.shape), tuple(y.stride()), y.device)
+    ent = _BPLANES.get(key)
+    if ent is None:
+        if len(_BPLANES) >= 512:
+            _BPLANES.clear()
+        nbytes = lib.b200_fq_gemm_tc_bplane_bytes(K, N)
+        plane = torch.empty(nbytes, dtype=torch.uint8, device=y.device)
+        _lib.check(lib.b200_fq_gemm_tc_prepare_b(_ptr(y), y.stride(0), y.stride(1), K, N, _ptr(plane), nbytes, _stream()))
+        ent = _BPLANES[key] = (plane, y)
+    return ent[0]
+
+
+def fq_matmul(x, y, bias=None, out=None, cache_b=False):
     """The non-approx `x @ y` of fake-quantized operands (approx/approx_calculation.py:968-969, :704-705) on the
     tcgen05 tensor cores: bf16 operands (exact for FP8-grid values), fp32 accumulation in tensor memory.
-    Operands that are not exact in bf16 are detected on the device and computed in fp32 instead."""
+    Operands that are not exact in bf16 are detected on the device and computed in fp32 instead.
+    bias: [N], added to every row in the kernel's epilogue (`output += bias`, :1020-1021).
+    cache_b (opt-in): `y` is a tensor that stays the same call after call (fixed-range weights): its bf16 plane is
+    built once and reused (b200_fq_gemm_tc_pre)."""
     lib = _lib.load()
     _require_cuda(x, y)
     assert x.dim() == 2 and y.dim() == 2 and x.shape[1] == y.shape[0]
@@ -312,8 +333,13 @@ def fq_matmul(x, y, bias=None, out=None):
         assert b.numel() == N
     ws = _workspace(x.device, lib.b200_fq_gemm_tc_workspace_bytes(Mrows, K, N))
     with torch.cuda.device(x.device):
-        rc = lib.b200_fq_gemm_tc(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out), out.stride(0),
-                                 Mrows, K, N, _ptr(b), _ptr(ws), ws.numel(), _stream())
+        if cache_b and K > 0 and N > 0 and Mrows > 0:
+            plane = _prepared_b(lib, y, K, N)
+            rc = lib.b200_fq_gemm_tc_pre(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(plane), _ptr(out),
+                                         out.stride(0), Mrows, K, N, _ptr(b), _ptr(ws), ws.numel(), _stream())
+        else:
+            rc = lib.b200_fq_gemm_tc(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(out), out.stride(0),
+                                     Mrows, K, N, _ptr(b), _ptr(ws), ws.numel(), _stream())
     _lib.check(rc)
     return out
 

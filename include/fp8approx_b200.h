@@ -220,6 +220,17 @@ int b200_fq_gemm_tc(const float *A, int64_t lda, const float *B, int64_t sb_k, i
                     int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *bias_dev,
                     void *workspace, size_t workspace_bytes, void *stream);
 
+/* Prepared right operand (opt-in): once the ranges are fixed the fake-quantized weights are the same tensor in every
+ * call, so their bf16 plane can be built once.  b200_fq_gemm_tc_prepare_b writes it (and whether it is exact in bf16)
+ * to `bplane` (device, 256-byte aligned, b200_fq_gemm_tc_bplane_bytes(K, N) bytes); b200_fq_gemm_tc_pre is
+ * b200_fq_gemm_tc without the convert pass over B (B itself is still read by the fp32 fallback kernel). */
+size_t b200_fq_gemm_tc_bplane_bytes(int64_t K, int64_t N);
+int b200_fq_gemm_tc_prepare_b(const float *B, int64_t sb_k, int64_t sb_n, int64_t K, int64_t N, void *bplane,
+                              size_t bplane_bytes, void *stream);
+int b200_fq_gemm_tc_pre(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n, const void *bplane,
+                        float *C, int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float *bias_dev,
+                        void *workspace, size_t workspace_bytes, void *stream);
+
 /* Fused input fake-quantizer: the hijacker's `x = self.activation_quantizer(x)`
  * (quantization/hijacker.py:82-88 -> fp8_quantizer.py:97-173) evaluated inside the operand decode pass of the
  * GEMM / conv instead of as a separate pass over the activations.  A / x then hold the RAW activations;

@@ -110,3 +110,30 @@ def test_plain_linear_layer_uses_tensor_cores(fq):
         wq, b = layer.get_params()
         ref = (xq.double().reshape(-1, 192) @ wq.double().t() + b.double()).reshape(3, 50, 160)
     assert float((y.double() - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+
+
+@pytest.mark.parametrize("shape", [(300, 200, 130), (129, 1000, 257), (512, 768, 768)])
+def test_prepared_right_operand_equals_per_call_conversion(fq, shape):
+    """b200_fq_gemm_tc_prepare_b + b200_fq_gemm_tc_pre (opt-in: the bf16 plane of fixed-range weights built once) return
+    the bits of b200_fq_gemm_tc, for both operand layouts, with the bias epilogue, on repeated calls; a right operand
+    that is not exact in bf16 carries its flag in the plane header and still takes the fp32 fallback."""
+    Mr, K, N = shape
+    g = torch.Generator().manual_seed(7 * K + N)
+    x = _fakequant(fq, (torch.randn(Mr, K, generator=g) * 0.5).cuda(), 3, False)
+    w = _fakequant(fq, (torch.randn(N, K, generator=g) * 0.05).cuda(), 3, True)
+    bias = (torch.randn(N, generator=g) * 0.01).cuda()
+    for y in (w.t(), w.t().contiguous()):
+        want = fq.ops.fq_matmul(x, y, bias=bias)
+        assert fq.ops.last_path() == "tcgen05"
+        for _ in range(2):
+            got = fq.ops.fq_matmul(x, y, bias=bias, cache_b=True)
+            assert fq.ops.last_path() == "tcgen05-preB"
+            assert torch.equal(got.view(torch.int32), want.view(torch.int32))
+        got2 = fq.ops.fq_matmul(x * 0.5, y, cache_b=True)           # same plane, other activations
+        assert torch.equal(got2.view(torch.int32), fq.ops.fq_matmul(x * 0.5, y).view(torch.int32))
+    w_bad = w.clone()
+    w_bad[3, 5] = 0.1234567                                          # not exact in bf16
+    got = fq.ops.fq_matmul(x, w_bad.t(), cache_b=True)
+    want = fq.ops.fq_matmul(x, w_bad.t())
+    assert torch.equal(got.view(torch.int32), want.view(torch.int32))
+    _check(got, x, w_bad.t())
