@@ -19,6 +19,7 @@
 // (+bias) -> fp32 stores.  If the flag is up (operands not fake-quantized), the tensor-core kernel
 // exits at once and an fp32 CUDA-core kernel computes the product instead: still no CPU path.
 #include <cuda.h>
+#include <cstring>
 #include <cuda_bf16.h>
 
 #include <algorithm>
@@ -89,6 +90,42 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// Epilogue store of one 32 x 32 fp32 chunk through shared memory and TMA: thread = row, v = its 32 consecutive
+// columns.  The chunk is written in the 128-byte-swizzle layout the C tensor map expects (16-byte chunk q of row r at
+// chunk q ^ (r & 7): conflict-free 128-bit shared stores), then ONE lane issues cp.async.bulk.tensor (global <- shared):
+// full 128-byte lines instead of 16 bytes per row per store instruction, ragged edges clipped by the tensor map.
+// `buf`: this warp's 4 KB staging buffer for this chunk parity (1024-byte aligned).
+constexpr int TC_EPI_BYTES = 4 * 2 * 4096;     // 4 epilogue warps x double buffer x (32 rows x 128 B)
+__device__ __forceinline__ void epi_store_chunk_tma(const CUtensorMap* mapC, uint8_t* buf, const uint32_t (&v)[32], int lane,
+                                                    const float* __restrict__ bias, int64_t n, int64_t N, int row0)
+{
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the store that last read `buf` is done with it
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        float4 o = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]),
+                               __uint_as_float(v[4 * q + 3]));
+        if (bias) {
+            if (n + 4 * q + 4 <= N) {
+                const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + n + 4 * q));
+                o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+            } else {
+                if (n + 4 * q < N) o.x += __ldg(bias + n + 4 * q);
+                if (n + 4 * q + 1 < N) o.y += __ldg(bias + n + 4 * q + 1);
+                if (n + 4 * q + 2 < N) o.z += __ldg(bias + n + 4 * q + 2);
+            }
+        }
+        *reinterpret_cast<float4*>(buf + lane * 128 + ((q ^ (lane & 7)) << 4)) = o;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    if (lane == 0) {
+        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                     ::"l"(mapC), "r"(s32(buf)), "r"((int)n), "r"(row0) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+}
+
 // Shared-memory matrix descriptor of a K-major tile stored as TMA's 128-byte swizzle writes it:
 // row r at byte r*128, 16-byte chunks XOR-ed with (r & 7); 8-row groups are 1024 B apart (SBO).
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr)
@@ -114,7 +151,8 @@ struct TcSmem {
     static constexpr int B_BYTES = BN * TC_BK * 2;
     static constexpr int STAGE = A_BYTES + B_BYTES;
     static constexpr int BARS = ST * STAGE;                  // full[ST], empty[ST], tmem_full[2], tmem_empty[2], TMEM base
-    static constexpr int TOTAL = BARS + (2 * ST + 4) * 8 + 16 + 1024;   // + slack for the 1024 B alignment
+    static constexpr int EPI = BARS + 1024;                  // epilogue staging (TMA stores), 1024-byte aligned
+    static constexpr int TOTAL = 1024 + BARS + 1024 + TC_EPI_BYTES;   // alignment slack, stages, barriers, staging
 };
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar)
@@ -129,6 +167,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar)
 template <int BN, int ST>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+                  const __grid_constant__ CUtensorMap mapC, int tma_store,
                   float* __restrict__ C, int64_t ldc, int64_t Mrows, int64_t N, int nkb, int m_blocks, int n_tiles,
                   const float* __restrict__ bias, const int* __restrict__ inexact)
 {
@@ -213,7 +252,10 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 uint32_t v[32];
                 tc_ld32(tmem + ((uint32_t)(w * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
                 const int64_t n = (int64_t)n0 + c * 32;
-                if (row < Mrows && n < N) {
+                if (tma_store) {
+                    if (n < N && (int64_t)m0 + w * 32 < Mrows)
+                        epi_store_chunk_tma(&mapC, smem + L::EPI + (w * 2 + (c & 1)) * 4096, v, lane, bias, n, N, m0 + w * 32);
+                } else if (row < Mrows && n < N) {
                     if (vec_ok && n + 32 <= N) {
 #pragma unroll
                         for (int j = 0; j < 32; j += 4) {
@@ -236,11 +278,204 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
             __syncwarp();
             if (lane == 0) mbar_arrive(tmem_empty + as);    // this warp's quarter of the stage is drained
         }
+        if (tma_store && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores complete before exit
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 2)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)(2 * BN)) : "memory");
+}
+
+// ---- CTA-pair variant (cta_group::2) ------------------------------------------------------------------------------
+// Two CTAs of a cluster (the two SMs of a TPC) compute ONE 256 x 256 output tile: each loads its own 128 rows of A and
+// its own 128 columns (rows of the [N][K] plane) of B; the LEADER CTA's single MMA thread issues
+// tcgen05.mma.cta_group::2 (M = 256, N = 256), which reads A from each CTA's shared memory for that CTA's half of the
+// accumulator rows and B from BOTH CTAs' shared memory.  Per SM and k block that is 16 KB of A + 16 KB of B instead of
+// 16 + 32: the shared-memory operand feed -- what holds the single-CTA kernel at ~55 % tensor-pipe activity -- is
+// halved, and six pipeline stages fit where four did.
+//   full[s]   (leader): 1 arrival (leader's producer: expect_tx of BOTH CTAs' bytes) + the TMA bytes of both CTAs
+//   empty[s]  (each CTA): tcgen05.commit multicast to both CTAs when the MMAs that read stage s have finished
+//   tmem_full[a]  (each CTA): commit multicast: accumulator stage a is complete
+//   tmem_empty[a] (leader): 8 arrivals = 4 epilogue warps of each CTA (the peer's arrive remotely)
+constexpr int TC2_BN = 256, TC2_ST = 6, TC2_HALF_N = 128;
+struct Tc2Smem {
+    static constexpr int A_BYTES = TC_BM * TC_BK * 2;          // 16 KB: this CTA's 128 rows
+    static constexpr int B_BYTES = TC2_HALF_N * TC_BK * 2;     // 16 KB: this CTA's 128 columns of B
+    static constexpr int STAGE = A_BYTES + B_BYTES;
+    static constexpr int BARS = TC2_ST * STAGE;
+    static constexpr int EPI = BARS + 1024;
+    static constexpr int TOTAL = 1024 + BARS + 1024 + TC_EPI_BYTES;
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank()
+{
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// both CTAs execute this; the byte count lands on the LEADER's barrier (same offset, CTA rank 0)
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint32_t leader_bar, int c0, int c1)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(s32(dst)), "l"(map), "r"(leader_bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ uint32_t map_to_rank0(uint32_t local_addr)
+{
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(r) : "r"(local_addr));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr)
+{
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint64_t* bar)
+{
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(s32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
+fq_gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+                   const __grid_constant__ CUtensorMap mapC, int tma_store,
+                   float* __restrict__ C, int64_t ldc, int64_t Mrows, int64_t N, int nkb, int m_blocks, int n_tiles,
+                   const float* __restrict__ bias, const int* __restrict__ inexact)
+{
+    if (*inexact != 0) return;   // uniform over the grid: both CTAs of a pair leave together
+    using L = Tc2Smem;
+    constexpr int ST = TC2_ST, BN = TC2_BN;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::BARS);
+    uint64_t* empty = full + ST;
+    uint64_t* tmem_full = empty + ST;      // [2]
+    uint64_t* tmem_empty = tmem_full + 2;  // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+
+    if (threadIdx.x == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < ST; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {   // the same logical warp in both CTAs: 2 accumulator stages x 256 columns = all of tensor memory
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(tmem_slot)), "r"((uint32_t)(2 * BN)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();          // the peer's barriers exist before anything arrives on them
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        // ===== TMA producer (both CTAs): own rows of A, own columns of B; bytes are counted on the leader's barrier =====
+        int it = 0;
+        for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+            const int m0 = (tile % m_blocks) * (2 * TC_BM) + (int)rank * TC_BM;
+            const int n0 = (tile / m_blocks) * BN + (int)rank * TC2_HALF_N;
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+                const int s = it % ST;
+                mbar_wait(empty + s, ((it / ST) & 1) ^ 1);
+                const uint32_t lbar = map_to_rank0(s32(full + s));
+                if (leader) mbar_expect_tx(full + s, 2 * L::STAGE);
+                tma_load_2d_pair(smem + s * L::STAGE, &mapA, lbar, kb * TC_BK, m0);
+                tma_load_2d_pair(smem + s * L::STAGE + L::A_BYTES, &mapB, lbar, kb * TC_BK, n0);
+            }
+        }
+    } else if (warp == 1 && lane == 0) {
+        if (leader) {
+            // ===== MMA issuer: one thread of the leader CTA drives both SMs' tensor cores =====
+            constexpr uint32_t idesc = umma_idesc_bf16(2 * TC_BM, BN);
+            int it = 0, ti = 0;
+            for (int tile = pair; tile < n_tiles; tile += n_pairs, ++ti) {
+                const int as = ti & 1;
+                mbar_wait(tmem_empty + as, ((ti >> 1) & 1) ^ 1);     // both CTAs' epilogues have drained this stage
+                tc_fence_after();
+                const uint32_t d_tmem = tmem + (uint32_t)(as * BN);
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % ST;
+                    mbar_wait(full + s, (it / ST) & 1);
+                    tc_fence_after();
+                    const uint64_t adesc = umma_desc_sw128(s32(smem + s * L::STAGE));
+                    const uint64_t bdesc = umma_desc_sw128(s32(smem + s * L::STAGE + L::A_BYTES));
+#pragma unroll
+                    for (int k = 0; k < TC_BK / TC_UK; ++k)
+                        tc_mma_bf16_pair(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+                    tc_commit_pair(empty + s);     // frees stage s in BOTH CTAs
+                }
+                tc_commit_pair(tmem_full + as);    // accumulator complete, in both CTAs
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue (both CTAs): own 128 rows x 256 columns, TMEM -> registers -> (+bias) -> global fp32 =====
+        const int w = warp - 4;
+        const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+        int ti = 0;
+        for (int tile = pair; tile < n_tiles; tile += n_pairs, ++ti) {
+            const int m0 = (tile % m_blocks) * (2 * TC_BM) + (int)rank * TC_BM, n0 = (tile / m_blocks) * BN;
+            const int as = ti & 1;
+            mbar_wait(tmem_full + as, (ti >> 1) & 1);
+            tc_fence_after();
+            const int64_t row = (int64_t)m0 + w * 32 + lane;
+            float* crow = C + row * ldc;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t v[32];
+                tc_ld32(tmem + ((uint32_t)(w * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
+                const int64_t n = (int64_t)n0 + c * 32;
+                if (tma_store) {
+                    if (n < N && (int64_t)m0 + w * 32 < Mrows)
+                        epi_store_chunk_tma(&mapC, smem + L::EPI + (w * 2 + (c & 1)) * 4096, v, lane, bias, n, N, m0 + w * 32);
+                } else if (row < Mrows && n < N) {
+                    if (vec_ok && n + 32 <= N) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            float4 o = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                                   __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+                            if (bias) {
+                                const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + n + j));
+                                o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+                            }
+                            *reinterpret_cast<float4*>(crow + n + j) = o;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (n + j < N) crow[n + j] = __uint_as_float(v[j]) + (bias ? __ldg(bias + n + j) : 0.0f);
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(map_to_rank0(s32(tmem_empty + as)));   // counted on the leader
+        }
+        if (tma_store && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();          // nobody leaves while the pair's barriers / shared memory may still be signalled
+    if (warp == 2)
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)(2 * BN)) : "memory");
 }
 
 // ---- convert pass: fp32 operand -> bf16 plane [rows][Kp], k contiguous, zero padded to Kp ---------
@@ -346,6 +581,20 @@ static int make_map(EncodeTiledFn enc, CUtensorMap* map, const void* base, int64
     return B200_OK;
 }
 
+// C [Mrows][ldc] fp32 as a 2-D tensor {N, Mrows}, box 32 columns x 32 rows, 128-byte swizzle (the epilogue's TMA stores)
+static int make_map_c(EncodeTiledFn enc, CUtensorMap* map, const float* C, int64_t ldc, int64_t Mrows, int64_t N)
+{
+    const cuuint64_t gdim[2] = {(cuuint64_t)N, (cuuint64_t)Mrows};
+    const cuuint64_t gstride[1] = {(cuuint64_t)ldc * 4};
+    const cuuint32_t box[2] = {32, 32};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(C), gdim, gstride, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(C) failed (code " + std::to_string((int)r) + ")"); return B200_ERR_CUDA; }
+    return B200_OK;
+}
+
 constexpr size_t kTcFlagBytes = 256;
 
 }  // namespace b200
@@ -446,29 +695,48 @@ static int fq_gemm_tc_impl(const float* A, int64_t lda, const float* B, int64_t 
     if (int rc = once.get(&sms, []() -> int {
             B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<256, 4>::TOTAL));
             B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<128, 4>::TOTAL));
+            B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Tc2Smem::TOTAL));
             return B200_OK;
         }))
         return rc;
-    CUtensorMap mapA, mapB;
+    CUtensorMap mapA, mapB, mapC;
     if (int rc = make_map(enc, &mapA, Ah, Mrows, Kp, TC_BM)) return rc;
-    if (N > 128) {
+    // epilogue through TMA stores when C allows a tensor map (16-byte aligned base and pitch, extents in int32);
+    // B200_TC_TMA_STORE=0: direct stores from registers
+    const char* se = getenv("B200_TC_TMA_STORE");
+    int tma_store = ((ldc & 3) == 0 && ((uintptr_t)C & 15) == 0 && Mrows < ((int64_t)1 << 31) && N < ((int64_t)1 << 31) &&
+                     (bias_dev == nullptr || ((uintptr_t)bias_dev & 15) == 0) && !(se && atoi(se) == 0)) ? 1 : 0;
+    memset(&mapC, 0, sizeof(mapC));
+    if (tma_store)
+        if (int rc = make_map_c(enc, &mapC, C, ldc, Mrows, N)) return rc;
+    // CTA pairs (cta_group::2, 256 x 256 tiles) where there is enough work for them; B200_TC_PAIR=0: single-CTA kernel
+    const char* pe = getenv("B200_TC_PAIR");
+    const bool pair_ok = N > 128 && Mrows > 128 && sms >= 2 && !(pe && atoi(pe) == 0) &&
+                         ((pe && atoi(pe) == 2) || ceil_div(Mrows, 2 * TC_BM) * ceil_div(N, TC2_BN) >= sms / 4);   // 2: force (tests)
+    if (pair_ok) {
+        if (int rc = make_map(enc, &mapB, Bh, N, Kp, TC2_HALF_N)) return rc;
+        const int m_blocks = (int)ceil_div(Mrows, 2 * TC_BM), n_tiles = m_blocks * (int)ceil_div(N, TC2_BN);
+        const int pairs = std::min(n_tiles, sms / 2);
+        fq_gemm_tc2_kernel<<<(unsigned)(2 * pairs), TC_THREADS, Tc2Smem::TOTAL, st>>>(
+            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
+    } else if (N > 128) {
         constexpr int BN = 256, ST = 4;
         if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
         const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
         fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
-            mapA, mapB, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
+            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
     } else {
         constexpr int BN = 128, ST = 4;
         if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
         const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
         fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
-            mapA, mapB, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
+            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
     }
     B200_LAUNCH_CHECK("fq_gemm_tc_kernel");
     // runs only if the convert pass found an operand that is not exact in bf16
     pair_gemm_kernel<PlainOp><<<pair_gemm_grid(Mrows, N), 256, 0, st>>>(asrc, bsrc, C, ldc, Mrows, K, N, pop, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<PlainOp>(conditional)");
-    set_path(bplane ? "tcgen05-preB" : "tcgen05");
+    set_path(pair_ok ? (bplane ? "tcgen05-pair-preB" : "tcgen05-pair") : (bplane ? "tcgen05-preB" : "tcgen05"));
     return B200_OK;
 }
 

@@ -137,3 +137,29 @@ def test_prepared_right_operand_equals_per_call_conversion(fq, shape):
     want = fq.ops.fq_matmul(x, w_bad.t())
     assert torch.equal(got.view(torch.int32), want.view(torch.int32))
     _check(got, x, w_bad.t())
+
+
+@pytest.mark.parametrize("shape", [(300, 200, 130), (129, 1000, 257), (512, 768, 768), (1000, 77, 513), (2048, 4096, 1024)])
+def test_cta_pair_kernel_equals_single_cta_kernel(fq, shape):
+    """fq_gemm_tc2_kernel (cta_group::2: a CTA pair per 256 x 256 tile, B shared across the two SMs) against the
+    single-CTA kernel: same products, same fp32 accumulation in tensor memory over the same k order -> same bits;
+    ragged rows / columns / K through TMA zero fill, bias epilogue, prepared right operand."""
+    import os
+    Mr, K, N = shape
+    g = torch.Generator().manual_seed(3 * K + N)
+    x = _fakequant(fq, (torch.randn(Mr, K, generator=g) * 0.5).cuda(), 3, False)
+    w = _fakequant(fq, (torch.randn(N, K, generator=g) * 0.05).cuda(), 3, True)
+    bias = (torch.randn(N, generator=g) * 0.01).cuda()
+    outs = {}
+    for mode in ("0", "2"):
+        os.environ["B200_TC_PAIR"] = mode
+        try:
+            outs[mode] = (fq.ops.fq_matmul(x, w.t(), bias=bias), fq.ops.last_path(),
+                          fq.ops.fq_matmul(x, w.t(), cache_b=True), fq.ops.last_path())
+        finally:
+            os.environ.pop("B200_TC_PAIR", None)
+    assert outs["0"][1] == "tcgen05" and outs["2"][1] == "tcgen05-pair", (outs["0"][1], outs["2"][1])
+    assert outs["2"][3] == "tcgen05-pair-preB"
+    _check(outs["2"][0], x, w.t(), bias)
+    assert torch.equal(outs["0"][0].view(torch.int32), outs["2"][0].view(torch.int32))
+    assert torch.equal(outs["0"][2].view(torch.int32), outs["2"][2].view(torch.int32))
