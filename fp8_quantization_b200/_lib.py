@@ -108,6 +108,8 @@ SIGNATURES = {
     "b200_fq_gemm_tc_prepare_b": (c_int, [c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_sz, c_vp]),
     "b200_fq_gemm_tc_pre": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_sz,
                                     c_vp]),
+    "b200_fq_gemm_tc_ex": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, ctypes.POINTER(ActQuant), ctypes.POINTER(ActQuant),
+                                   c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_sz, c_vp]),
     "b200_conv_out_shape": (c_int, [ctypes.POINTER(ConvGeom), ctypes.POINTER(c_i64), ctypes.POINTER(ctypes.c_int32),
                                     ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32),
                                     ctypes.POINTER(ctypes.c_int32)]),

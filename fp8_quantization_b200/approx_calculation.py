@@ -45,7 +45,9 @@ class _ApproxMixin:
             # `x @ y[:, i]` per column (:968-969): tcgen05.  Opt-in (quantization.enable_fusions): `+ bias` in the kernel's
             # epilogue, and the bf16 plane of cached fixed-range weights built once
             return ops.fq_matmul(x, y, bias=self.__dict__.pop("_b200_plain_bias", None),
-                                 cache_b=self.__dict__.get("_b200_wcache") is not None)
+                                 cache_b=self.__dict__.get("_b200_wcache") is not None,
+                                 act_quant=self.__dict__.pop("_b200_act_quant", None),
+                                 res_quant=self.__dict__.pop("_b200_res_quant", None))
         # single output column (every depthwise group): int32-TENSOR biases in the reference
         # (:985-994) -> integer-pow numerics, no quantize_after_mult_and_add branch
         if self.approx_flag:
@@ -58,6 +60,8 @@ class _ApproxMixin:
 
 
 class QCustomLinearTorch(_ApproxMixin, QuantizationHijacker, nn.Linear):
+    _plain_matmul_fuses_quantizers = True      # ops.fq_matmul(act_quant=, res_quant=): b200_fq_gemm_tc_ex
+
     def _fusable_input_quant(self, x):
         return self.out_features != 1          # a single output column takes the tensor-bias branch on x_q
 

@@ -26,6 +26,7 @@
 #include <mutex>
 
 #include "common.cuh"
+#include "gemm_impl.cuh"
 #include "pair_gemm.cuh"
 
 namespace b200 {
@@ -90,6 +91,22 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// A fake-quantizer evaluated inside this file's kernels (opt-in fusions): on the left operand while it is converted
+// to bf16 (the hijacker's `x = self.activation_quantizer(x)`, quantization/hijacker.py:82-88) and on the result in the
+// epilogue (`res = self.res_quantizer(res)`, :93-94).  Same element function as the stand-alone kernel
+// (quantize_to_fp8_ste_MM, quantization/quantizers/fp8_quantizer.py:119-154), with the exponent bias that kernel
+// derived from the same per-tensor maxval: bit-identical to the separate pass.
+struct FqParams {
+    const float* maxval;   // device [1] or null: no quantizer
+    const float* bias;     // device [1]
+    float Mf;
+    int sign;
+    __device__ __forceinline__ float apply(float v, float mx, float fb, bool fast) const
+    {
+        return fast ? fp8_ste_quant_fast(v, mx, (int)fb, (int)Mf, sign) : fp8_ste_quant(v, mx, fb, Mf, sign);
+    }
+};
+
 // Epilogue store of one 32 x 32 fp32 chunk through shared memory and TMA: thread = row, v = its 32 consecutive
 // columns.  The chunk is written in the 128-byte-swizzle layout the C tensor map expects (16-byte chunk q of row r at
 // chunk q ^ (r & 7): conflict-free 128-bit shared stores), then ONE lane issues cp.async.bulk.tensor (global <- shared):
@@ -97,7 +114,8 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32])
 // `buf`: this warp's 4 KB staging buffer for this chunk parity (1024-byte aligned).
 constexpr int TC_EPI_BYTES = 4 * 2 * 4096;     // 4 epilogue warps x double buffer x (32 rows x 128 B)
 __device__ __forceinline__ void epi_store_chunk_tma(const CUtensorMap* mapC, uint8_t* buf, const uint32_t (&v)[32], int lane,
-                                                    const float* __restrict__ bias, int64_t n, int64_t N, int row0)
+                                                    const float* __restrict__ bias, int64_t n, int64_t N, int row0,
+                                                    const FqParams& oq, float omx, float ofb, bool ofast)
 {
     if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the store that last read `buf` is done with it
     __syncwarp();
@@ -114,6 +132,10 @@ __device__ __forceinline__ void epi_store_chunk_tma(const CUtensorMap* mapC, uin
                 if (n + 4 * q + 1 < N) o.y += __ldg(bias + n + 4 * q + 1);
                 if (n + 4 * q + 2 < N) o.z += __ldg(bias + n + 4 * q + 2);
             }
+        }
+        if (oq.maxval) {
+            o.x = oq.apply(o.x, omx, ofb, ofast); o.y = oq.apply(o.y, omx, ofb, ofast);
+            o.z = oq.apply(o.z, omx, ofb, ofast); o.w = oq.apply(o.w, omx, ofb, ofast);
         }
         *reinterpret_cast<float4*>(buf + lane * 128 + ((q ^ (lane & 7)) << 4)) = o;
     }
@@ -169,7 +191,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const __grid_constant__ CUtensorMap mapC, int tma_store,
                   float* __restrict__ C, int64_t ldc, int64_t Mrows, int64_t N, int nkb, int m_blocks, int n_tiles,
-                  const float* __restrict__ bias, const int* __restrict__ inexact)
+                  const float* __restrict__ bias, const int* __restrict__ inexact, FqParams oq)
 {
     if (*inexact != 0) return;   // an operand does not fit bf16 exactly: the fp32 kernel takes over
     using L = TcSmem<BN, ST>;
@@ -239,6 +261,8 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         // ===== epilogue: TMEM -> registers -> (+bias) -> global fp32 =====
         const int w = warp - 4;                       // == warp % 4: the TMEM lane quarter this warp may read
         const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+        const float omx = oq.maxval ? __ldg(oq.maxval) : 0.0f, ofb = oq.maxval ? __ldg(oq.bias) : 0.0f;   // result quantizer
+        const bool ofast = oq.maxval && fp8_ste_fast_ok(ofb);
         int ti = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++ti) {
             const int m0 = (tile % m_blocks) * TC_BM, n0 = (tile / m_blocks) * BN;
@@ -254,7 +278,7 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 const int64_t n = (int64_t)n0 + c * 32;
                 if (tma_store) {
                     if (n < N && (int64_t)m0 + w * 32 < Mrows)
-                        epi_store_chunk_tma(&mapC, smem + L::EPI + (w * 2 + (c & 1)) * 4096, v, lane, bias, n, N, m0 + w * 32);
+                        epi_store_chunk_tma(&mapC, smem + L::EPI + (w * 2 + (c & 1)) * 4096, v, lane, bias, n, N, m0 + w * 32, oq, omx, ofb, ofast);
                 } else if (row < Mrows && n < N) {
                     if (vec_ok && n + 32 <= N) {
 #pragma unroll
@@ -265,12 +289,20 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                                 const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + n + j));
                                 o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
                             }
+                            if (oq.maxval) {
+                                o.x = oq.apply(o.x, omx, ofb, ofast); o.y = oq.apply(o.y, omx, ofb, ofast);
+                                o.z = oq.apply(o.z, omx, ofb, ofast); o.w = oq.apply(o.w, omx, ofb, ofast);
+                            }
                             *reinterpret_cast<float4*>(crow + n + j) = o;
                         }
                     } else {
 #pragma unroll
                         for (int j = 0; j < 32; ++j)
-                            if (n + j < N) crow[n + j] = __uint_as_float(v[j]) + (bias ? __ldg(bias + n + j) : 0.0f);
+                            if (n + j < N) {
+                                float o = __uint_as_float(v[j]);
+                                if (bias) o += __ldg(bias + n + j);
+                                crow[n + j] = oq.maxval ? oq.apply(o, omx, ofb, ofast) : o;
+                            }
                     }
                 }
             }
@@ -351,7 +383,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
 fq_gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                    const __grid_constant__ CUtensorMap mapC, int tma_store,
                    float* __restrict__ C, int64_t ldc, int64_t Mrows, int64_t N, int nkb, int m_blocks, int n_tiles,
-                   const float* __restrict__ bias, const int* __restrict__ inexact)
+                   const float* __restrict__ bias, const int* __restrict__ inexact, FqParams oq)
 {
     if (*inexact != 0) return;   // uniform over the grid: both CTAs of a pair leave together
     using L = Tc2Smem;
@@ -430,6 +462,8 @@ fq_gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
         // ===== epilogue (both CTAs): own 128 rows x 256 columns, TMEM -> registers -> (+bias) -> global fp32 =====
         const int w = warp - 4;
         const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+        const float omx = oq.maxval ? __ldg(oq.maxval) : 0.0f, ofb = oq.maxval ? __ldg(oq.bias) : 0.0f;   // result quantizer
+        const bool ofast = oq.maxval && fp8_ste_fast_ok(ofb);
         int ti = 0;
         for (int tile = pair; tile < n_tiles; tile += n_pairs, ++ti) {
             const int m0 = (tile % m_blocks) * (2 * TC_BM) + (int)rank * TC_BM, n0 = (tile / m_blocks) * BN;
@@ -445,7 +479,7 @@ fq_gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
                 const int64_t n = (int64_t)n0 + c * 32;
                 if (tma_store) {
                     if (n < N && (int64_t)m0 + w * 32 < Mrows)
-                        epi_store_chunk_tma(&mapC, smem + L::EPI + (w * 2 + (c & 1)) * 4096, v, lane, bias, n, N, m0 + w * 32);
+                        epi_store_chunk_tma(&mapC, smem + L::EPI + (w * 2 + (c & 1)) * 4096, v, lane, bias, n, N, m0 + w * 32, oq, omx, ofb, ofast);
                 } else if (row < Mrows && n < N) {
                     if (vec_ok && n + 32 <= N) {
 #pragma unroll
@@ -456,12 +490,20 @@ fq_gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
                                 const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + n + j));
                                 o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
                             }
+                            if (oq.maxval) {
+                                o.x = oq.apply(o.x, omx, ofb, ofast); o.y = oq.apply(o.y, omx, ofb, ofast);
+                                o.z = oq.apply(o.z, omx, ofb, ofast); o.w = oq.apply(o.w, omx, ofb, ofast);
+                            }
                             *reinterpret_cast<float4*>(crow + n + j) = o;
                         }
                     } else {
 #pragma unroll
                         for (int j = 0; j < 32; ++j)
-                            if (n + j < N) crow[n + j] = __uint_as_float(v[j]) + (bias ? __ldg(bias + n + j) : 0.0f);
+                            if (n + j < N) {
+                                float o = __uint_as_float(v[j]);
+                                if (bias) o += __ldg(bias + n + j);
+                                crow[n + j] = oq.maxval ? oq.apply(o, omx, ofb, ofast) : o;
+                            }
                     }
                 }
             }
@@ -483,9 +525,11 @@ fq_gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
 template <bool SRC_K_CONTIG>
 __global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ src, int64_t s_row, int64_t s_k,
                                                       __nv_bfloat16* __restrict__ dst, int64_t rows, int64_t K,
-                                                      int64_t Kp, int* __restrict__ inexact)
+                                                      int64_t Kp, int* __restrict__ inexact, FqParams iq)
 {
     int bad = 0;
+    const float imx = iq.maxval ? __ldg(iq.maxval) : 0.0f, ifb = iq.maxval ? __ldg(iq.bias) : 0.0f;   // fused input quantizer
+    const bool ifast = iq.maxval && fp8_ste_fast_ok(ifb);
     if (SRC_K_CONTIG) {
         // one thread: 8 consecutive k of one row (two float4 loads when the source allows it, one 16-byte store)
         const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -507,6 +551,7 @@ __global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ 
             uint32_t h[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
+                if (iq.maxval) v[j] = iq.apply(v[j], imx, ifb, ifast);
                 const uint32_t b = __float_as_uint(v[j]);
                 bad |= (b & 0xFFFFu) != 0;
                 h[j] = b >> 16;
@@ -523,7 +568,11 @@ __global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ 
         for (int i = 0; i < 4; ++i) {
             const int64_t k = k0 + ty + i * 8, r = r0 + tx;
             uint32_t b = 0;
-            if (r < rows && k < K) b = __float_as_uint(__ldg(src + r * s_row + k * s_k));
+            if (r < rows && k < K) {
+                float v = __ldg(src + r * s_row + k * s_k);
+                if (iq.maxval) v = iq.apply(v, imx, ifb, ifast);
+                b = __float_as_uint(v);
+            }
             bad |= (b & 0xFFFFu) != 0;
             tile[ty + i * 8][tx] = (uint16_t)(b >> 16);   // [k][r]
         }
@@ -541,10 +590,22 @@ __global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ 
 struct PlainOp {
     struct Col { float bias; };
     const float* bias;
-    __device__ __forceinline__ void begin() {}
+    FqParams oq;           // result quantizer (opt-in), or maxval == null
+    float omx, ofb;
+    bool ofast;
+    __device__ __forceinline__ void begin()
+    {
+        omx = oq.maxval ? __ldg(oq.maxval) : 0.0f;
+        ofb = oq.maxval ? __ldg(oq.bias) : 0.0f;
+        ofast = oq.maxval && fp8_ste_fast_ok(ofb);
+    }
     __device__ __forceinline__ Col column(int64_t n) const { return Col{bias ? __ldg(bias + n) : 0.0f}; }
     __device__ __forceinline__ float pair(float a, float b, const Col&) const { return a * b; }
-    __device__ __forceinline__ float finish(float acc, const Col& c) const { return acc + c.bias; }
+    __device__ __forceinline__ float finish(float acc, const Col& c) const
+    {
+        const float o = bias ? acc + c.bias : acc;
+        return oq.maxval ? oq.apply(o, omx, ofb, ofast) : o;
+    }
 };
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -623,9 +684,9 @@ static int convert_b(const float* B, int64_t sb_k, int64_t sb_n, int64_t K, int6
 {
     if (sb_k == 1) {
         const int64_t n = N * (Kp / 8);
-        to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(B, sb_n, 1, Bh, N, K, Kp, flag);
+        to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(B, sb_n, 1, Bh, N, K, Kp, flag, FqParams{});
     } else {
-        to_bf16_kernel<false><<<dim3((unsigned)ceil_div(N, 32), (unsigned)(Kp / 32)), 256, 0, st>>>(B, sb_n, sb_k, Bh, N, K, Kp, flag);
+        to_bf16_kernel<false><<<dim3((unsigned)ceil_div(N, 32), (unsigned)(Kp / 32)), 256, 0, st>>>(B, sb_n, sb_k, Bh, N, K, Kp, flag, FqParams{});
     }
     B200_LAUNCH_CHECK("to_bf16_kernel<B>");
     return B200_OK;
@@ -647,18 +708,38 @@ extern "C" int b200_fq_gemm_tc_prepare_b(const float* B, int64_t sb_k, int64_t s
                      flag, st);
 }
 
+static int make_fq(const b200_act_quant* aq, FqParams* out, const char* who)
+{
+    *out = FqParams{nullptr, nullptr, 0.0f, 0};
+    if (!aq) return B200_OK;
+    if (!aq->maxval_dev || !aq->bias_dev || aq->n_bits < 2 || aq->sign_bits < 0 || aq->sign_bits > 1) {
+        set_error(std::string(who) + ": bad b200_act_quant descriptor");
+        return B200_ERR_ARGUMENT;
+    }
+    out->maxval = aq->maxval_dev;
+    out->bias = aq->bias_dev;
+    out->Mf = fminf(fmaxf(rintf(aq->mantissa_bits), 1.0f), (float)(aq->n_bits - aq->sign_bits));
+    out->sign = aq->sign_bits;
+    return B200_OK;
+}
+
 static int fq_gemm_tc_impl(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, const void* bplane, float* C,
                            int64_t ldc, int64_t Mrows, int64_t K, int64_t N, const float* bias_dev, void* workspace,
-                           size_t workspace_bytes, void* stream)
+                           size_t workspace_bytes, void* stream, const b200_act_quant* aq_in = nullptr,
+                           const b200_act_quant* aq_out = nullptr)
 {
     if (int rc = check_device()) return rc;
     if (Mrows < 0 || K < 0 || N < 0) { set_error("b200_fq_gemm_tc: bad argument"); return B200_ERR_ARGUMENT; }
     if (Mrows == 0 || N == 0) return B200_OK;
     if ((K > 0 && (!A || !B)) || !C) { set_error("b200_fq_gemm_tc: NULL operand"); return B200_ERR_ARGUMENT; }
     cudaStream_t st = (cudaStream_t)stream;
-    const ASrc asrc = make_gemm_asrc(A, lda);
+    ASrc asrc = make_gemm_asrc(A, lda);
+    if (int rc = apply_act_quant(&asrc, aq_in)) return rc;     // the fp32 fallback quantizes on load as well
+    FqParams iq, oq;
+    if (int rc = make_fq(aq_in, &iq, "b200_fq_gemm_tc_ex(input quantizer)")) return rc;
+    if (int rc = make_fq(aq_out, &oq, "b200_fq_gemm_tc_ex(result quantizer)")) return rc;
     const BSrc bsrc{B, sb_k, sb_n};
-    const PlainOp pop{bias_dev};
+    const PlainOp pop{bias_dev, oq, 0.0f, 0.0f, false};
     if (K == 0) {
         pair_gemm_kernel<PlainOp><<<pair_gemm_grid(Mrows, N), 256, 0, st>>>(asrc, bsrc, C, ldc, Mrows, K, N, pop, nullptr, 0);
         B200_LAUNCH_CHECK("pair_gemm_kernel<PlainOp>");
@@ -683,7 +764,7 @@ static int fq_gemm_tc_impl(const float* A, int64_t lda, const float* B, int64_t 
     }
     {
         const int64_t n = Mrows * (Kp / 8);
-        to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(A, lda, 1, Ah, Mrows, K, Kp, flag);
+        to_bf16_kernel<true><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(A, lda, 1, Ah, Mrows, K, Kp, flag, iq);
         B200_LAUNCH_CHECK("to_bf16_kernel<A>");
     }
     if (!bplane)
@@ -712,25 +793,25 @@ static int fq_gemm_tc_impl(const float* A, int64_t lda, const float* B, int64_t 
     // CTA pairs (cta_group::2, 256 x 256 tiles) where there is enough work for them; B200_TC_PAIR=0: single-CTA kernel
     const char* pe = getenv("B200_TC_PAIR");
     const bool pair_ok = N > 128 && Mrows > 128 && sms >= 2 && !(pe && atoi(pe) == 0) &&
-                         ((pe && atoi(pe) == 2) || ceil_div(Mrows, 2 * TC_BM) * ceil_div(N, TC2_BN) >= sms / 4);   // 2: force (tests)
+                         ((pe && atoi(pe) == 2) || ceil_div(Mrows, 2 * TC_BM) * ceil_div(N, TC2_BN) >= sms / 2);   // a full wave of pairs; 2: force (tests)
     if (pair_ok) {
         if (int rc = make_map(enc, &mapB, Bh, N, Kp, TC2_HALF_N)) return rc;
         const int m_blocks = (int)ceil_div(Mrows, 2 * TC_BM), n_tiles = m_blocks * (int)ceil_div(N, TC2_BN);
         const int pairs = std::min(n_tiles, sms / 2);
         fq_gemm_tc2_kernel<<<(unsigned)(2 * pairs), TC_THREADS, Tc2Smem::TOTAL, st>>>(
-            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
+            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag, oq);
     } else if (N > 128) {
         constexpr int BN = 256, ST = 4;
         if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
         const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
         fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
-            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
+            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag, oq);
     } else {
         constexpr int BN = 128, ST = 4;
         if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
         const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
         fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
-            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag);
+            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag, oq);
     }
     B200_LAUNCH_CHECK("fq_gemm_tc_kernel");
     // runs only if the convert pass found an operand that is not exact in bf16
@@ -753,4 +834,17 @@ extern "C" int b200_fq_gemm_tc_pre(const float* A, int64_t lda, const float* B, 
 {
     if (!bplane || K < 1) { set_error("b200_fq_gemm_tc_pre: needs a prepared plane (b200_fq_gemm_tc_prepare_b) and K >= 1"); return B200_ERR_ARGUMENT; }
     return fq_gemm_tc_impl(A, lda, B, sb_k, sb_n, bplane, C, ldc, Mrows, K, N, bias_dev, workspace, workspace_bytes, stream);
+}
+
+// The most general form (opt-in fusions): optional prepared right operand (bplane, may be NULL), optional input
+// fake-quantizer applied while A is converted (aq_in: A then holds the RAW activations) and optional result
+// fake-quantizer applied in the epilogue after the bias (aq_out).  b200_act_quant as in b200_approx_gemm_fbias_fq.
+extern "C" int b200_fq_gemm_tc_ex(const float* A, int64_t lda, const float* B, int64_t sb_k, int64_t sb_n, const void* bplane,
+                                  const b200_act_quant* aq_in, const b200_act_quant* aq_out, float* C, int64_t ldc,
+                                  int64_t Mrows, int64_t K, int64_t N, const float* bias_dev, void* workspace,
+                                  size_t workspace_bytes, void* stream)
+{
+    if (bplane && K < 1) { set_error("b200_fq_gemm_tc_ex: a prepared plane needs K >= 1"); return B200_ERR_ARGUMENT; }
+    return fq_gemm_tc_impl(A, lda, B, sb_k, sb_n, bplane, C, ldc, Mrows, K, N, bias_dev, workspace, workspace_bytes, stream,
+                           aq_in, aq_out);
 }

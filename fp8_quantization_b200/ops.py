@@ -309,13 +309,16 @@ def _prepared_b(lib, y, K, N):
     return ent[0]
 
 
-def fq_matmul(x, y, bias=None, out=None, cache_b=False):
+def fq_matmul(x, y, bias=None, out=None, cache_b=False, act_quant=None, res_quant=None):
     """The non-approx `x @ y` of fake-quantized operands (approx/approx_calculation.py:968-969, :704-705) on the
     tcgen05 tensor cores: bf16 operands (exact for FP8-grid values), fp32 accumulation in tensor memory.
     Operands that are not exact in bf16 are detected on the device and computed in fp32 instead.
     bias: [N], added to every row in the kernel's epilogue (`output += bias`, :1020-1021).
     cache_b (opt-in): `y` is a tensor that stays the same call after call (fixed-range weights): its bf16 plane is
-    built once and reused (b200_fq_gemm_tc_pre)."""
+    built once and reused (b200_fq_gemm_tc_pre).
+    act_quant / res_quant (opt-in) = (maxval, bias, mantissa_bits, n_bits, sign_bits): the input fake-quantizer runs while
+    `x` (then RAW activations) is converted to bf16, the result fake-quantizer in the epilogue after the bias
+    (b200_fq_gemm_tc_ex); bit-identical to the separate passes."""
     lib = _lib.load()
     _require_cuda(x, y)
     assert x.dim() == 2 and y.dim() == 2 and x.shape[1] == y.shape[0]
@@ -333,7 +336,15 @@ def fq_matmul(x, y, bias=None, out=None, cache_b=False):
         assert b.numel() == N
     ws = _workspace(x.device, lib.b200_fq_gemm_tc_workspace_bytes(Mrows, K, N))
     with torch.cuda.device(x.device):
-        if cache_b and K > 0 and N > 0 and Mrows > 0:
+        if act_quant is not None or res_quant is not None:
+            plane = _prepared_b(lib, y, K, N) if (cache_b and K > 0 and N > 0 and Mrows > 0) else None
+            aqi, keep1 = _act_quant_struct(act_quant, x.device) if act_quant is not None else (None, None)
+            aqo, keep2 = _act_quant_struct(res_quant, x.device) if res_quant is not None else (None, None)
+            rc = lib.b200_fq_gemm_tc_ex(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(plane),
+                                        ctypes.byref(aqi) if aqi is not None else None,
+                                        ctypes.byref(aqo) if aqo is not None else None, _ptr(out), out.stride(0), Mrows, K, N,
+                                        _ptr(b), _ptr(ws), ws.numel(), _stream())
+        elif cache_b and K > 0 and N > 0 and Mrows > 0:
             plane = _prepared_b(lib, y, K, N)
             rc = lib.b200_fq_gemm_tc_pre(_ptr(x), x.stride(0), _ptr(y), y.stride(0), y.stride(1), _ptr(plane), _ptr(out),
                                          out.stride(0), Mrows, K, N, _ptr(b), _ptr(ws), ws.numel(), _stream())

@@ -387,8 +387,12 @@ class QuantizationHijacker(QuantizedModule):
         weight, bias = self.get_params()
         res = None
         if self.fix_ranges_flag is False or self.original_quantize_res:
+            want_rq = self.quantize_input and self._quant_a and self.res_quantizer_flag
+            rq = self._fused_res_quant(x) if want_rq else None
+            if rq is not None:
+                self.__dict__["_b200_res_quant"] = rq      # popped by the plain matmul that applies it in its epilogue
             res = self.run_forward(x, weight, bias, offsets=offsets)
-            if self.quantize_input and self._quant_a and self.res_quantizer_flag:
+            if want_rq and (rq is None or self.__dict__.pop("_b200_res_quant", None) is not None):
                 res = self.res_quantizer(res)
         if self.res_quantizer_flag and self.quantize_after_mult_and_add:
             res = self.run_forward(x, weight, bias)
@@ -428,8 +432,9 @@ class QuantizationHijacker(QuantizedModule):
         the usual way (calibrating, other run modes, depthwise groups, per-channel ranges...)."""
         if not FUSE_INPUT_QUANT or self.training or not self.fix_ranges_flag:
             return None
-        if not (self.approx_flag and self.res_quantizer_flag) or self.original_quantize_res or \
-                self.quantize_after_mult_and_add:
+        approx_once = self.approx_flag and self.res_quantizer_flag and not self.original_quantize_res and \
+            not self.quantize_after_mult_and_add
+        if not (approx_once or self._plain_once()):
             return None
         aqm = self.activation_quantizer
         q = aqm.quantizer
@@ -438,6 +443,27 @@ class QuantizationHijacker(QuantizedModule):
             return None
         fusable = getattr(self, "_fusable_input_quant", None)
         if fusable is None or not x.is_cuda or x.dtype != torch.float32 or not fusable(x):
+            return None
+        return (q.maxval, q.custom_bias, float(q.mantissa_bits), q.n_bits, q.sign_bits)
+
+    def _plain_once(self):
+        """The non-approx configuration in which exactly ONE plain run_forward produces the result (hijacker.py:89-94 with
+        original_quantize_res, neither approx nor quantize_after_mult_and_add) on a layer whose plain matmul is the
+        tensor-core kernel with fused quantizers (Linear layers)."""
+        return self.original_quantize_res and not self.approx_flag and not self.quantize_after_mult_and_add and \
+            getattr(self, "_plain_matmul_fuses_quantizers", False)
+
+    def _fused_res_quant(self, x):
+        """Opt-in (FUSED_GEMM_EPILOGUE): `res = self.res_quantizer(res)` (hijacker.py:93-94) evaluated in the epilogue of
+        the tensor-core matmul.  Returns the descriptor or None (calibrating, other modes, per-channel ranges, ...)."""
+        if not FUSED_GEMM_EPILOGUE or self.training or not self.fix_ranges_flag or not self._plain_once():
+            return None
+        rqm = self.res_quantizer
+        q = rqm.quantizer
+        if rqm.state != Qstates.fix_ranges or not isinstance(q, FPQuantizer) or q.custom_bias is None or \
+                q._bias_version != q._range_version or q.maxval.numel() != 1 or q.custom_bias.numel() != 1:
+            return None
+        if not x.is_cuda or x.dtype != torch.float32:
             return None
         return (q.maxval, q.custom_bias, float(q.mantissa_bits), q.n_bits, q.sign_bits)
 

@@ -251,6 +251,15 @@ int b200_approx_gemm_fbias_fq(const float *A, int64_t lda, const float *B, int64
                               const b200_approx_params *p, const b200_act_quant *aq, void *workspace,
                               size_t workspace_bytes, void *stream);
 
+/* K3 with the neighbouring fake-quantizers fused (opt-in): bplane (may be NULL) as in b200_fq_gemm_tc_pre; aq_in: A
+ * holds RAW activations and `x = self.activation_quantizer(x)` (quantization/hijacker.py:82-88) runs inside the bf16
+ * convert pass; aq_out: `res = self.res_quantizer(res)` (:93-94) runs in the epilogue after the bias.  Either may be
+ * NULL.  Bit-identical to running the quantizers as separate passes. */
+int b200_fq_gemm_tc_ex(const float *A, int64_t lda, const float *B, int64_t sb_k, int64_t sb_n, const void *bplane,
+                       const b200_act_quant *aq_in, const b200_act_quant *aq_out, float *C, int64_t ldc,
+                       int64_t Mrows, int64_t K, int64_t N, const float *bias_dev, void *workspace,
+                       size_t workspace_bytes, void *stream);
+
 /* ---- N2: fused epilogue (OPT-IN: the entry points above keep the reference's pass structure) --- */
 /* What the reference does to a layer's product sums before the next layer reads them, evaluated in the epilogue of
  * the GEMM / conv kernels instead of as separate passes over the output, in the reference's operation order
