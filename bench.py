@@ -596,9 +596,10 @@ def run_ours(args):
         "per_gpu": round(value / world, 2),
         "e2e": {"value": round(e2e_value, 2), "unit": "GMAC/s", "h2d_bytes_per_step": rows * K_DIM * 4,
                 "d2h_bytes_per_step": rows * N_DIM * 4,
-                "through": "QCustomLinearTorch.forward (input fake-quant fused into the operand decode, quantized W cached "
-                           "once the ranges are fixed, approx GEMM, +bias), pinned host in/out; steps software pipelined: "
-                           "copies of adjacent steps overlap the forward on side streams",
+                "through": "QCustomLinearTorch.forward with quantization.enable_fusions() (input fake-quant fused into the "
+                           "operand decode, quantized W cached once the ranges are fixed, approx GEMM with +bias in its "
+                           "epilogue; same bits as the reference's pass structure), pinned host in/out; steps software "
+                           "pipelined: copies of adjacent steps overlap the forward on side streams",
                 "chunks": nch, "checksum": checksum},
         "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks,
     }

@@ -44,6 +44,13 @@ def _worker(rank, world, port, result_dir):
         ok = ok and logits.shape == whole.shape and torch.equal(logits, whole)
     open(os.path.join(result_dir, f"r{rank}"), "w").write(f"{'ok' if ok else 'bad'} {fwd.collective_in_graph}")
     dist.barrier()
+    # a live CUDA graph that holds captured NCCL kernels keeps the communicator busy: destroy_process_group() then
+    # waits for ever -- drop the graphs first
+    import gc
+    fwd._graphs.clear()
+    del fwd, logits
+    gc.collect()
+    torch.cuda.synchronize()
     dist.destroy_process_group()
 
 

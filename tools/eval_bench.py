@@ -90,6 +90,12 @@ def main():
                           "sharded_equals_single_gpu": same, "logits_checksum": float(logits.double().sum())}),
               flush=True)
     if world > 1:
+        if fwd is not None:      # a live graph with captured NCCL kernels makes destroy_process_group() wait for ever
+            fwd._graphs.clear()
+        del fwd
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
         dist.destroy_process_group()
 
 

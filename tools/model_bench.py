@@ -16,13 +16,18 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 MACS_PER_IMAGE = {"resnet18": 1.814e9, "mobilenetv2": 0.301e9, "vit_b16": 16.73e9, "bert_base": 10.87e9}   # bert_base: per sequence of 128 tokens, NON-approx (tcgen05)
 
 
-def build(model_name, E, M, device):
+def build(model_name, E, M, device, ofuf=False):
+    """ofuf: the opt-in v5 overflow / underflow mode (BASELINE configs[3] "with OF/UF sim"):
+    sim_hw_add_OFUF / with_OF_opt / with_UF_opt on and LIVE (ofuf_mode = 1)."""
     import torch
     import model_cases as mc
     from fp8_quantization_b200 import model_wrap as mw
+    cap = mc.approx_params(E, M)
+    if ofuf:
+        cap.update(sim_hw_add_OFUF=True, with_OF_opt=True, with_UF_opt=True, ofuf_mode=1)
     qp = dict(method="fp_quantizer", act_method="fp_quantizer", n_bits=8, n_bits_act=8, per_channel_weights=True,
               weight_range_method="current_minmax", act_range_method="allminmax", quantize_input=True,
-              fp8_kwargs=dict(mantissa_bits=M, set_maxval=True), custom_approx_params=mc.approx_params(E, M),
+              fp8_kwargs=dict(mantissa_bits=M, set_maxval=True), custom_approx_params=cap,
               run_method=dict(mc.RUN_APPROX))
     if model_name == "resnet18":
         model = mw.QuantizedResNet(mc.fp_resnet18(), **qp)

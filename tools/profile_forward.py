@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--mant-width", type=int, default=3)
     ap.add_argument("--no-autotune", action="store_true")
+    ap.add_argument("--ofuf", action="store_true", help="opt-in v5 overflow/underflow mode (ofuf_mode = 1), BASELINE configs[3]")
     a = ap.parse_args()
     import torch
     import model_bench as mb
@@ -34,7 +35,7 @@ def main():
     from fp8_quantization_b200 import quantization as _Q
     _Q.enable_fusions(True)      # opt-in fused forward (input quantizer, fixed-weight cache, GEMM epilogue): same bits
     M = a.mant_width
-    model = mb.build(a.model, 7 - M, M, dev)
+    model = mb.build(a.model, 7 - M, M, dev, ofuf=a.ofuf)
     if a.model == "bert_base":
         ids = lambda n, seed: torch.randint(0, 30522, (n, 128), generator=torch.Generator().manual_seed(seed))
         x_cal, x = ids(a.batch, 1).to(dev), ids(a.batch, 2).to(dev)
@@ -58,7 +59,7 @@ def main():
         g.replay()
         torch.cuda.synchronize()
         torch.cuda.profiler.stop()
-    print(json.dumps({"model": a.model, "batch": a.batch, "format": f"E{7 - M}M{M}", "ms_per_forward": round(ms, 3),
+    print(json.dumps({"model": a.model, "batch": a.batch, "format": f"E{7 - M}M{M}", "ofuf_mode": int(a.ofuf), "ms_per_forward": round(ms, 3),
                       "images_per_s": round(a.batch / ms * 1e3, 1), "logits_checksum": float(y.double().sum())}))
 
 
