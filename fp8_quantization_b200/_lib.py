@@ -33,7 +33,7 @@ class ApproxParams(ctypes.Structure):
         ("withComp", c_u8), ("with_approx", c_u8), ("with_s2nn2s_opt", c_u8), ("sim_hw_add_OFUF", c_u8),
         ("with_OF_opt", c_u8), ("with_UF_opt", c_u8), ("golden_clip_OF", c_u8), ("quant_btw_mult_accu", c_u8),
         ("self_check_mode", c_u8), ("single_column_quirk", c_u8), ("allow_unpinned_format", c_u8),
-        ("force_generic", c_u8), ("ofuf_mode", c_u8),
+        ("force_generic", c_u8), ("ofuf_mode", c_u8), ("force_table16", c_u8),
         ("custom_table", c_vp),
     ]
 

@@ -35,6 +35,7 @@
 #include "tables.h"
 #include "epilogue.cuh"
 #include "gemm_impl.cuh"
+#include "lut_gemm.cuh"
 
 namespace b200 {
 
@@ -171,6 +172,81 @@ __global__ void lut_build_qamaa_kernel(LutGeom g, QamaaOp op, uint16_t* __restri
     lut[idx] = out;
 }
 
+// Byte-cell companion of a pair table (lut_gemm.cuh, C8): cell8 = the 16-bit cell where it is an integer of
+// magnitude <= 127 (units of u), else 0, and *bad = NT - (first table row holding a cell that does not fit).
+// The table GEMM uses byte cells only for rows below that one.  `flag16` (qamaa: the 16-bit table was declared
+// unusable on the device) is passed through unchanged.
+__global__ void lut8_build_kernel(LutGeom g, const uint16_t* __restrict__ lut16, int8_t* __restrict__ lut8, int n8,
+                                  int* __restrict__ bad)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n8) return;
+    int8_t out = 0;
+    if (idx < g.zeroA_off) {
+        const float v = __uint_as_float((uint32_t)lut16[idx] << 16);
+        if (v == rintf(v) && fabsf(v) <= 127.0f) out = (int8_t)(int)v;
+        else atomicMax(bad, g.NT - (idx >> g.M) % g.NT);
+    }
+    lut8[idx] = out;
+}
+
+constexpr int kEscLists = 32;
+
+// Correction pass of the byte-cell variant: for every listed escape A element (row m, k) and every column n, the
+// pair's 16-bit cell is looked up in the full table; where the byte table holds 0 in its place (the cell is not an
+// integer within +-127) the cell, in units of u, is added to D[m][n].  The byte-cell GEMM starts its sums from D.
+// Work is (escapes x N) cheap tests and rare lookups: escapes are at most 1/8 of the A elements (usually a 1e-4
+// fraction), or the gate is closed and nobody reads D.  Block 0 also publishes the total and the overflow flag.
+struct C8CorrectArgs {
+    const unsigned long long* esc_list;
+    unsigned esc_cap;
+    const unsigned* esc_counters;
+    unsigned* esc_total;       // [0] total, [1] a list overflowed
+    const uint32_t* Aw;
+    const uint32_t* Bw;
+    int64_t Mpad, Npad, N;
+    const uint16_t* lut16;
+    const int* c8_bad;
+    const int* tmax;           // [0] A, [1] B
+    int NT, M, sidx;
+    uint32_t nt_magic;
+    int* D;
+};
+__global__ void __launch_bounds__(256) c8_correct_kernel(C8CorrectArgs a)
+{
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned tot = 0, ovf = 0;
+        for (int l = 0; l < kEscLists; ++l) { const unsigned c = a.esc_counters[l]; tot += c; ovf |= (c > a.esc_cap); }
+        a.esc_total[0] = tot;
+        a.esc_total[1] = ovf;
+    }
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int R8 = a.NT - 1 - *a.c8_bad;
+    for (int l = 0; l < kEscLists; ++l) {
+        const unsigned cnt = min(a.esc_counters[l], a.esc_cap);
+        for (int64_t e = warp; e < cnt; e += nwarps) {
+            const unsigned long long ent = a.esc_list[(size_t)l * a.esc_cap + e];
+            const int64_t m = (int64_t)(ent & 0xFFFFFFFFull), k = (int64_t)(ent >> 32);
+            const uint32_t aw = a.Aw[k * a.Mpad + m];
+            const uint32_t x = aw >> (a.M + 1);
+            const int tA = (int)(x - (uint32_t)a.NT * __umulhi(x, a.nt_magic));
+            const uint32_t* brow = a.Bw + k * a.Npad;
+            for (int64_t n = lane; n < a.N; n += 32) {
+                const uint32_t bw = __ldg(brow + n);
+                const uint32_t o16 = a.sidx ? bw : (bw & 0xFFFFu);
+                // plain layout: the B offset's row is tB_idx; rows up to R8 hold int8 cells only (signed-index layout:
+                // the region offset hides tB_idx -- look every pair up)
+                if (!a.sidx && tA + (int)(o16 >> (a.M + 1)) <= R8) continue;
+                const float v = __uint_as_float((uint32_t)__ldg(a.lut16 + ((aw + o16) >> 1)) << 16);
+                if (v == rintf(v) && fabsf(v) <= 127.0f) continue;                 // the byte table has this cell
+                const int sg = a.sidx ? 1 : (((int)bw >> 30) | 1);
+                atomicAdd(a.D + m * a.N + n, __float2int_rn(v) * sg);
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // Operand predecode: fp32 -> packed table offsets, transposed to [K][rows] so that the GEMM reads
 // 128-bit vectors of consecutive rows/columns.  HBM-bound, one pass.
@@ -185,11 +261,38 @@ struct PredecodeArgs {
     BiasSrc bias;
     int* offgrid;          // raised if any element cannot take the table path
     unsigned long long* zero_count;   // A operand: number of zero elements (sampled; picks the GEMM's k loop), or null
-    int* tmax;                        // split-K only: atomicMax of the operand's table row index (bounds the addends)
+    int* tmax;                        // atomicMax of the operand's table row index (bounds the addends), or null
+    // byte-cell variant of the table GEMM (lut_gemm.cuh, A operand only; esc_list == null: off): A elements whose
+    // table rows may hold a cell beyond +-127 -- tA_idx > (last all-int8 row) - (largest tB_idx, known because B is
+    // decoded first) -- are "escapes": appended as (k << 32 | row) to one of kEscLists lists (block-hashed, so that the
+    // list counters are not one contended address); c8_correct_kernel adds the cells the byte table dropped for them
+    unsigned long long* esc_list;     // [kEscLists][esc_cap]
+    unsigned esc_cap;
+    unsigned* esc_counters;           // [kEscLists]
+    const int* c8_bad;                // NT - (first row with a cell that does not fit int8), 0 if none
+    const int* tmaxB;
+    __device__ __forceinline__ int thrA(const LutGeom& g) const
+    {
+        return esc_list ? (g.NT - 1 - *c8_bad) - *tmaxB : 0x7FFFFFFF;
+    }
+    // warp-aggregated append; every lane of the warp calls it (esc false where there is nothing to report)
+    __device__ __forceinline__ void escape(bool esc, int64_t r, int64_t k, unsigned list) const
+    {
+        const unsigned m = __ballot_sync(0xFFFFFFFFu, esc);
+        if (m == 0) return;
+        const unsigned lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+        unsigned base = 0;
+        if (lane == leader) base = atomicAdd(esc_counters + list, __popc(m));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+        if (esc) {
+            const unsigned pos = base + __popc(m & ((1u << lane) - 1u));
+            if (pos < esc_cap) esc_list[(size_t)list * esc_cap + pos] = ((unsigned long long)k << 32) | (unsigned long long)(uint32_t)r;
+        }
+    }
 };
-
-__device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int bA, int& off, int& tmax)
+__device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int bA, int& off, int& tmax, int thrA, bool& esc)
 {
+    esc = false;
     const uint32_t bits = __float_as_uint(v);
     const uint32_t mag = bits & 0x7FFFFFFFu;
     if (mag == 0) return 2u * (uint32_t)g.zeroA_off;
@@ -206,7 +309,13 @@ __device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int b
     const uint32_t mA = frac >> (23 - M);
     const uint32_t sa = bits >> 31;
     tmax = max(tmax, tA);
+    esc = tA > thrA;
     return 2u * (uint32_t)(g.row_entries * (tA + g.NT * (int)(mA + (sa << M))));
+}
+__device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int bA, int& off, int& tmax)
+{
+    bool esc;
+    return predecode_a(g, v, bA, off, tmax, 0x7FFFFFFF, esc);
 }
 
 __device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int bA, int bB, int bR, int& off, int& tmax)
@@ -289,18 +398,22 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
     int off = 0, zeros = 0, tmax = 0;
     const int bA = a.bias.A(), bR = a.bias.R();
+    const int thrA = IS_B ? 0 : a.thrA(g);
+    const unsigned elist = (blockIdx.x * 7u + blockIdx.y * 13u) % kEscLists;
     if (bA <= -64 || bA >= 64 || bR <= -64 || bR >= 64) off = 1;
     if (SRC_K_CONTIG) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int64_t r = r0 + ty + i * 8, k = k0 + tx;
             uint32_t w = IS_B ? (g.sidx ? 0u : (kBf16One << 16)) : 2u * (uint32_t)g.zeroA_off;
+            bool esc = false;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
                 w = IS_B ? (g.v5 ? predecode_b_v5(g, v, bA, a.bias.B(r), bR, off) : predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax))
-                         : (g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax));
+                         : (g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax, thrA, esc));
                 if (!IS_B) zeros += (v == 0.0f);
             }
+            if (!IS_B && a.esc_list) a.escape(esc, r, k, elist);
             tile[tx][ty + i * 8] = w;   // [k][r]
         }
         __syncthreads();
@@ -314,12 +427,14 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
         for (int i = 0; i < 4; ++i) {
             const int64_t k = k0 + ty + i * 8, r = r0 + tx;
             uint32_t w = IS_B ? (g.sidx ? 0u : (kBf16One << 16)) : 2u * (uint32_t)g.zeroA_off;
+            bool esc = false;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
                 w = IS_B ? (g.v5 ? predecode_b_v5(g, v, bA, a.bias.B(r), bR, off) : predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax))
-                         : (g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax));
+                         : (g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax, thrA, esc));
                 if (!IS_B) zeros += (v == 0.0f);
             }
+            if (!IS_B && a.esc_list) a.escape(esc, r, k, elist);
             if (k < a.Kpad && r < a.Rpad) a.dst[k * a.Rpad + r] = w;
         }
     }
@@ -358,6 +473,8 @@ __global__ void __launch_bounds__(PC_ROWS) predecode_conv_kernel(PredecodeArgs a
     const int k0 = blockIdx.y * PC_KCH;
     int off = 0, zeros = 0, tmax = 0;
     const int bA = a.bias.A(), bR = a.bias.R();
+    const int thrA = a.thrA(g);
+    const unsigned elist = (blockIdx.x * 7u + blockIdx.y * 13u) % kEscLists;
     if (bA <= -64 || bA >= 64 || bR <= -64 || bR >= 64) off = 1;
     const bool valid_r = r < a.rows;
     const int wo = (int)(r % s.Wo);
@@ -374,13 +491,15 @@ __global__ void __launch_bounds__(PC_ROWS) predecode_conv_kernel(PredecodeArgs a
 #pragma unroll 4
     for (int kk = 0; kk < kend; ++kk) {
         uint32_t w = zero_word;
+        bool esc = false;
         if (valid_r && k0 + kk < a.K) {
             const int h = h0 + ky * s.dh, wi = w0 + kx * s.dw;
             float v = 0.0f;                                              // F.pad zeros (:727)
             if (h >= 0 && h < s.H && wi >= 0 && wi < s.W) v = s.fq(__ldg(base + ((int64_t)c * s.H + h) * s.W + wi));
-            w = g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax);
+            w = g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax, thrA, esc);
             zeros += (v == 0.0f);
         }
+        if (a.esc_list) a.escape(esc, r, k0 + kk, elist);
         dst[(int64_t)kk * a.Rpad] = w;
         if (++kx == s.kw) { kx = 0; if (++ky == s.kh) { ky = 0; ++c; } }
     }
@@ -418,6 +537,8 @@ __global__ void __launch_bounds__(256) predecode_1x1_kernel(PredecodeArgs a, Lut
     const int k = blockIdx.y;
     int off = 0, zeros = 0, tmax = 0;
     const int bA = a.bias.A(), bR = a.bias.R();
+    const int thrA = a.thrA(g);
+    bool e0 = false, e1 = false, e2 = false, e3 = false;
     if (bA <= -64 || bA >= 64 || bR <= -64 || bR >= 64) off = 1;
     const uint32_t zero_word = 2u * (uint32_t)g.zeroA_off;
     const bool live = r < a.rows && k < a.K;
@@ -444,8 +565,8 @@ __global__ void __launch_bounds__(256) predecode_1x1_kernel(PredecodeArgs a, Lut
                 w.x = predecode_a_v5(g, v.x, bA, off); w.y = predecode_a_v5(g, v.y, bA, off);
                 w.z = predecode_a_v5(g, v.z, bA, off); w.w = predecode_a_v5(g, v.w, bA, off);
             } else {
-                w.x = predecode_a(g, v.x, bA, off, tmax); w.y = predecode_a(g, v.y, bA, off, tmax);
-                w.z = predecode_a(g, v.z, bA, off, tmax); w.w = predecode_a(g, v.w, bA, off, tmax);
+                w.x = predecode_a(g, v.x, bA, off, tmax, thrA, e0); w.y = predecode_a(g, v.y, bA, off, tmax, thrA, e1);
+                w.z = predecode_a(g, v.z, bA, off, tmax, thrA, e2); w.w = predecode_a(g, v.w, bA, off, tmax, thrA, e3);
             }
             zeros = (v.x == 0.0f) + (v.y == 0.0f) + (v.z == 0.0f) + (v.w == 0.0f);
         }
@@ -455,6 +576,10 @@ __global__ void __launch_bounds__(256) predecode_1x1_kernel(PredecodeArgs a, Lut
     if (a.tmax) {
         tmax = __reduce_max_sync(0xFFFFFFFFu, tmax);
         if ((threadIdx.x & 31) == 0 && tmax > *(volatile int*)a.tmax) atomicMax(a.tmax, tmax);
+    }
+    if (a.esc_list) {
+        const unsigned elist = (blockIdx.x * 7u + blockIdx.y * 13u) % kEscLists;
+        a.escape(e0, r, k, elist); a.escape(e1, r + 1, k, elist); a.escape(e2, r + 2, k, elist); a.escape(e3, r + 3, k, elist);
     }
     if (a.zero_count && (blockIdx.x & 7) == 0 && (blockIdx.y & 3) == 0) {   // sampled zero statistics
         __shared__ int s_zeros;
@@ -469,18 +594,6 @@ __global__ void __launch_bounds__(256) predecode_1x1_kernel(PredecodeArgs a, Lut
         }
     }
 }
-
-// Conv form, second variant: the group's input channels are decoded ONCE, in place of the kh*kw-times
-// inflated plane above, into words Pw[b][c][h][w]; the GEMM's A-tile loader then does the im2col gather
-// itself (4-byte cp.async from this L2-resident plane).  kinfo[k] = {word offset of tap k = (c, ky, kx)
-// relative to the pixel's top-left tap, ky*dh | kx*dw << 16}; k >= K gets an always-out-of-range row offset.
-struct ConvPlane {
-    const uint32_t* Pw;       // [B][Cg][H][W] words
-    const int2* kinfo;        // [Kpad]
-    const uint32_t* zero_src; // one word: the A word of a == 0 (padding, rows / k beyond the matrix)
-    int64_t img_words;        // Cg * H * W
-    int H, W, Ho, Wo, sh, sw, ph, pw;
-};
 
 __global__ void __launch_bounds__(256) predecode_plane_kernel(PredecodeArgs a, LutGeom g, uint32_t* __restrict__ Pw,
                                                               int2* __restrict__ kinfo, uint32_t* __restrict__ zero_dst,
@@ -534,486 +647,6 @@ __global__ void __launch_bounds__(256) predecode_plane_kernel(PredecodeArgs a, L
             if (n > 0) atomicAdd(a.zero_count, (unsigned long long)s_zeros | ((unsigned long long)n << 32));
         }
     }
-}
-
-// ------------------------------------------------------------------------------------------------
-// Table-driven GEMM.  Template <WARPS, RPW, CPL>: CTA tile (RPW*WARPS) x (32*CPL); one warp =
-// RPW rows x 32*CPL columns; one lane = RPW rows x CPL consecutive columns (RPW*CPL = 64 or 32 fp32
-// accumulators).  For a fixed k all lanes of a warp use the same RPW A words (broadcast LDS.128) and
-// their own CPL B words (one conflict-free LDS.128 / LDS.64).  Operand tiles are staged through a
-// 3-deep cp.async ring; the pair table lives in shared memory for the life of the CTA.
-// Per MAC: IADD (table address) + LDS.U16 + FHFMA.BF16.
-// ------------------------------------------------------------------------------------------------
-constexpr int LUT_STAGES = 3;
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ unsigned short lds_u16(uint32_t addr)
-{
-    unsigned short v;
-    asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
-    return v;
-}
-// acc += e * m with e, m bf16 and acc fp32 (PTX ISA 8.6 mixed-precision fma, SASS FHFMA.BF16):
-// the product of two bf16 is exact in fp32 and the add rounds once -- identical to an fp32 add of
-// the (exactly representable) table value.
-__device__ __forceinline__ void fma_bf16(float& acc, unsigned short e, unsigned short m)
-{
-    asm("fma.rn.f32.bf16 %0, %1, %2, %0;" : "+f"(acc) : "h"(e), "h"(m));
-}
-// One A element against CPL B elements: table address add, 16-bit table load, fp32 += bf16 * bf16,
-// skipped as a whole when a == 0.  The test is warp-uniform (all lanes of a warp hold the same A
-// word), which `bra.uni` tells ptxas: a plain branch, no BSSY/BSYNC reconvergence pair.  Zero
-// activations -- about half of a post-ReLU tensor -- issue no shared-memory lookups at all.
-__device__ __forceinline__ void mac_row4(float& c0, float& c1, float& c2, float& c3, uint32_t aw, uint32_t zero_word,
-                                         uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3, unsigned short m0,
-                                         unsigned short m1, unsigned short m2, unsigned short m3)
-{
-    asm("{\n\t.reg .pred p;\n\t.reg .b16 e0, e1, e2, e3;\n\t.reg .u32 x0, x1, x2, x3;\n\t"
-        "setp.ne.u32 p, %4, %5;\n\t"
-        "add.u32 x0, %4, %6;\n\tadd.u32 x1, %4, %7;\n\tadd.u32 x2, %4, %8;\n\tadd.u32 x3, %4, %9;\n\t"
-        "@p ld.shared.u16 x0, [x0];\n\t@p ld.shared.u16 x1, [x1];\n\t@p ld.shared.u16 x2, [x2];\n\t@p ld.shared.u16 x3, [x3];\n\t"
-        "cvt.u16.u32 e0, x0;\n\tcvt.u16.u32 e1, x1;\n\tcvt.u16.u32 e2, x2;\n\tcvt.u16.u32 e3, x3;\n\t"
-        "@p fma.rn.f32.bf16 %0, e0, %10, %0;\n\t@p fma.rn.f32.bf16 %1, e1, %11, %1;\n\t"
-        "@p fma.rn.f32.bf16 %2, e2, %12, %2;\n\t@p fma.rn.f32.bf16 %3, e3, %13, %3;\n\t}"
-        : "+f"(c0), "+f"(c1), "+f"(c2), "+f"(c3)
-        : "r"(aw), "r"(zero_word), "r"(b0), "r"(b1), "r"(b2), "r"(b3), "h"(m0), "h"(m1), "h"(m2), "h"(m3));
-}
-__device__ __forceinline__ void mac_row2(float& c0, float& c1, uint32_t aw, uint32_t zero_word, uint32_t b0,
-                                         uint32_t b1, unsigned short m0, unsigned short m1)
-{
-    asm("{\n\t.reg .pred p;\n\t.reg .b16 e0, e1;\n\t.reg .u32 x0, x1;\n\t"
-        "setp.ne.u32 p, %2, %3;\n\t"
-        "add.u32 x0, %2, %4;\n\tadd.u32 x1, %2, %5;\n\t"
-        "@p ld.shared.u16 x0, [x0];\n\t@p ld.shared.u16 x1, [x1];\n\t"
-        "cvt.u16.u32 e0, x0;\n\tcvt.u16.u32 e1, x1;\n\t"
-        "@p fma.rn.f32.bf16 %0, e0, %6, %0;\n\t@p fma.rn.f32.bf16 %1, e1, %7, %1;\n\t}"
-        : "+f"(c0), "+f"(c1)
-        : "r"(aw), "r"(zero_word), "r"(b0), "r"(b1), "h"(m0), "h"(m1));
-}
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-// TMA operand staging (GEMM form): the k-major planes Aw[Kpad][Mpad] / Bw[Kpad][Npad] are dense 2-D tensors, one
-// cp.async.bulk.tensor.2d per operand and k tile lands a [KT][BM] / [KT][BN] box in shared memory and signals a
-// per-stage mbarrier with the byte count; issued by ONE thread, no address arithmetic or LDGSTS in the other 255.
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n\t.reg .pred P1;\n\t"
-        "LUT_WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
-        "@P1 bra LUT_WAIT_DONE;\n\t"
-        "bra LUT_WAIT_LOOP;\n\t"
-        "LUT_WAIT_DONE:\n\t}" ::"r"(bar), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1)
-{
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
-}
-
-struct LutGemmArgs {
-    const uint32_t* Aw;   // [Kpad][Mpad]
-    const uint32_t* Bw;   // [Kpad][Npad]
-    const uint16_t* lut;  // total_entries (padded to 16 B)
-    float* C;
-    int64_t ldc, Mrows, N, Mpad, Npad;
-    int Kpad;
-    int lut_bytes;        // multiple of 16
-    BiasSrc bias;
-    int M;                // unit u = 2^(1 - bR - M)
-    uint32_t zero_word;   // the A word of a == 0
-    int sparse_a;         // 1 / 0: force the branchy / predicated k loop; -1: decide from zero_count
-    const unsigned long long* zero_count;   // zero activations counted by the predecode pass
-    const int* offgrid;
-    int qamaa;            // 1: epilogue applies the result quantizer to the sum (quantize_after_mult_and_add)
-    QamaaOp qop;
-    // split-K (grids that cannot fill the SMs): blockIdx.z owns a slice of the k tiles and stores its partial
-    // sums, in units of u, to `partial`; splitk_reduce_kernel adds the slices in order.  That changes the
-    // summation order, so it is only USED when every sum involved is provably exact in fp32 (see below);
-    // otherwise *inexact is raised and the unsplit kernel (gate != null) recomputes the output.
-    int splits;
-    float* partial;       // [splits][Mrows][N]
-    int* inexact;
-    const int* tmax;      // [2]: largest table row index of A / of B seen by the predecode pass
-    int t_bias;           // t = tA_idx + tB_idx - t_bias
-    const int* gate;      // non-null: run only if *gate != 0
-    ConvPlane cp;         // CONV instantiations: the A operand is gathered from a decoded NCHW plane
-    // stream-K (sk_ctas > 0): a 1-D grid of sk_ctas persistent CTAs; the (tile, k-tile) work units, tiles in
-    // column-fastest order, are dealt in equal contiguous ranges.  A CTA that covers a tile's whole K range
-    // stores it directly; partial ranges go to `partial` as [cta][slot][BM][BN] (slot 0: the CTA's first
-    // segment, slot 1: its last) and streamk_fixup_kernel adds a tile's segments in k order -- under the same
-    // exactness certificate as split-K (`splits` = upper bound of segments per tile).
-    int sk_ctas, sk_tiles_n;
-    int64_t sk_tiles;
-    Epilogue ep;          // fused +bias -> BN -> activation -> (NCHW) store, epilogue.cuh; ep.on == 0: plain store
-    int use_tma;          // GEMM form only: operand tiles arrive by TMA (mapA / mapB) instead of the cp.async ring
-    alignas(64) CUtensorMap mapA;   // Aw as a 2-D tensor {Mpad, Kpad}, box {BM, KT}
-    alignas(64) CUtensorMap mapB;   // Bw as a 2-D tensor {Npad, Kpad}, box {BN, KT}
-};
-
-// KT: k-tile depth (8 where a large table leaves little shared memory for the operand ring).
-// SIDX: signed-index table layout (lut.cuh): the B word is a full 32-bit byte offset, multiplier +1.0.
-// CONV: implicit im2col in the A-tile loader (ConvPlane) instead of a pre-gathered Aw plane.
-// SK: stream-K instantiation (persistent CTAs over (tile, k-tile) ranges, see LutGemmArgs::sk_ctas).
-template <int WARPS, int RPW, int CPL, int KT, bool SIDX, bool CONV, bool SK>
-__global__ void __launch_bounds__(32 * WARPS, (WARPS >= 16) ? 1 : ((RPW * CPL >= 64) ? 16 / WARPS : 24 / WARPS))
-approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
-{
-    constexpr int BM = RPW * WARPS, BN = 32 * CPL, ST = LUT_STAGES, NTHR = 32 * WARPS;
-    static_assert(CPL == 4 || CPL == 2, "a lane owns 2 or 4 consecutive columns");
-    static_assert(RPW % 4 == 0, "A words are read 4 at a time");
-    if (*a.offgrid != 0) return;   // some operand is off the FP8 grid: the generic kernel takes over
-    if (a.gate && *a.gate == 0) return;
-    extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ __align__(8) uint64_t full_bar[2 * ST];                // TMA: [s] "stage s has landed", [ST + s] "every warp has read stage s"
-    uint32_t* As = reinterpret_cast<uint32_t*>(smem + ((a.lut_bytes + 127) & ~127));   // [ST][KT][BM], 128-byte aligned (TMA)
-    uint32_t* Bs = As + ST * KT * BM;                                 // [ST][KT][BN]
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const bool tma = !CONV && a.use_tma != 0;
-    int64_t m0 = (int64_t)blockIdx.x * BM, n0 = (int64_t)blockIdx.y * BN;
-
-    // pair table -> shared memory
-    {
-        const uint4* src = reinterpret_cast<const uint4*>(a.lut);
-        uint4* dst = reinterpret_cast<uint4*>(smem);
-        for (int i = tid; i < a.lut_bytes / 16; i += NTHR) dst[i] = __ldg(src + i);
-    }
-    const uint32_t lut_base = smem_u32(smem);
-    const uint32_t As_u = smem_u32(As), Bs_u = smem_u32(Bs);
-    const uint32_t bar_u = smem_u32(full_bar);
-    if (tma) {
-        if (tid == 0) {
-#pragma unroll
-            for (int s = 0; s < ST; ++s) { mbar_init(bar_u + 8u * s, 1); mbar_init(bar_u + 8u * (ST + s), WARPS); }
-            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        }
-        __syncthreads();   // nobody polls a barrier before it is initialised
-    }
-
-    // CONV: this thread gathers row (tid % BM) of every A tile, k = tid / BM + j * (NTHR / BM)
-    static_assert(NTHR % BM == 0 && (KT * BM) % NTHR == 0, "A-tile gather mapping");
-    const uint32_t* crow = nullptr;   // address of the row's top-left tap (may lie outside the image: never read)
-    int ch0 = 0, cw0 = 0;
-    auto conv_row_setup = [&]() {
-        const int64_t r = m0 + tid % BM;
-        const int wo = (int)(r % a.cp.Wo);
-        const int64_t t2 = r / a.cp.Wo;
-        const int ho = (int)(t2 % a.cp.Ho);
-        const int64_t b = t2 / a.cp.Ho;
-        ch0 = ho * a.cp.sh - a.cp.ph;
-        cw0 = wo * a.cp.sw - a.cp.pw;
-        if (r >= a.Mrows) ch0 = -(1 << 20);   // rows beyond the matrix: every tap out of range
-        crow = a.cp.Pw + b * a.cp.img_words + (int64_t)ch0 * a.cp.W + cw0;
-    };
-    if (CONV) conv_row_setup();
-    auto load_tile = [&](int kt, int stage) {
-        if (tma) {
-            if (tid == 0) {
-                // the stage was last read through the generic proxy (LDS) before the __syncthreads that precedes this call
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                const uint32_t bar = bar_u + 8u * stage;
-                mbar_expect_tx(bar, (uint32_t)(KT * (BM + BN) * 4));
-                tma_load_2d(As_u + 4u * (uint32_t)(stage * KT * BM), &a.mapA, bar, (int)m0, kt * KT);
-                tma_load_2d(Bs_u + 4u * (uint32_t)(stage * KT * BN), &a.mapB, bar, (int)n0, kt * KT);
-            }
-            return;
-        }
-        const uint32_t* gb = a.Bw + (int64_t)kt * KT * a.Npad + n0;
-        if (CONV) {
-            const int2* ki = a.cp.kinfo + kt * KT + tid / BM;
-            const uint32_t dst = As_u + 4u * (uint32_t)((stage * KT + tid / BM) * BM + tid % BM);
-#pragma unroll
-            for (int j = 0; j < KT * BM / NTHR; ++j) {
-                const int2 q = __ldg(ki + j * (NTHR / BM));
-                const int h = ch0 + (int)(short)(q.y & 0xFFFF), w = cw0 + (q.y >> 16);
-                const bool ok = (unsigned)h < (unsigned)a.cp.H && (unsigned)w < (unsigned)a.cp.W;
-                const uint32_t* src = ok ? crow + q.x : a.cp.zero_src;
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + 4u * (uint32_t)(j * (NTHR / BM) * BM)), "l"(src) : "memory");
-            }
-        } else {
-            const uint32_t* ga = a.Aw + (int64_t)kt * KT * a.Mpad + m0;
-#pragma unroll
-            for (int i = tid; i < KT * BM / 4; i += NTHR) {
-                const int r = i / (BM / 4), c = i % (BM / 4);
-                cp_async16(As_u + 4u * (uint32_t)((stage * KT + r) * BM + c * 4), ga + (int64_t)r * a.Mpad + c * 4);
-            }
-        }
-#pragma unroll
-        for (int i = tid; i < KT * BN / 4; i += NTHR) {
-            const int r = i / (BN / 4), c = i % (BN / 4);
-            cp_async16(Bs_u + 4u * (uint32_t)((stage * KT + r) * BN + c * 4), gb + (int64_t)r * a.Npad + c * 4);
-        }
-    };
-
-    float acc[RPW][CPL];
-#pragma unroll
-    for (int i = 0; i < RPW; ++i)
-#pragma unroll
-        for (int j = 0; j < CPL; ++j) acc[i][j] = 0.0f;
-
-    const int nk_all = a.Kpad / KT;
-    constexpr bool streamk = SK;
-    int kt0 = (!streamk && a.splits > 1) ? (int)((int64_t)blockIdx.z * nk_all / a.splits) : 0;
-    int nk = ((!streamk && a.splits > 1) ? (int)((int64_t)(blockIdx.z + 1) * nk_all / a.splits) : nk_all) - kt0;
-    float macc = 0.0f;   // split-K / stream-K: largest |partial sum| seen at a k-tile boundary
-    const uint32_t zero_word = a.zero_word;
-    // sampled zero statistics of the activations (predecode pass): low half zeros, high half elements
-    const unsigned long long zc = *a.zero_count;
-    const bool sparse = a.sparse_a >= 0 ? a.sparse_a != 0
-                                        : (CPL == 4 && 10ull * (zc & 0xFFFFFFFFull) >= 4ull * (zc >> 32));
-    // stream-K: this CTA's contiguous range of (tile, k-tile) units
-    const int64_t sk_units = a.sk_tiles * nk_all;
-    int64_t sk_u = streamk ? (int64_t)blockIdx.x * sk_units / a.sk_ctas : 0;
-    const int64_t sk_end = streamk ? (int64_t)(blockIdx.x + 1) * sk_units / a.sk_ctas : 1;
-    bool sk_first = true;
-    uint32_t it_base = 0;   // TMA: tiles issued so far by this CTA (stage = it % ST, barrier parity = (it / ST) & 1)
-  for (; sk_u < sk_end; sk_first = false) {
-    if (streamk) {
-        const int64_t tile = sk_u / nk_all;
-        kt0 = (int)(sk_u - tile * nk_all);
-        nk = (int)((nk_all - kt0 < sk_end - sk_u) ? (nk_all - kt0) : (sk_end - sk_u));
-        sk_u += nk;
-        m0 = (tile / a.sk_tiles_n) * BM;
-        n0 = (tile % a.sk_tiles_n) * BN;
-        if (CONV) conv_row_setup();
-#pragma unroll
-        for (int i = 0; i < RPW; ++i)
-#pragma unroll
-            for (int j = 0; j < CPL; ++j) acc[i][j] = 0.0f;
-        macc = 0.0f;
-        __syncthreads();   // every warp is done with the previous segment's operand stages
-    } else {
-        sk_u = sk_end;
-    }
-#pragma unroll
-    for (int s = 0; s < ST - 1; ++s) {
-        if (s < nk) load_tile(kt0 + s, tma ? (int)((it_base + s) % ST) : s);
-        cp_async_commit();
-    }
-    // The k loop exists twice: dense activations use the predicated row (no branches, full ILP across
-    // rows); sparse ones (post-ReLU tensors, about half zeros) use a warp-uniform branch per row.
-    auto mainloop = [&](auto branchy) {
-        constexpr bool BRANCHY = decltype(branchy)::value;
-        for (int kt = 0; kt < nk; ++kt) {
-            const uint32_t it = it_base + (uint32_t)kt;
-            const int stage = tma ? (int)(it % ST) : kt % ST;
-            if (tma) {
-                // no CTA-wide barrier per k tile: a warp only waits for its data; warp 0 (whose lane 0 issues the
-                // loads) additionally waits until every warp has released the stage it is about to refill
-                mbar_wait(bar_u + 8u * stage, (it / ST) & 1u);
-                if (warp == 0 && kt + ST - 1 < nk) {
-                    if (it >= 1) mbar_wait(bar_u + 8u * (ST + (it - 1) % ST), ((it - 1) / ST) & 1u);
-                    load_tile(kt0 + kt + ST - 1, (int)((it + ST - 1) % ST));
-                }
-            } else {
-                cp_async_wait<ST - 2>();
-                __syncthreads();
-                if (kt + ST - 1 < nk) load_tile(kt0 + kt + ST - 1, (kt + ST - 1) % ST);
-                cp_async_commit();
-            }
-            const uint32_t* Asm = As + stage * KT * BM + warp * RPW;
-            const uint32_t* Bsm = Bs + stage * KT * BN + lane * CPL;
-#pragma unroll (KT >= 16 ? 4 : 2)
-            for (int kk = 0; kk < KT; ++kk) {
-                uint32_t bw[CPL];
-                if (CPL == 4) {
-                    const uint4 bq = *reinterpret_cast<const uint4*>(Bsm + kk * BN);
-                    bw[0] = bq.x; bw[1] = bq.y; bw[CPL - 2] = bq.z; bw[CPL - 1] = bq.w;
-                } else {
-                    const uint2 bq = *reinterpret_cast<const uint2*>(Bsm + kk * BN);
-                    bw[0] = bq.x; bw[1] = bq.y;
-                }
-                uint32_t bo[CPL];
-                unsigned short bm[CPL];
-#pragma unroll
-                for (int j = 0; j < CPL; ++j) {
-                    bo[j] = (SIDX ? bw[j] : (bw[j] & 0xFFFFu)) + lut_base;   // table byte address of the (tB_idx, mB) part
-                    bm[j] = SIDX ? (unsigned short)kBf16One : (unsigned short)(bw[j] >> 16);   // bf16 sign of b
-                }
-#pragma unroll
-                for (int i4 = 0; i4 < RPW / 4; ++i4) {
-                    const uint4 aq = *reinterpret_cast<const uint4*>(Asm + kk * BM + i4 * 4);
-                    const uint32_t aw[4] = {aq.x, aq.y, aq.z, aq.w};
-#pragma unroll
-                    for (int ii = 0; ii < 4; ++ii) {
-                        if (BRANCHY) {
-                            // sparse activations: a real (warp-uniform) branch, so that a zero costs neither
-                            // issue slots nor LSU slots (a predicated-off LDS still takes its LSU slot)
-                            if (aw[ii] != zero_word) {
-#pragma unroll
-                                for (int j = 0; j < CPL; ++j)
-                                    fma_bf16(acc[i4 * 4 + ii][j], lds_u16(aw[ii] + bo[j]), bm[j]);
-                            }
-                        } else if (CPL == 4) mac_row4(acc[i4 * 4 + ii][0], acc[i4 * 4 + ii][1], acc[i4 * 4 + ii][CPL - 2],
-                                               acc[i4 * 4 + ii][CPL - 1], aw[ii], zero_word, bo[0], bo[1], bo[CPL - 2],
-                                               bo[CPL - 1], bm[0], bm[1], bm[CPL - 2], bm[CPL - 1]);
-                        else mac_row2(acc[i4 * 4 + ii][0], acc[i4 * 4 + ii][1], aw[ii], zero_word, bo[0], bo[1],
-                                               bm[0], bm[1]);
-                    }
-                }
-            }
-            if (a.splits > 1) {
-#pragma unroll
-                for (int i = 0; i < RPW; ++i)
-#pragma unroll
-                    for (int j = 0; j < CPL; ++j) macc = fmaxf(macc, fabsf(acc[i][j]));
-            }
-            if (tma) {   // this warp is done with the stage
-                __syncwarp();
-                if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_u + 8u * (ST + stage)) : "memory");
-            }
-        }
-    };
-    if (sparse) mainloop(std::true_type{});
-    else            mainloop(std::false_type{});
-    cp_async_wait<0>();
-    it_base += (uint32_t)nk;
-
-    if (streamk && nk < nk_all) {
-        // a partial k range of this tile: certificate as for split-K (see below), then the slot store
-        const int t_max = a.tmax[0] + a.tmax[1] - a.t_bias;
-        int lg = 0;
-        while ((1 << lg) < KT) ++lg;
-        const int dl = t_max + a.M + 1 + lg;
-        if (dl > 23 || !(macc * (float)a.splits <= 16777216.0f - (float)(1 << (dl > 0 ? dl : 0)))) *a.inexact = 1;
-        float* P = a.partial + ((int64_t)blockIdx.x * 2 + (sk_first ? 0 : 1)) * (int64_t)(BM * BN);
-#pragma unroll
-        for (int i = 0; i < RPW; ++i) {
-            float* prow = P + (warp * RPW + i) * BN + lane * CPL;
-            if (CPL == 4) *reinterpret_cast<float4*>(prow) = make_float4(acc[i][0], acc[i][1], acc[i][CPL - 2], acc[i][CPL - 1]);
-            else          *reinterpret_cast<float2*>(prow) = make_float2(acc[i][0], acc[i][1]);
-        }
-        continue;
-    }
-    if (!streamk && a.splits > 1) {
-        // Exactness certificate.  Table entries are integers (units of u) of magnitude <= 2^(t + M + 1), so one
-        // k tile moves a running sum by at most D = KT * 2^(t_max + M + 1).  If every slice's running sum stayed
-        // within (2^24 - D) / splits at all of its k-tile boundaries, then every intermediate sum of every slice,
-        // of the ordered combination of the slices AND of the unsplit k-ascending order is an integer of
-        // magnitude <= 2^24: all of them are exact in fp32, hence the result is bit-identical to the unsplit
-        // kernel's.
-        const int t_max = a.tmax[0] + a.tmax[1] - a.t_bias;
-        int lg = 0;
-        while ((1 << lg) < KT) ++lg;
-        const int dl = t_max + a.M + 1 + lg;   // log2 of D, the most one k tile can move a sum
-        if (dl > 23 || !(macc * (float)a.splits <= 16777216.0f - (float)(1 << (dl > 0 ? dl : 0)))) *a.inexact = 1;
-        float* P = a.partial + (int64_t)blockIdx.z * a.Mrows * a.N;
-        const int64_t n = n0 + lane * CPL;
-#pragma unroll
-        for (int i = 0; i < RPW; ++i) {
-            const int64_t m = m0 + warp * RPW + i;
-            if (m >= a.Mrows) break;
-#pragma unroll
-            for (int j = 0; j < CPL; ++j)
-                if (n + j < a.N) P[m * a.N + n + j] = acc[i][j];
-        }
-        return;
-    }
-    // epilogue: C = acc * u (exact power-of-two scaling); quantize_after_mult_and_add: C = Q(acc * u)
-    const float unit = pow2f_i(1 - a.bias.R() - a.M);
-    if (a.qamaa) {
-        QamaaOp q = a.qop;
-        q.begin();
-#pragma unroll
-        for (int i = 0; i < RPW; ++i)
-#pragma unroll
-            for (int j = 0; j < CPL; ++j) acc[i][j] = q.quant(acc[i][j] * unit) / unit;   // stored below as acc * unit
-    }
-    const int64_t n = n0 + lane * CPL;
-    if (a.ep.on) {
-        // fused epilogue (epilogue.cuh): the lane owns CPL fixed columns = output channels, so their bias / BN
-        // constants live in registers; the final values are computed here
-        Epilogue::Col ec[CPL];
-#pragma unroll
-        for (int j = 0; j < CPL; ++j) ec[j] = a.ep.column(n + j < a.N ? n + j : a.N - 1);
-#pragma unroll
-        for (int i = 0; i < RPW; ++i)
-#pragma unroll
-            for (int j = 0; j < CPL; ++j) acc[i][j] = a.ep.apply(acc[i][j] * unit, ec[j]);
-        if (a.ep.HW > 0) {
-            // NCHW store.  A warp holds RPW consecutive rows (pixels) of 32 * CPL channels: transposed through a
-            // warp-private patch of the (now idle) operand ring, one column of every lane per pass, so that a
-            // store instruction writes runs of RPW consecutive pixels (RPW * 4 contiguous bytes per channel).
-            static_assert(RPW == 16 || RPW == 32, "the transposing store assumes 16 or 32 rows per warp");
-            static_assert((size_t)ST * KT * (BM + BN) * 4 >= (size_t)WARPS * 32 * (RPW + 1) * 4, "staging patch fits the operand ring");
-            __syncthreads();   // every warp is done reading operand stages (no cp.async is in flight: wait<0> above)
-            float* patch = reinterpret_cast<float*>(As) + warp * (32 * (RPW + 1));
-            const int row = lane % RPW, cgrp = lane / RPW;           // this lane's row in the store phase
-            constexpr int CPI = 32 / RPW;                            // channels per store instruction
-            const int64_t m = m0 + warp * RPW + row;
-            const int64_t bimg = m / a.ep.HW, pix = m - bimg * a.ep.HW;
-            float* obase = a.C + (bimg * a.ep.Ctot + a.ep.c0) * a.ep.HW + pix;
-#pragma unroll
-            for (int j = 0; j < CPL; ++j) {
-#pragma unroll
-                for (int i = 0; i < RPW; ++i) patch[lane * (RPW + 1) + i] = acc[i][j];
-                __syncwarp();
-                if (m < a.Mrows) {
-#pragma unroll 4
-                    for (int c = cgrp; c < 32; c += CPI) {
-                        const int64_t nn = n0 + c * CPL + j;
-                        if (nn < a.N) obase[nn * a.ep.HW] = patch[c * (RPW + 1) + row];
-                    }
-                }
-                __syncwarp();
-            }
-            if (streamk) __syncthreads();   // the next segment's prologue overwrites the ring
-            continue;
-        }
-        // row-major: the plain store below, with the scaling already applied
-        const bool vec = ((a.ldc & (CPL - 1)) == 0) && ((reinterpret_cast<uintptr_t>(a.C) & (4 * CPL - 1)) == 0) &&
-                         (n + CPL - 1 < a.N);
-#pragma unroll
-        for (int i = 0; i < RPW; ++i) {
-            const int64_t m = m0 + warp * RPW + i;
-            if (m >= a.Mrows) break;
-            float* crow = a.C + m * a.ldc;
-            if (vec && CPL == 4) {
-                *reinterpret_cast<float4*>(crow + n) = make_float4(acc[i][0], acc[i][1], acc[i][CPL - 2], acc[i][CPL - 1]);
-            } else if (vec) {
-                *reinterpret_cast<float2*>(crow + n) = make_float2(acc[i][0], acc[i][1]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < CPL; ++j)
-                    if (n + j < a.N) crow[n + j] = acc[i][j];
-            }
-        }
-        continue;
-    }
-    const bool vec = ((a.ldc & (CPL - 1)) == 0) && ((reinterpret_cast<uintptr_t>(a.C) & (4 * CPL - 1)) == 0) &&
-                     (n + CPL - 1 < a.N);
-#pragma unroll
-    for (int i = 0; i < RPW; ++i) {
-        const int64_t m = m0 + warp * RPW + i;
-        if (m >= a.Mrows) break;
-        float* crow = a.C + m * a.ldc;
-        if (vec && CPL == 4) {
-            *reinterpret_cast<float4*>(crow + n) =
-                make_float4(acc[i][0] * unit, acc[i][1] * unit, acc[i][CPL - 2] * unit, acc[i][CPL - 1] * unit);
-        } else if (vec) {
-            *reinterpret_cast<float2*>(crow + n) = make_float2(acc[i][0] * unit, acc[i][1] * unit);
-        } else {
-#pragma unroll
-            for (int j = 0; j < CPL; ++j)
-                if (n + j < a.N) crow[n + j] = acc[i][j] * unit;
-        }
-    }
-  }   // stream-K segment loop (one pass otherwise)
 }
 
 // stream-K fix-up: one CTA per output tile.  Finds the CTAs whose unit ranges intersect the tile's K range; a
@@ -1124,6 +757,9 @@ struct LutTileCfg {
     void (*sk_kernel)(LutGemmArgs);
     void (*sk_conv_kernel)(LutGemmArgs);
     int BM() const { return warps * rpw; }
+    // byte-cell twins (approx_gemm_c8.cu), or null
+    void (*kernel8() const)(LutGemmArgs) { void (*k)(LutGemmArgs) = nullptr, (*sk)(LutGemmArgs) = nullptr; lut_c8_kernels(warps, rpw, cpl, kt, sidx, &k, &sk); return k; }
+    void (*sk_kernel8() const)(LutGemmArgs) { void (*k)(LutGemmArgs) = nullptr, (*sk)(LutGemmArgs) = nullptr; lut_c8_kernels(warps, rpw, cpl, kt, sidx, &k, &sk); return sk; }
     int BN() const { return 32 * cpl; }
     size_t smem(int lut_bytes) const { return (size_t)((lut_bytes + 127) & ~127) + (size_t)LUT_STAGES * kt * (BM() + BN()) * 4; }
 };
@@ -1284,6 +920,9 @@ struct LutEntry {
     uint16_t* d_lut = nullptr;
     int lut_bytes = 0;
     LutFlags flags{0, 0};
+    int8_t* d_lut8 = nullptr;     // byte-cell companion (M >= 4, approx_v9 flavour), with d_bad[0] = NT - first unfit row
+    int lut8_bytes = 0;
+    int* d_bad = nullptr;
 };
 
 static std::mutex g_cache_mu;
@@ -1308,6 +947,14 @@ int device_table(const signed char* host, int M, const signed char** dev_out)
     }
     *dev_out = it->second;
     return B200_OK;
+}
+
+// Formats whose table GEMM has a byte-cell variant: the wide mantissas, whose 16-bit cells spread a warp's lookups over
+// more words than there are banks.  B200_LUT_C8=0 switches it off (before / after measurements).
+static bool c8_format(int M)
+{
+    static const bool on = !(getenv("B200_LUT_C8") && atoi(getenv("B200_LUT_C8")) == 0);
+    return on && M >= 4;
 }
 
 // Builds (once per configuration and device) the pair table of lut.cuh.  First use synchronises.
@@ -1335,6 +982,15 @@ static int build_lut(int E, int M, const signed char* dev_table, int with_approx
     B200_LAUNCH_CHECK("lut_build_kernel");
     B200_CUDA_TRY(cudaMemcpy(&e->flags, d_flags, sizeof(LutFlags), cudaMemcpyDeviceToHost));
     cudaFree(d_flags);
+    if (c8_format(M) && !(v5 && v5->on) && !quirk) {
+        e->lut8_bytes = (int)round_up((int64_t)e->geom.total_entries, 16);
+        B200_CUDA_TRY(cudaMalloc(&e->d_lut8, e->lut8_bytes));
+        B200_CUDA_TRY(cudaMalloc(&e->d_bad, sizeof(int)));
+        B200_CUDA_TRY(cudaMemset(e->d_bad, 0, sizeof(int)));
+        lut8_build_kernel<<<(int)ceil_div(e->lut8_bytes, 256), 256>>>(e->geom, e->d_lut, e->d_lut8, e->lut8_bytes, e->d_bad);
+        B200_LAUNCH_CHECK("lut8_build_kernel");
+        B200_CUDA_TRY(cudaDeviceSynchronize());
+    }
     return B200_OK;
 }
 
@@ -1354,6 +1010,8 @@ static int get_lut(int E, int M, const signed char* host_table, const signed cha
         if (!is_v5 && !quirk && e.flags.sign_quirk && !e.flags.unrepresentable) {
             // not odd in the operand signs: rebuild with both signs in the index (lut.cuh)
             cudaFree(e.d_lut);
+            if (e.d_lut8) cudaFree(e.d_lut8);
+            if (e.d_bad) cudaFree(e.d_bad);
             e = LutEntry();
             if (int rc = build_lut(E, M, dev_table, with_approx, clip_OF, true, false, &e)) return rc;
         }
@@ -1463,7 +1121,23 @@ constexpr int kTuneCandidates = 6;
 constexpr int64_t kTuneMinMacs = (int64_t)1 << 26;
 
 constexpr int64_t kPadM = 256, kPadN = 128, kPadK = 32;
-constexpr size_t kFlagBytes = 256;   // ints: [0] off-grid, [2..3] zero statistics, [4..5] row maxima, [6] split-K inexact
+constexpr size_t kFlagBytes = 256;   // ints: [0] off-grid, [2..3] zero statistics, [4..5] row maxima, [6] split-K inexact,
+                                     // [8] escapes, [9] escape-list overflow, [10] qamaa: byte-cell table's "bad row" word,
+                                     // [11] byte cells ran, [16] qamaa: result bias, [32..63] escape-list counters
+constexpr size_t kFlagClearBytes = kFlagBytes;
+// byte-cell variant: escape lists (room for 1/8 of the A elements, 8 bytes each) and the correction sums D[Mrows][N]
+static unsigned esc_list_cap(int64_t Mpad, int64_t Kpad) { return (unsigned)std::max<int64_t>(64, Mpad * Kpad / 8 / kEscLists); }
+static size_t esc_list_bytes(int64_t Mpad, int64_t Kpad) { return (size_t)esc_list_cap(Mpad, Kpad) * kEscLists * 8; }
+static size_t c8_extra_bytes(int64_t Mrows, int64_t N, int64_t Mpad, int64_t Kpad)
+{
+    return esc_list_bytes(Mpad, Kpad) + (size_t)round_up(Mrows * N * 4, 256);
+}
+struct C8Src {
+    const int8_t* lut8 = nullptr;
+    int lut8_bytes = 0;
+    const int* bad = nullptr;
+    uint8_t* extra = nullptr;   // c8_extra_bytes: the escape lists, then D
+};
 static thread_local int g_last_splits = 1;
 
 // Predecode of both operands + the table GEMM launch, shared by the approx path and the
@@ -1472,7 +1146,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
                         int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const LutGeom& geom,
                         const uint16_t* d_lut, int lut_bytes, int* flag, uint32_t* Aw, uint32_t* Bw, int64_t Mpad,
                         int64_t Npad, int64_t Kpad, const QamaaOp* qop, float* partial, void* conv_ws, size_t conv_ws_bytes,
-                        cudaStream_t st, const Epilogue& ep = Epilogue{})
+                        cudaStream_t st, const Epilogue& ep = Epilogue{}, const C8Src& c8src = C8Src{})
 {
     const int M = geom.M;
     static PerDeviceOnce once;
@@ -1484,7 +1158,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
                 B200_CUDA_TRY(cudaFuncSetAttribute(c.sk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
                 B200_CUDA_TRY(cudaFuncSetAttribute(c.sk_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
             }
-            return B200_OK;
+            return lut_c8_set_attributes();
         }))
         return rc;
     int S = 1;
@@ -1493,12 +1167,28 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     bool forced = false;
     const LutTileCfg* tc = choose_lut_tile(Mrows, N, Kpad, lut_bytes, geom.sidx, sms, max_s, &S, &cands, &forced);
     if (!tc) { set_error("b200_approx_gemm: pair table does not fit shared memory"); return B200_ERR_ARGUMENT; }
+    // byte-cell variant: needs the companion table, the flag map and pre-gathered planes (decided below for convs)
+    const bool c8_inputs = c8src.lut8 && c8src.extra && c8src.bad && !geom.v5 && Mpad < ((int64_t)1 << 31) &&
+                           Mpad * Kpad / 8 < ((int64_t)1 << 31);
     PredecodeArgs pa;
-    pa.tmax = partial ? flag + 4 : nullptr;
+    pa.tmax = (partial || c8_inputs) ? flag + 4 : nullptr;
     pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
     pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
+    pa.esc_list = nullptr; pa.esc_cap = esc_list_cap(Mpad, Kpad); pa.esc_counters = reinterpret_cast<unsigned*>(flag + 32);
+    pa.c8_bad = c8src.bad; pa.tmaxB = flag + 5;
     // v5 flavour: a zero operand is an ordinary code (its product is not zero), so there is nothing to skip
     pa.zero_count = geom.v5 ? nullptr : reinterpret_cast<unsigned long long*>(flag + 2);
+    // B first: the A pass of the byte-cell variant compares against the largest tB_idx
+    {
+        PredecodeArgs pb = pa;
+        pb.zero_count = nullptr;
+        pb.tmax = pa.tmax ? flag + 5 : nullptr;
+        pb.src = B; pb.s_row = sb_n; pb.s_k = sb_k; pb.dst = Bw; pb.rows = N; pb.Rpad = Npad;
+        const dim3 pgrid((unsigned)(Npad / 32), (unsigned)(Kpad / 32));
+        if (sb_k == 1 && sb_n != 1) predecode_kernel<true, true><<<pgrid, 256, 0, st>>>(pb, geom);
+        else                        predecode_kernel<true, false><<<pgrid, 256, 0, st>>>(pb, geom);
+        B200_LAUNCH_CHECK("predecode_kernel<B>");
+    }
     // Conv form: decode the input once and let the GEMM gather (needs 16-byte-aligned images and the extra
     // workspace b200_approx_conv2d_workspace_bytes reserves); else write the im2col plane from the NCHW tensor
     // (contiguous along the output pixel, i.e. along rows: read and write row-fastest).
@@ -1519,6 +1209,16 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         // (0, 0), which the gather's shared "zero word" cannot tell from k / row padding: im2col plane only)
         gather = !geom.v5 && mode != 0 && pays && conv_ws && conv_ws_bytes >= need && img % 4 == 0 && total < ((int64_t)1 << 31) &&
                  ((uintptr_t)A.p & 15) == 0 && A.H < 16384 && A.W < 16384 && nB * A.Ho * A.Wo == Mrows;
+    }
+    const bool c8 = c8_inputs && !gather;
+    int* c8_D = c8 ? reinterpret_cast<int*>(c8src.extra + esc_list_bytes(Mpad, Kpad)) : nullptr;
+    if (c8) {
+        pa.esc_list = reinterpret_cast<unsigned long long*>(c8src.extra);
+        B200_CUDA_TRY(cudaMemsetAsync(c8_D, 0, (size_t)Mrows * N * 4, st));
+    }
+    if (A.conv) {
+        const int64_t Cg = K / ((int64_t)A.kh * A.kw), img = Cg * A.H * A.W;
+        const int64_t nB = Mrows / ((int64_t)A.Ho * A.Wo), total = nB * img;
         if (gather) {
             uint32_t* Pw = reinterpret_cast<uint32_t*>(conv_ws);
             int2* kinfo = reinterpret_cast<int2*>(Pw + round_up(total, 4));
@@ -1538,14 +1238,16 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         predecode_kernel<false, true><<<dim3((unsigned)(Mpad / 32), (unsigned)(Kpad / 32)), 256, 0, st>>>(pa, geom);
     }
     B200_LAUNCH_CHECK("predecode_kernel<A>");
-    PredecodeArgs pb = pa;
-    pb.zero_count = nullptr;
-    pb.tmax = partial ? flag + 5 : nullptr;
-    pb.src = B; pb.s_row = sb_n; pb.s_k = sb_k; pb.dst = Bw; pb.rows = N; pb.Rpad = Npad;
-    const dim3 pgrid((unsigned)(Npad / 32), (unsigned)(Kpad / 32));
-    if (sb_k == 1 && sb_n != 1) predecode_kernel<true, true><<<pgrid, 256, 0, st>>>(pb, geom);
-    else                        predecode_kernel<true, false><<<pgrid, 256, 0, st>>>(pb, geom);
-    B200_LAUNCH_CHECK("predecode_kernel<B>");
+    const uint32_t nt_magic = (uint32_t)(((uint64_t)1 << 32) / (uint64_t)geom.NT) + 1u;
+    if (c8) {
+        C8CorrectArgs ca;
+        ca.esc_list = pa.esc_list; ca.esc_cap = pa.esc_cap; ca.esc_counters = pa.esc_counters;
+        ca.esc_total = reinterpret_cast<unsigned*>(flag + 8);
+        ca.Aw = Aw; ca.Bw = Bw; ca.Mpad = Mpad; ca.Npad = Npad; ca.N = N; ca.lut16 = d_lut; ca.c8_bad = c8src.bad;
+        ca.tmax = flag + 4; ca.NT = geom.NT; ca.M = M; ca.sidx = geom.sidx; ca.nt_magic = nt_magic; ca.D = c8_D;
+        c8_correct_kernel<<<(unsigned)(4 * sms), 256, 0, st>>>(ca);
+        B200_LAUNCH_CHECK("c8_correct_kernel");
+    }
 
     LutGemmArgs la;
     la.Aw = Aw; la.Bw = Bw; la.lut = d_lut; la.C = C; la.ldc = ldc; la.Mrows = Mrows; la.N = N;
@@ -1561,6 +1263,12 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     la.partial = partial; la.inexact = flag + 6; la.tmax = flag + 4; la.t_bias = geom.RA + M + 2;
     la.cp = cp;
     la.ep = ep;
+    la.c8 = c8 ? 1 : 0;
+    la.lut8 = c8src.lut8; la.lut8_bytes = c8src.lut8_bytes;
+    la.esc_total = reinterpret_cast<const unsigned*>(flag + 8);
+    la.esc_limit = std::min<int64_t>((int64_t)pa.esc_cap * kEscLists, Mrows * K / 8);
+    la.c8_D = c8_D;
+    la.c8_ran = flag + 11;
     la.use_tma = 0;
     memset(&la.mapA, 0, sizeof(la.mapA));
     memset(&la.mapB, 0, sizeof(la.mapB));
@@ -1578,6 +1286,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     };
     auto launch = [&](const LutTileCfg* cfg, int splits) -> int {
         LutGemmArgs l = la;
+        if (l.c8 && (!cfg->kernel8() || !cfg->sk_kernel8())) l.c8 = 0;
         if (int rc = set_maps(l, cfg)) return rc;
         l.splits = splits; l.gate = nullptr;
         l.sk_ctas = 0; l.sk_tiles_n = 0; l.sk_tiles = 0;
@@ -1589,12 +1298,20 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
             l.splits = (int)(2 + nk_all / std::max<int64_t>(1, tiles * nk_all / G));   // segments per tile, upper bound
             (gather ? cfg->sk_conv_kernel : cfg->sk_kernel)<<<dim3((unsigned)G), 32 * cfg->warps, cfg->smem(lut_bytes), st>>>(l);
             B200_LAUNCH_CHECK("approx_gemm_lut_kernel(stream-K)");
+            if (l.c8) {   // the byte-cell twin: same units, same slots; one of the two exits at once (c8_selected)
+                cfg->sk_kernel8()<<<dim3((unsigned)G), 32 * cfg->warps, cfg->smem(l.lut8_bytes), st>>>(l);
+                B200_LAUNCH_CHECK("approx_gemm_lut_kernel(stream-K, byte cells)");
+            }
             streamk_fixup_kernel<<<(unsigned)tiles, 256, 0, st>>>(partial, (int)G, tiles, (int)tgrid.y, (int)nk_all, cfg->BM(),
                                                                   cfg->BN(), C, ldc, Mrows, N, bias, M, l.qamaa, l.qop,
                                                                   flag + 6, flag, ep);
             B200_LAUNCH_CHECK("streamk_fixup_kernel");
         } else {
             (gather ? cfg->conv_kernel : cfg->kernel)<<<tgrid, 32 * cfg->warps, cfg->smem(lut_bytes), st>>>(l);
+            if (l.c8) {   // the byte-cell twin on the same planes; one of the two exits at once (c8_selected)
+                B200_LAUNCH_CHECK("approx_gemm_lut_kernel");
+                cfg->kernel8()<<<tgrid, 32 * cfg->warps, cfg->smem(l.lut8_bytes), st>>>(l);
+            }
         }
         if (splits > 1) {
             B200_LAUNCH_CHECK("approx_gemm_lut_kernel(split-K)");
@@ -1711,7 +1428,7 @@ extern "C" size_t b200_approx_gemm_workspace_bytes(int64_t Mrows, int64_t K, int
     if (Mrows < 0 || K < 0 || N < 0) return 0;
     const int64_t Mpad = round_up(Mrows > 0 ? Mrows : 1, kPadM), Npad = round_up(N > 0 ? N : 1, kPadN);
     const int64_t Kpad = round_up(K > 0 ? K : 1, kPadK);
-    return kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4 + splitk_partial_bytes(Mrows, N);
+    return kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4 + c8_extra_bytes(Mrows, N, Mpad, Kpad) + splitk_partial_bytes(Mrows, N);
 }
 
 size_t b200::conv_gather_workspace_bytes(int64_t nB, int64_t Cg, int64_t H, int64_t W, int64_t Kg)
@@ -1781,7 +1498,9 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     }
 
     const int64_t Mpad = round_up(Mrows, kPadM), Npad = round_up(N, kPadN), Kpad = round_up(K, kPadK);
-    const size_t words = kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4, need = words;
+    // flag block, both decoded planes, the byte-cell variant's escape lists and correction sums
+    const size_t planes = kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4;
+    const size_t words = planes + c8_extra_bytes(Mrows, N, Mpad, Kpad), need = words;
     if (!workspace || workspace_bytes < need) {
         set_error("b200_approx_gemm: workspace too small (see b200_approx_gemm_workspace_bytes)");
         return B200_ERR_WORKSPACE;
@@ -1789,7 +1508,12 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     int* flag = reinterpret_cast<int*>(workspace);
     uint32_t* Aw = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(workspace) + kFlagBytes);
     uint32_t* Bw = Aw + (size_t)Kpad * Mpad;
-    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 32, st));
+    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, kFlagClearBytes, st));
+    C8Src c8src;
+    if (lut->d_lut8 && !p->force_table16) {
+        c8src.lut8 = lut->d_lut8; c8src.lut8_bytes = lut->lut8_bytes; c8src.bad = lut->d_bad;
+        c8src.extra = reinterpret_cast<uint8_t*>(workspace) + planes;
+    }
 
     // split-K partial sums: only if the caller's workspace has the room b200_approx_gemm_workspace_bytes asks for
     // (not in the v5 flavour: without sim_hw_add_OFUF its cells need not be integers of u, and the exactness
@@ -1800,7 +1524,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     void* conv_ws = workspace_bytes > words + pbytes ? reinterpret_cast<char*>(workspace) + words + pbytes : nullptr;
     const size_t conv_ws_bytes = conv_ws ? workspace_bytes - words - pbytes : 0;
     if (int rc = run_lut_gemm(A, B, sb_k, sb_n, C, ldc, Mrows, K, N, bias, lut->geom, lut->d_lut, lut->lut_bytes, flag,
-                              Aw, Bw, Mpad, Npad, Kpad, nullptr, partial, conv_ws, conv_ws_bytes, st, ep))
+                              Aw, Bw, Mpad, Npad, Kpad, nullptr, partial, conv_ws, conv_ws_bytes, st, ep, c8src))
         return rc;
     // runs only if the predecode found an off-grid operand
     pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1, ep);
@@ -1813,7 +1537,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
 // quantize_after_mult_and_add on the table kernel.  `hint` carries the operand exponent biases (the
 // fake-quantizers' custom_bias tensors): they only fix the table's index range -- an operand outside the
 // grid they describe raises the device flag and the arithmetic kernel recomputes the output.
-constexpr size_t kQamaaTableBytes = 128 * 1024;
+constexpr size_t kQamaaTable16Bytes = 128 * 1024, kQamaaTableBytes = 192 * 1024;   // 16-bit table + byte-cell companion
 
 extern "C" size_t b200_qamaa_gemm_workspace_bytes(int64_t Mrows, int64_t K, int64_t N)
 {
@@ -1845,25 +1569,36 @@ int b200::qamaa_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t s
     }
     const LutGeom geom = make_lut_geom(E, M);
     const int lut_bytes = (int)round_up((int64_t)geom.total_entries * 2, 16);
-    if ((size_t)lut_bytes > kQamaaTableBytes) { set_error("b200_qamaa_gemm: table does not fit"); return B200_ERR_ARGUMENT; }
+    const int lut8_bytes = (int)round_up((int64_t)geom.total_entries, 16);
+    if ((size_t)lut_bytes > kQamaaTable16Bytes || (size_t)lut8_bytes > kQamaaTableBytes - kQamaaTable16Bytes) {
+        set_error("b200_qamaa_gemm: table does not fit");
+        return B200_ERR_ARGUMENT;
+    }
     const int64_t Mpad = round_up(Mrows, kPadM), Npad = round_up(N, kPadN), Kpad = round_up(K, kPadK);
     int* flag = reinterpret_cast<int*>(workspace);
     float* bias_R = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 64);
     uint32_t* Aw = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(workspace) + kFlagBytes);
     uint32_t* Bw = Aw + (size_t)Kpad * Mpad;
     uint16_t* d_lut = reinterpret_cast<uint16_t*>(Bw + (size_t)Kpad * Npad);
-    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, 32, st));
+    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, kFlagClearBytes, st));
     lut_build_qamaa_kernel<<<(int)ceil_div(lut_bytes / 2, 256), 256, 0, st>>>(geom, op, d_lut, bias_R, flag);
     B200_LAUNCH_CHECK("lut_build_qamaa_kernel");
+    C8Src c8src;
+    uint8_t* after_tables = reinterpret_cast<uint8_t*>(d_lut) + kQamaaTableBytes;
+    if (c8_format(M)) {   // byte-cell companion of this call's table, its "bad row" word in the flag block
+        int8_t* d_lut8 = reinterpret_cast<int8_t*>(reinterpret_cast<char*>(d_lut) + kQamaaTable16Bytes);
+        lut8_build_kernel<<<(int)ceil_div(lut8_bytes, 256), 256, 0, st>>>(geom, d_lut, d_lut8, lut8_bytes, flag + 10);
+        B200_LAUNCH_CHECK("lut8_build_kernel");
+        c8src.lut8 = d_lut8; c8src.lut8_bytes = lut8_bytes; c8src.bad = flag + 10; c8src.extra = after_tables;
+    }
     BiasSrc bias = *hint;
     bias.fR = bias_R;                                   // result bias = the quantizer's, computed on the device
-    float* partial = splitk_partial_bytes(Mrows, N)
-                         ? reinterpret_cast<float*>(reinterpret_cast<char*>(d_lut) + kQamaaTableBytes) : nullptr;
+    float* partial = splitk_partial_bytes(Mrows, N) ? reinterpret_cast<float*>(after_tables + c8_extra_bytes(Mrows, N, Mpad, Kpad)) : nullptr;
     const size_t base_bytes = b200_qamaa_gemm_workspace_bytes(Mrows, K, N);
     void* conv_ws = workspace_bytes > base_bytes ? reinterpret_cast<char*>(workspace) + base_bytes : nullptr;
     const size_t conv_ws_bytes = conv_ws ? workspace_bytes - base_bytes : 0;
     if (int rc = run_lut_gemm(A, B, sb_k, sb_n, C, ldc, Mrows, K, N, bias, geom, d_lut, lut_bytes, flag, Aw, Bw, Mpad,
-                              Npad, Kpad, &op, partial, conv_ws, conv_ws_bytes, st))
+                              Npad, Kpad, &op, partial, conv_ws, conv_ws_bytes, st, Epilogue{}, c8src))
         return rc;
     pair_gemm_kernel<QamaaOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1);
     B200_LAUNCH_CHECK("pair_gemm_kernel<QamaaOp>(conditional)");
@@ -1990,7 +1725,7 @@ extern "C" int b200_profile_end(double* total_ms, int* launches)
 //   * In host code `g_static_scratch` is only a stand-in for the symbol: its device address is looked up once
 //     per device (with that device current) through cudaGetSymbolAddress and that pointer goes to the kernels.
 //   * All calls on a device share the array and it keeps the previous call's contents: the flag words are
-//     cleared at the start of every call (qamaa_gemm_impl: cudaMemsetAsync(flag, 0, 32)), planes, table and
+//     cleared at the start of every call (qamaa_gemm_impl: cudaMemsetAsync of the flag words), planes, table and
 //     partial sums are fully rewritten before they are read.  Calls that overlap on the GPU (two streams, two
 //     host threads) RACE on it -- serialise them.
 //   * No cudaMalloc / cudaFree / allocating library routine on this path.

@@ -64,8 +64,21 @@ def _workspace(device, nbytes):
     return ws
 
 
+def table_variant(device=None):
+    """Which variant of the table GEMM computed the last approx / qamaa call on this (device, stream): "byte-cells"
+    (int8 cells in shared memory, integer accumulators; picked on the device for mant_width >= 4 when every sum is
+    exact and escapes are rare) or "16-bit".  Reads one flag word of the workspace: synchronises (tests, tools)."""
+    idx = torch.cuda.current_device() if device is None else torch.device(device).index
+    ws = _WORKSPACES.get((idx, torch.cuda.current_stream(idx).cuda_stream))
+    if ws is None:
+        return None
+    flags = ws[:48].view(torch.int32).cpu()
+    return {"variant": "byte-cells" if int(flags[11]) else "16-bit", "escapes": int(flags[8]) & 0xFFFFFFFF,
+            "tmax": (int(flags[4]), int(flags[5])), "offgrid": int(flags[0])}
+
+
 def make_params(custom_approx_params=None, *, single_column_quirk=False, allow_unpinned_format=False,
-                force_generic=False, ofuf_mode=None, **overrides):
+                force_generic=False, ofuf_mode=None, force_table16=False, **overrides):
     """Builds the POD struct from the reference's `custom_approx_params` dict (13 keys,
     utils/click_options.py:589-606); missing keys take the defaults of custom_matmul_vectorize's
     signature (approx/approx_matmul_whole_v9.py:10-18).
@@ -86,6 +99,7 @@ def make_params(custom_approx_params=None, *, single_column_quirk=False, allow_u
     p.single_column_quirk = 1 if single_column_quirk else 0
     p.allow_unpinned_format = 1 if allow_unpinned_format else 0
     p.force_generic = 1 if force_generic else 0
+    p.force_table16 = 1 if force_table16 else 0    # tests / before-after runs: skip the byte-cell table variant
     if ofuf_mode is None:
         ofuf_mode = (custom_approx_params or {}).get("ofuf_mode", 0)
     p.ofuf_mode = 1 if ofuf_mode in (1, True, "v5") else 0

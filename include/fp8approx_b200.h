@@ -61,6 +61,8 @@ typedef struct b200_approx_params {
     uint8_t force_generic;       /* 1: skip the table kernel, use the per-pair arithmetic kernel (tests) */
     uint8_t ofuf_mode;           /* 0: approx_v9 (OF/UF flags ignored).  1: the v5 integer-add GEMM with the simulated
                                     hardware-adder overflow / underflow, approx_matmul_whole_v5.py:10-182 */
+    uint8_t force_table16;       /* 1: never take the byte-cell variant of the table kernel (tests, before / after runs).
+                                    The variant computes the same bits; it is picked on the device for mant_width >= 4 */
     const int8_t *custom_table;  /* HOST pointer or NULL.  Non-NULL: use this 2^M x 2^M int8 table (the
                                     error_table_NN argument of custom_matmul_vectorize,
                                     approx_matmul_whole_v9.py:12) instead of selecting by withComp/dnsmp_factor */
