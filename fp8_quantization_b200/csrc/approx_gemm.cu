@@ -197,25 +197,72 @@ constexpr int kEscLists = 32;
 // integer within +-127) the cell, in units of u, is added to D[m][n].  The byte-cell GEMM starts its sums from D.
 // Work is (escapes x N) cheap tests and rare lookups: escapes are at most 1/8 of the A elements (usually a 1e-4
 // fraction), or the gate is closed and nobody reads D.  Block 0 also publishes the total and the overflow flag.
+// Two-sided escapes.  A pair needs a 16-bit cell only if tA_idx + tB_idx lies above the last all-int8 row, so what
+// counts as an A escape depends on the largest tB_idx -- and one thinly populated top binade of B (the channel maxima)
+// can turn a whole populated binade of A into escapes.  c8_pick_kernel therefore reads the histogram of tB_idx and
+// declares the top levels holding at most 1/256 of B "rare"; c8_brare_kernel lists those elements; the A pass compares
+// against the largest NON-rare level, and the correction pass covers (A escape x any B) and (rare B x non-escape A).
 struct C8CorrectArgs {
     const unsigned long long* esc_list;
     unsigned esc_cap;
     const unsigned* esc_counters;
     unsigned* esc_total;       // [0] total, [1] a list overflowed
+    const unsigned long long* brare_list;
+    unsigned brare_cap;
+    const unsigned* brare_count;
     const uint32_t* Aw;
     const uint32_t* Bw;
-    int64_t Mpad, Npad, N;
+    int64_t Mpad, Npad, N, Mrows;
     const uint16_t* lut16;
     const int* c8_bad;
-    const int* tmax;           // [0] A, [1] B
+    const int* tb_eff;         // largest non-rare tB_idx
     int NT, M, sidx;
-    uint32_t nt_magic;
+    uint32_t nt_magic, zero_word;
     int* D;
 };
+__global__ void c8_pick_kernel(const unsigned* __restrict__ hist, const int* __restrict__ tmaxB, int64_t elements, int sidx,
+                               int* __restrict__ tb_eff)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    int t = *tmaxB;
+    if (!sidx) {   // (signed-index layout: the B word hides tB_idx -- no rare class)
+        unsigned long long rare = 0;
+        while (t > 0 && (rare + hist[t & 63]) * 256ull <= (unsigned long long)elements) { rare += hist[t & 63]; --t; }
+    }
+    *tb_eff = t;
+}
+__global__ void __launch_bounds__(256) c8_brare_kernel(const uint32_t* __restrict__ Bw, int64_t Npad, int64_t N, int64_t K, int M,
+                                                       const int* __restrict__ tb_eff, unsigned long long* __restrict__ list,
+                                                       unsigned cap, unsigned* __restrict__ count)
+{
+    const int thr = *tb_eff;
+    const int64_t total = K * Npad, stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x; i0 < total; i0 += stride) {   // warp-uniform trip count
+        const int64_t i = i0 + threadIdx.x;
+        bool rare = false;
+        int64_t k = 0, n = 0;
+        if (i < total) {
+            k = i / Npad; n = i - k * Npad;
+            rare = n < N && (int)((__ldg(Bw + i) & 0xFFFFu) >> (M + 1)) > thr;
+        }
+        const unsigned m = __ballot_sync(0xFFFFFFFFu, rare);
+        if (m == 0) continue;
+        const unsigned lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+        unsigned base = 0;
+        if (lane == leader) base = atomicAdd(count, __popc(m));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+        if (rare) {
+            const unsigned pos = base + __popc(m & ((1u << lane) - 1u));
+            if (pos < cap) list[pos] = ((unsigned long long)k << 32) | (unsigned long long)(uint32_t)n;
+        }
+    }
+}
+__device__ __forceinline__ bool c8_fits(float v) { return v == rintf(v) && fabsf(v) <= 127.0f; }
 __global__ void __launch_bounds__(256) c8_correct_kernel(C8CorrectArgs a)
 {
+    const unsigned nbr = *a.brare_count;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        unsigned tot = 0, ovf = 0;
+        unsigned tot = 0, ovf = nbr > a.brare_cap;
         for (int l = 0; l < kEscLists; ++l) { const unsigned c = a.esc_counters[l]; tot += c; ovf |= (c > a.esc_cap); }
         a.esc_total[0] = tot;
         a.esc_total[1] = ovf;
@@ -223,27 +270,57 @@ __global__ void __launch_bounds__(256) c8_correct_kernel(C8CorrectArgs a)
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int R8 = a.NT - 1 - *a.c8_bad;
+    const int thrA = R8 - *a.tb_eff;
+    // Work items are (list entry, 32-wide chunk of the other dimension), dealt round-robin to the warps: thousands of
+    // short independent items instead of a few long serial walks (the loads are L2 / DRAM latency bound).
+    // (A escape) x (every column)
+    const uint32_t nch = (uint32_t)((a.N + 31) >> 5);
     for (int l = 0; l < kEscLists; ++l) {
         const unsigned cnt = min(a.esc_counters[l], a.esc_cap);
-        for (int64_t e = warp; e < cnt; e += nwarps) {
+        const int64_t items = (int64_t)cnt * nch;
+        for (int64_t it = warp; it < items; it += nwarps) {
+            const uint32_t e = items < ((int64_t)1 << 32) ? (uint32_t)it / nch : (uint32_t)(it / nch);
+            const uint32_t ch = (uint32_t)(it - (int64_t)e * nch);
             const unsigned long long ent = a.esc_list[(size_t)l * a.esc_cap + e];
             const int64_t m = (int64_t)(ent & 0xFFFFFFFFull), k = (int64_t)(ent >> 32);
-            const uint32_t aw = a.Aw[k * a.Mpad + m];
+            const int64_t n = (int64_t)ch * 32 + lane;
+            if (n >= a.N) continue;
+            const uint32_t aw = __ldg(a.Aw + k * a.Mpad + m);
+            const uint32_t bw = __ldg(a.Bw + k * a.Npad + n);
             const uint32_t x = aw >> (a.M + 1);
             const int tA = (int)(x - (uint32_t)a.NT * __umulhi(x, a.nt_magic));
-            const uint32_t* brow = a.Bw + k * a.Npad;
-            for (int64_t n = lane; n < a.N; n += 32) {
-                const uint32_t bw = __ldg(brow + n);
-                const uint32_t o16 = a.sidx ? bw : (bw & 0xFFFFu);
-                // plain layout: the B offset's row is tB_idx; rows up to R8 hold int8 cells only (signed-index layout:
-                // the region offset hides tB_idx -- look every pair up)
-                if (!a.sidx && tA + (int)(o16 >> (a.M + 1)) <= R8) continue;
-                const float v = __uint_as_float((uint32_t)__ldg(a.lut16 + ((aw + o16) >> 1)) << 16);
-                if (v == rintf(v) && fabsf(v) <= 127.0f) continue;                 // the byte table has this cell
-                const int sg = a.sidx ? 1 : (((int)bw >> 30) | 1);
-                atomicAdd(a.D + m * a.N + n, __float2int_rn(v) * sg);
-            }
+            const uint32_t o16 = a.sidx ? bw : (bw & 0xFFFFu);
+            // plain layout: the B offset's row is tB_idx; rows up to R8 hold int8 cells only (signed-index layout:
+            // the region offset hides tB_idx -- look every pair up)
+            if (!a.sidx && tA + (int)(o16 >> (a.M + 1)) <= R8) continue;
+            const float v = __uint_as_float((uint32_t)__ldg(a.lut16 + ((aw + o16) >> 1)) << 16);
+            if (c8_fits(v)) continue;                                              // the byte table has this cell
+            const int sg = a.sidx ? 1 : (((int)bw >> 30) | 1);
+            atomicAdd(a.D + m * a.N + n, __float2int_rn(v) * sg);
         }
+    }
+    // (rare B) x (every row that is not an A escape)
+    const unsigned nb = min(nbr, a.brare_cap);
+    const uint32_t mch = (uint32_t)((a.Mrows + 31) >> 5);
+    const int64_t items = (int64_t)nb * mch;
+    for (int64_t it = warp; it < items; it += nwarps) {
+        const uint32_t e = items < ((int64_t)1 << 32) ? (uint32_t)it / mch : (uint32_t)(it / mch);
+        const uint32_t ch = (uint32_t)(it - (int64_t)e * mch);
+        const unsigned long long ent = a.brare_list[e];
+        const int64_t n = (int64_t)(ent & 0xFFFFFFFFull), k = (int64_t)(ent >> 32);
+        const int64_t m = (int64_t)ch * 32 + lane;
+        if (m >= a.Mrows) continue;
+        const uint32_t bw = __ldg(a.Bw + k * a.Npad + n);
+        const uint32_t aw = __ldg(a.Aw + k * a.Mpad + m);
+        if (aw == a.zero_word) continue;
+        const uint32_t o16 = bw & 0xFFFFu;
+        const int tB = (int)(o16 >> (a.M + 1));
+        const uint32_t x = aw >> (a.M + 1);
+        const int tA = (int)(x - (uint32_t)a.NT * __umulhi(x, a.nt_magic));
+        if (tA > thrA || tA + tB <= R8) continue;                                  // an escape (done above) / int8 rows only
+        const float v = __uint_as_float((uint32_t)__ldg(a.lut16 + ((aw + o16) >> 1)) << 16);
+        if (c8_fits(v)) continue;
+        atomicAdd(a.D + m * a.N + n, __float2int_rn(v) * (((int)bw >> 30) | 1));
     }
 }
 
@@ -270,7 +347,8 @@ struct PredecodeArgs {
     unsigned esc_cap;
     unsigned* esc_counters;           // [kEscLists]
     const int* c8_bad;                // NT - (first row with a cell that does not fit int8), 0 if none
-    const int* tmaxB;
+    const int* tmaxB;                 // largest tB_idx among the B elements that are not "rare" (c8_pick_kernel)
+    unsigned* hist;                   // B operand: [64] histogram of tB_idx, or null
     __device__ __forceinline__ int thrA(const LutGeom& g) const
     {
         return esc_list ? (g.NT - 1 - *c8_bad) - *tmaxB : 0x7FFFFFFF;
@@ -318,8 +396,9 @@ __device__ __forceinline__ uint32_t predecode_a(const LutGeom& g, float v, int b
     return predecode_a(g, v, bA, off, tmax, 0x7FFFFFFF, esc);
 }
 
-__device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int bA, int bB, int bR, int& off, int& tmax)
+__device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int bA, int bB, int bR, int& off, int& tmax, int& tbi)
 {
+    tbi = -1;
     const uint32_t bits = __float_as_uint(v);
     const uint32_t mag = bits & 0x7FFFFFFFu;
     const uint32_t zero_b = g.sidx ? 0u : (kBf16One << 16);   // tB_idx = 0: every product rounds to 0
@@ -335,6 +414,7 @@ __device__ __forceinline__ uint32_t predecode_b(const LutGeom& g, float v, int b
     }
     if (tB < -g.RA) tB = -g.RA;
     tmax = max(tmax, tB + g.RA);
+    tbi = tB + g.RA;
     const uint32_t mB = frac >> (23 - M);
     const uint32_t boff = 2u * (mB + (uint32_t)(g.row_entries * (tB + g.RA)));
     if (g.sidx) return boff + ((bits >> 31) ? 2u * (uint32_t)g.s_stride : 0u);   // sign of b selects a region
@@ -394,6 +474,11 @@ template <bool IS_B, bool SRC_K_CONTIG>
 __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom g)
 {
     __shared__ uint32_t tile[32][33];
+    __shared__ unsigned s_hist[64];   // B operand, byte-cell variant: histogram of tB_idx
+    if (IS_B && a.hist) {
+        if (threadIdx.x < 64) s_hist[threadIdx.x] = 0;
+        __syncthreads();
+    }
     const int64_t r0 = (int64_t)blockIdx.x * 32, k0 = (int64_t)blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
     int off = 0, zeros = 0, tmax = 0;
@@ -407,13 +492,15 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
             const int64_t r = r0 + ty + i * 8, k = k0 + tx;
             uint32_t w = IS_B ? (g.sidx ? 0u : (kBf16One << 16)) : 2u * (uint32_t)g.zeroA_off;
             bool esc = false;
+            int tbi = -1;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
-                w = IS_B ? (g.v5 ? predecode_b_v5(g, v, bA, a.bias.B(r), bR, off) : predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax))
+                w = IS_B ? (g.v5 ? predecode_b_v5(g, v, bA, a.bias.B(r), bR, off) : predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax, tbi))
                          : (g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax, thrA, esc));
                 if (!IS_B) zeros += (v == 0.0f);
             }
             if (!IS_B && a.esc_list) a.escape(esc, r, k, elist);
+            if (IS_B && a.hist && tbi >= 0) atomicAdd(&s_hist[tbi & 63], 1u);
             tile[tx][ty + i * 8] = w;   // [k][r]
         }
         __syncthreads();
@@ -428,13 +515,15 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
             const int64_t k = k0 + ty + i * 8, r = r0 + tx;
             uint32_t w = IS_B ? (g.sidx ? 0u : (kBf16One << 16)) : 2u * (uint32_t)g.zeroA_off;
             bool esc = false;
+            int tbi = -1;
             if (r < a.rows && k < a.K) {
                 const float v = IS_B ? a.src[r * a.s_row + k * a.s_k] : a.asrc.load(r, k);
-                w = IS_B ? (g.v5 ? predecode_b_v5(g, v, bA, a.bias.B(r), bR, off) : predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax))
+                w = IS_B ? (g.v5 ? predecode_b_v5(g, v, bA, a.bias.B(r), bR, off) : predecode_b(g, v, bA, a.bias.B(r), bR, off, tmax, tbi))
                          : (g.v5 ? predecode_a_v5(g, v, bA, off) : predecode_a(g, v, bA, off, tmax, thrA, esc));
                 if (!IS_B) zeros += (v == 0.0f);
             }
             if (!IS_B && a.esc_list) a.escape(esc, r, k, elist);
+            if (IS_B && a.hist && tbi >= 0) atomicAdd(&s_hist[tbi & 63], 1u);
             if (k < a.Kpad && r < a.Rpad) a.dst[k * a.Rpad + r] = w;
         }
     }
@@ -442,6 +531,10 @@ __global__ void __launch_bounds__(256) predecode_kernel(PredecodeArgs a, LutGeom
     if (a.tmax) {
         tmax = __reduce_max_sync(0xFFFFFFFFu, tmax);
         if ((threadIdx.x & 31) == 0 && tmax > *(volatile int*)a.tmax) atomicMax(a.tmax, tmax);
+    }
+    if (IS_B && a.hist) {
+        __syncthreads();
+        if (threadIdx.x < 64 && s_hist[threadIdx.x]) atomicAdd(a.hist + threadIdx.x, s_hist[threadIdx.x]);
     }
     // zero statistics of the A operand, sampled: one block in 8 along the rows counts its zeros and its
     // elements (one 64-bit atomic: zeros in the low half, elements in the high half)
@@ -1123,20 +1216,23 @@ constexpr int64_t kTuneMinMacs = (int64_t)1 << 26;
 constexpr int64_t kPadM = 256, kPadN = 128, kPadK = 32;
 constexpr size_t kFlagBytes = 256;   // ints: [0] off-grid, [2..3] zero statistics, [4..5] row maxima, [6] split-K inexact,
                                      // [8] escapes, [9] escape-list overflow, [10] qamaa: byte-cell table's "bad row" word,
-                                     // [11] byte cells ran, [16] qamaa: result bias, [32..63] escape-list counters
+                                     // [11] byte cells ran, [12] largest non-rare tB_idx, [13] rare B elements, [16] qamaa: result bias, [32..63] escape-list counters
 constexpr size_t kFlagClearBytes = kFlagBytes;
-// byte-cell variant: escape lists (room for 1/8 of the A elements, 8 bytes each) and the correction sums D[Mrows][N]
+// byte-cell variant, extra workspace: [histogram of tB_idx, 256 B][correction sums D[Mrows][N]][rare-B list]
+// [escape lists of A: room for 1/8 of the A elements, 8 bytes each]
 static unsigned esc_list_cap(int64_t Mpad, int64_t Kpad) { return (unsigned)std::max<int64_t>(64, Mpad * Kpad / 8 / kEscLists); }
 static size_t esc_list_bytes(int64_t Mpad, int64_t Kpad) { return (size_t)esc_list_cap(Mpad, Kpad) * kEscLists * 8; }
-static size_t c8_extra_bytes(int64_t Mrows, int64_t N, int64_t Mpad, int64_t Kpad)
+static unsigned brare_cap(int64_t Npad, int64_t Kpad) { return (unsigned)std::max<int64_t>(64, Npad * Kpad / 128); }
+static size_t c8_D_bytes(int64_t Mrows, int64_t N) { return (size_t)round_up(Mrows * N * 4, 256); }
+static size_t c8_extra_bytes(int64_t Mrows, int64_t N, int64_t Mpad, int64_t Npad, int64_t Kpad)
 {
-    return esc_list_bytes(Mpad, Kpad) + (size_t)round_up(Mrows * N * 4, 256);
+    return 256 + c8_D_bytes(Mrows, N) + (size_t)brare_cap(Npad, Kpad) * 8 + esc_list_bytes(Mpad, Kpad);
 }
 struct C8Src {
     const int8_t* lut8 = nullptr;
     int lut8_bytes = 0;
     const int* bad = nullptr;
-    uint8_t* extra = nullptr;   // c8_extra_bytes: the escape lists, then D
+    uint8_t* extra = nullptr;   // c8_extra_bytes
 };
 static thread_local int g_last_splits = 1;
 
@@ -1175,7 +1271,12 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
     pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
     pa.esc_list = nullptr; pa.esc_cap = esc_list_cap(Mpad, Kpad); pa.esc_counters = reinterpret_cast<unsigned*>(flag + 32);
-    pa.c8_bad = c8src.bad; pa.tmaxB = flag + 5;
+    pa.c8_bad = c8src.bad; pa.tmaxB = flag + 12; pa.hist = nullptr;
+    unsigned* c8_hist = reinterpret_cast<unsigned*>(c8src.extra);
+    int* c8_D = c8_inputs ? reinterpret_cast<int*>(c8src.extra + 256) : nullptr;
+    unsigned long long* brare_list = c8_inputs ? reinterpret_cast<unsigned long long*>(c8src.extra + 256 + c8_D_bytes(Mrows, N)) : nullptr;
+    if (c8_inputs)   // histogram + correction sums start at zero
+        B200_CUDA_TRY(cudaMemsetAsync(c8src.extra, 0, 256 + (size_t)Mrows * N * 4, st));
     // v5 flavour: a zero operand is an ordinary code (its product is not zero), so there is nothing to skip
     pa.zero_count = geom.v5 ? nullptr : reinterpret_cast<unsigned long long*>(flag + 2);
     // B first: the A pass of the byte-cell variant compares against the largest tB_idx
@@ -1184,10 +1285,20 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         pb.zero_count = nullptr;
         pb.tmax = pa.tmax ? flag + 5 : nullptr;
         pb.src = B; pb.s_row = sb_n; pb.s_k = sb_k; pb.dst = Bw; pb.rows = N; pb.Rpad = Npad;
+        pb.hist = (c8_inputs && !geom.sidx) ? c8_hist : nullptr;
         const dim3 pgrid((unsigned)(Npad / 32), (unsigned)(Kpad / 32));
         if (sb_k == 1 && sb_n != 1) predecode_kernel<true, true><<<pgrid, 256, 0, st>>>(pb, geom);
         else                        predecode_kernel<true, false><<<pgrid, 256, 0, st>>>(pb, geom);
         B200_LAUNCH_CHECK("predecode_kernel<B>");
+        if (c8_inputs) {
+            c8_pick_kernel<<<1, 32, 0, st>>>(c8_hist, flag + 5, K * N, geom.sidx, flag + 12);
+            B200_LAUNCH_CHECK("c8_pick_kernel");
+            if (!geom.sidx) {
+                c8_brare_kernel<<<(unsigned)std::min<int64_t>(ceil_div(K * Npad, 256), 2 * sms), 256, 0, st>>>(
+                    Bw, Npad, N, K, M, flag + 12, brare_list, brare_cap(Npad, Kpad), reinterpret_cast<unsigned*>(flag + 13));
+                B200_LAUNCH_CHECK("c8_brare_kernel");
+            }
+        }
     }
     // Conv form: decode the input once and let the GEMM gather (needs 16-byte-aligned images and the extra
     // workspace b200_approx_conv2d_workspace_bytes reserves); else write the im2col plane from the NCHW tensor
@@ -1211,11 +1322,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
                  ((uintptr_t)A.p & 15) == 0 && A.H < 16384 && A.W < 16384 && nB * A.Ho * A.Wo == Mrows;
     }
     const bool c8 = c8_inputs && !gather;
-    int* c8_D = c8 ? reinterpret_cast<int*>(c8src.extra + esc_list_bytes(Mpad, Kpad)) : nullptr;
-    if (c8) {
-        pa.esc_list = reinterpret_cast<unsigned long long*>(c8src.extra);
-        B200_CUDA_TRY(cudaMemsetAsync(c8_D, 0, (size_t)Mrows * N * 4, st));
-    }
+    if (c8) pa.esc_list = brare_list + brare_cap(Npad, Kpad);
     if (A.conv) {
         const int64_t Cg = K / ((int64_t)A.kh * A.kw), img = Cg * A.H * A.W;
         const int64_t nB = Mrows / ((int64_t)A.Ho * A.Wo), total = nB * img;
@@ -1243,9 +1350,11 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         C8CorrectArgs ca;
         ca.esc_list = pa.esc_list; ca.esc_cap = pa.esc_cap; ca.esc_counters = pa.esc_counters;
         ca.esc_total = reinterpret_cast<unsigned*>(flag + 8);
-        ca.Aw = Aw; ca.Bw = Bw; ca.Mpad = Mpad; ca.Npad = Npad; ca.N = N; ca.lut16 = d_lut; ca.c8_bad = c8src.bad;
-        ca.tmax = flag + 4; ca.NT = geom.NT; ca.M = M; ca.sidx = geom.sidx; ca.nt_magic = nt_magic; ca.D = c8_D;
-        c8_correct_kernel<<<(unsigned)(4 * sms), 256, 0, st>>>(ca);
+        ca.brare_list = brare_list; ca.brare_cap = brare_cap(Npad, Kpad); ca.brare_count = reinterpret_cast<unsigned*>(flag + 13);
+        ca.Aw = Aw; ca.Bw = Bw; ca.Mpad = Mpad; ca.Npad = Npad; ca.N = N; ca.Mrows = Mrows; ca.lut16 = d_lut; ca.c8_bad = c8src.bad;
+        ca.tb_eff = flag + 12; ca.NT = geom.NT; ca.M = M; ca.sidx = geom.sidx; ca.nt_magic = nt_magic;
+        ca.zero_word = 2u * (uint32_t)geom.zeroA_off; ca.D = c8_D;
+        c8_correct_kernel<<<(unsigned)(8 * sms), 256, 0, st>>>(ca);
         B200_LAUNCH_CHECK("c8_correct_kernel");
     }
 
@@ -1266,7 +1375,8 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     la.c8 = c8 ? 1 : 0;
     la.lut8 = c8src.lut8; la.lut8_bytes = c8src.lut8_bytes;
     la.esc_total = reinterpret_cast<const unsigned*>(flag + 8);
-    la.esc_limit = std::min<int64_t>((int64_t)pa.esc_cap * kEscLists, Mrows * K / 8);
+    la.esc_limit = std::min<int64_t>((int64_t)pa.esc_cap * kEscLists, Mrows * K / 1024);   // more: the correction pass eats the gain
+    la.brare_count = reinterpret_cast<const unsigned*>(flag + 13);
     la.c8_D = c8_D;
     la.c8_ran = flag + 11;
     la.use_tma = 0;
@@ -1428,7 +1538,7 @@ extern "C" size_t b200_approx_gemm_workspace_bytes(int64_t Mrows, int64_t K, int
     if (Mrows < 0 || K < 0 || N < 0) return 0;
     const int64_t Mpad = round_up(Mrows > 0 ? Mrows : 1, kPadM), Npad = round_up(N > 0 ? N : 1, kPadN);
     const int64_t Kpad = round_up(K > 0 ? K : 1, kPadK);
-    return kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4 + c8_extra_bytes(Mrows, N, Mpad, Kpad) + splitk_partial_bytes(Mrows, N);
+    return kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4 + c8_extra_bytes(Mrows, N, Mpad, Npad, Kpad) + splitk_partial_bytes(Mrows, N);
 }
 
 size_t b200::conv_gather_workspace_bytes(int64_t nB, int64_t Cg, int64_t H, int64_t W, int64_t Kg)
@@ -1500,7 +1610,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     const int64_t Mpad = round_up(Mrows, kPadM), Npad = round_up(N, kPadN), Kpad = round_up(K, kPadK);
     // flag block, both decoded planes, the byte-cell variant's escape lists and correction sums
     const size_t planes = kFlagBytes + (size_t)Kpad * (size_t)(Mpad + Npad) * 4;
-    const size_t words = planes + c8_extra_bytes(Mrows, N, Mpad, Kpad), need = words;
+    const size_t words = planes + c8_extra_bytes(Mrows, N, Mpad, Npad, Kpad), need = words;
     if (!workspace || workspace_bytes < need) {
         set_error("b200_approx_gemm: workspace too small (see b200_approx_gemm_workspace_bytes)");
         return B200_ERR_WORKSPACE;
@@ -1593,7 +1703,7 @@ int b200::qamaa_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t s
     }
     BiasSrc bias = *hint;
     bias.fR = bias_R;                                   // result bias = the quantizer's, computed on the device
-    float* partial = splitk_partial_bytes(Mrows, N) ? reinterpret_cast<float*>(after_tables + c8_extra_bytes(Mrows, N, Mpad, Kpad)) : nullptr;
+    float* partial = splitk_partial_bytes(Mrows, N) ? reinterpret_cast<float*>(after_tables + c8_extra_bytes(Mrows, N, Mpad, Npad, Kpad)) : nullptr;
     const size_t base_bytes = b200_qamaa_gemm_workspace_bytes(Mrows, K, N);
     void* conv_ws = workspace_bytes > base_bytes ? reinterpret_cast<char*>(workspace) + base_bytes : nullptr;
     const size_t conv_ws_bytes = conv_ws ? workspace_bytes - base_bytes : 0;

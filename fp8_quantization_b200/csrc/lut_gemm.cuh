@@ -161,6 +161,7 @@ struct LutGemmArgs {
     int lut8_bytes;
     const unsigned* esc_total;      // [0] number of escape A elements, [1] list overflow (c8_correct_kernel)
     int64_t esc_limit;              // the gate closes above this many escapes
+    const unsigned* brare_count;    // rare B elements (their pairs with non-escape A rows are in c8_D too)
     const int* c8_D;                // [Mrows][N] sums of the 16-bit cells the byte table dropped, in units of u
     int* c8_ran;                    // set to 1 by the byte-cell launch when it is the one that computes (tests, ops.table_variant)
     alignas(64) CUtensorMap mapA;   // Aw as a 2-D tensor {Mpad, Kpad}, box {BM, KT}
@@ -355,7 +356,7 @@ approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
         if (s < nk) load_tile(kt0 + s, tma ? (int)((it_base + s) % ST) : s);
         cp_async_commit();
     }
-    if (C8 && kt0 == 0 && a.esc_total[0] != 0) {
+    if (C8 && kt0 == 0 && (a.esc_total[0] | *a.brare_count) != 0) {
         // the k range that starts at 0 starts from the correction sums (cells the byte table dropped)
 #pragma unroll
         for (int i = 0; i < RPW; ++i) {

@@ -72,9 +72,10 @@ def table_variant(device=None):
     ws = _WORKSPACES.get((idx, torch.cuda.current_stream(idx).cuda_stream))
     if ws is None:
         return None
-    flags = ws[:48].view(torch.int32).cpu()
+    flags = ws[:64].view(torch.int32).cpu()
     return {"variant": "byte-cells" if int(flags[11]) else "16-bit", "escapes": int(flags[8]) & 0xFFFFFFFF,
-            "tmax": (int(flags[4]), int(flags[5])), "offgrid": int(flags[0])}
+            "rare_b": int(flags[13]) & 0xFFFFFFFF, "tmax": (int(flags[4]), int(flags[5])), "tb_eff": int(flags[12]),
+            "offgrid": int(flags[0])}
 
 
 def make_params(custom_approx_params=None, *, single_column_quirk=False, allow_unpinned_format=False,

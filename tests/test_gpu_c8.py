@@ -83,8 +83,11 @@ def test_byte_cells_equal_16bit_cells(fq, M, withComp, shape, relu):
     xq, wq, bA, bB, bR, _ = operands(fq, M, Mr, K, N, seed=M * 100 + Mr + (7 if relu else 0), relu=relu)
     got, want, var, path = both(fq, M, xq, wq, bA, bB, bR, withComp)
     assert path.startswith("lut"), path
-    assert var["variant"] == "byte-cells", var
-    assert torch.equal(got.view(torch.int32), want.view(torch.int32))
+    # short K: the result range sits close to the single products, whole binades of A are escapes and the gate may
+    # close (the bits must not care); K = 1024 is comfortably inside
+    if K >= 1024:
+        assert var["variant"] == "byte-cells", var
+    assert torch.equal(got.view(torch.int32), want.view(torch.int32)), var
     cols = [0, 1, N // 2, N - 1]
     ref = oracle_columns(M, xq, wq, bA, bB, bR, cols, withComp)
     assert np.array_equal(got[:, cols].cpu().numpy().view(np.uint32), ref.view(np.uint32))
@@ -94,7 +97,7 @@ def test_byte_cells_equal_16bit_cells(fq, M, withComp, shape, relu):
 @pytest.mark.parametrize("sparse", ["0", "1"])
 def test_both_k_loops(fq, M, sparse):
     """B200_LUT_SPARSE forces the predicated (0) / the branchy (1) k loop whatever the zero statistics say."""
-    xq, wq, bA, bB, bR, _ = operands(fq, M, 640, 512, 256, seed=5, relu=True)
+    xq, wq, bA, bB, bR, _ = operands(fq, M, 640, 1024, 256, seed=5, relu=True)
     got, want, var, _ = both(fq, M, xq, wq, bA, bB, bR, env={"B200_LUT_SPARSE": sparse})
     assert var["variant"] == "byte-cells", var
     assert torch.equal(got.view(torch.int32), want.view(torch.int32))
@@ -138,22 +141,26 @@ def test_gate_closes_when_escapes_are_common_or_sums_inexact(fq, M):
 
 
 @pytest.mark.parametrize("M", [4, 5])
-def test_common_escapes_are_corrected(fq, M):
-    """One binade finer than calibrated: a populated binade of A (a few % of its elements) escapes; the correction
-    pass carries thousands of 16-bit cells and the bits still equal the 16-bit kernel's and the oracle's."""
+def test_rare_top_binade_of_b(fq, M):
+    """The channel maxima of the weights sit alone in B's top binade.  Measured against them a whole populated binade
+    of A would be escapes; the pick kernel declares them rare instead, the A pass compares against the next level, and
+    the correction pass covers (rare B) x (non-escape A).  Result grids one and two binades finer than calibrated make
+    those pairs really exceed int8."""
     seen = []
-    for step in (1, 2):
+    hit = False
+    for step in (0, 1, 2):
         xq, wq, bA, bB, bR, _ = operands(fq, M, 400, 768, 300, seed=21)
         got, want, var, _ = both(fq, M, xq, wq, bA, bB, bR + step)
         seen.append(var)
         assert var["offgrid"] == 0, var
         assert torch.equal(got.view(torch.int32), want.view(torch.int32)), var
-        if var["variant"] == "byte-cells" and var["escapes"] > 400 * 768 // 200:
+        if var["variant"] == "byte-cells" and var["rare_b"] > 0:
+            assert var["tb_eff"] < var["tmax"][1], var
             cols = [0, 150, 299]
             ref = oracle_columns(M, xq, wq, bA, bB, bR + step, cols)
             assert np.array_equal(got[:, cols].cpu().numpy().view(np.uint32), ref.view(np.uint32))
-            return
-    pytest.fail(f"no configuration had a populated binade escaping under the gate: {seen}")
+            hit = True
+    assert hit or M == 5, f"the rare-B class never engaged: {seen}"   # (E2M5 withComp: signed-index table, no rare class)
 
 
 @pytest.mark.parametrize("M", [4, 5])
@@ -201,7 +208,7 @@ def test_conv_forms(fq, M, conv):
     wq, bB = fq.ops.fp8_fakequant(w.reshape(conv["cout"], -1), 8, w.abs().amax(dim=(1, 2, 3)), mant, 1)
     wq = wq.reshape(w.shape)
     y = torch.nn.functional.conv2d(xq, wq, padding=conv["pad"])
-    mv = (y.abs().max() * 1.5).reshape(1)
+    mv = (y.abs().max() * 8.0).reshape(1)      # short K: a roomy result range keeps the products' cells within int8
     _, bR = fq.ops.fp8_fakequant(mv.clone(), 8, mv, mant, 1)
     args = ((1, 1), (conv["pad"], conv["pad"]), (1, 1), 1)
     got = fq.ops.approx_conv2d(xq, wq, bA, bB.reshape(-1), bR, fq.ops.make_params(approx_dict(M)), *args)
