@@ -297,7 +297,7 @@ def measured_traffic(M, rows):
         ent = t.get(f"approx_gemm_lut_kernel E{7 - M}M{M} {rows}x{K_DIM}x{N_DIM}")
         if isinstance(ent, dict):
             return ent.get("bytes"), ent.get("source")
-        return ent, t.get("source")
+        return ent, t.get("source") or t.get("_source")
     except Exception:
         return None, None
 

@@ -216,6 +216,7 @@ struct C8CorrectArgs {
     const uint16_t* lut16;
     const int* c8_bad;
     const int* tb_eff;         // largest non-rare tB_idx
+    const int* tmax;           // [0] largest tA_idx, [1] largest tB_idx
     int NT, M, sidx;
     uint32_t nt_magic, zero_word;
     int* D;
@@ -271,10 +272,13 @@ __global__ void __launch_bounds__(256) c8_correct_kernel(C8CorrectArgs a)
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int R8 = a.NT - 1 - *a.c8_bad;
     const int thrA = R8 - *a.tb_eff;
-    // Work items are (list entry, 32-wide chunk of the other dimension), dealt round-robin to the warps: thousands of
-    // short independent items instead of a few long serial walks (the loads are L2 / DRAM latency bound).
+    const int tmaxA = a.tmax[0];
+    if (tmaxA + a.tmax[1] <= R8) return;   // every pair lies in an all-int8 row: nothing was dropped
+    // Work items are (list entry, 128-wide chunk of the other dimension), dealt round-robin to the warps: thousands of
+    // short independent items, each with its four plane loads in flight together (the pass is latency bound).
+    constexpr int U = 4;
     // (A escape) x (every column)
-    const uint32_t nch = (uint32_t)((a.N + 31) >> 5);
+    const uint32_t nch = (uint32_t)((a.N + 32 * U - 1) / (32 * U));
     for (int l = 0; l < kEscLists; ++l) {
         const unsigned cnt = min(a.esc_counters[l], a.esc_cap);
         const int64_t items = (int64_t)cnt * nch;
@@ -283,44 +287,60 @@ __global__ void __launch_bounds__(256) c8_correct_kernel(C8CorrectArgs a)
             const uint32_t ch = (uint32_t)(it - (int64_t)e * nch);
             const unsigned long long ent = a.esc_list[(size_t)l * a.esc_cap + e];
             const int64_t m = (int64_t)(ent & 0xFFFFFFFFull), k = (int64_t)(ent >> 32);
-            const int64_t n = (int64_t)ch * 32 + lane;
-            if (n >= a.N) continue;
             const uint32_t aw = __ldg(a.Aw + k * a.Mpad + m);
-            const uint32_t bw = __ldg(a.Bw + k * a.Npad + n);
+            uint32_t bw[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t n = ((int64_t)ch * U + u) * 32 + lane;
+                bw[u] = n < a.N ? __ldg(a.Bw + k * a.Npad + n) : 0u;      // 0: row 0 of the table, all zero cells
+            }
             const uint32_t x = aw >> (a.M + 1);
             const int tA = (int)(x - (uint32_t)a.NT * __umulhi(x, a.nt_magic));
-            const uint32_t o16 = a.sidx ? bw : (bw & 0xFFFFu);
-            // plain layout: the B offset's row is tB_idx; rows up to R8 hold int8 cells only (signed-index layout:
-            // the region offset hides tB_idx -- look every pair up)
-            if (!a.sidx && tA + (int)(o16 >> (a.M + 1)) <= R8) continue;
-            const float v = __uint_as_float((uint32_t)__ldg(a.lut16 + ((aw + o16) >> 1)) << 16);
-            if (c8_fits(v)) continue;                                              // the byte table has this cell
-            const int sg = a.sidx ? 1 : (((int)bw >> 30) | 1);
-            atomicAdd(a.D + m * a.N + n, __float2int_rn(v) * sg);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t n = ((int64_t)ch * U + u) * 32 + lane;
+                const uint32_t o16 = a.sidx ? bw[u] : (bw[u] & 0xFFFFu);
+                // plain layout: the B offset's row is tB_idx; rows up to R8 hold int8 cells only (signed-index layout:
+                // the region offset hides tB_idx -- look every pair up)
+                if (n >= a.N || (!a.sidx && tA + (int)(o16 >> (a.M + 1)) <= R8)) continue;
+                const float v = __uint_as_float((uint32_t)__ldg(a.lut16 + ((aw + o16) >> 1)) << 16);
+                if (c8_fits(v)) continue;                                          // the byte table has this cell
+                const int sg = a.sidx ? 1 : (((int)bw[u] >> 30) | 1);
+                atomicAdd(a.D + m * a.N + n, __float2int_rn(v) * sg);
+            }
         }
     }
     // (rare B) x (every row that is not an A escape)
     const unsigned nb = min(nbr, a.brare_cap);
-    const uint32_t mch = (uint32_t)((a.Mrows + 31) >> 5);
+    const uint32_t mch = (uint32_t)((a.Mrows + 32 * U - 1) / (32 * U));
     const int64_t items = (int64_t)nb * mch;
     for (int64_t it = warp; it < items; it += nwarps) {
         const uint32_t e = items < ((int64_t)1 << 32) ? (uint32_t)it / mch : (uint32_t)(it / mch);
         const uint32_t ch = (uint32_t)(it - (int64_t)e * mch);
         const unsigned long long ent = a.brare_list[e];
         const int64_t n = (int64_t)(ent & 0xFFFFFFFFull), k = (int64_t)(ent >> 32);
-        const int64_t m = (int64_t)ch * 32 + lane;
-        if (m >= a.Mrows) continue;
         const uint32_t bw = __ldg(a.Bw + k * a.Npad + n);
-        const uint32_t aw = __ldg(a.Aw + k * a.Mpad + m);
-        if (aw == a.zero_word) continue;
+        if (tmaxA + (int)((bw & 0xFFFFu) >> (a.M + 1)) <= R8) continue;   // no row reaches beyond the int8 rows with this element
+        uint32_t aw[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t m = ((int64_t)ch * U + u) * 32 + lane;
+            aw[u] = m < a.Mrows ? __ldg(a.Aw + k * a.Mpad + m) : a.zero_word;
+        }
         const uint32_t o16 = bw & 0xFFFFu;
         const int tB = (int)(o16 >> (a.M + 1));
-        const uint32_t x = aw >> (a.M + 1);
-        const int tA = (int)(x - (uint32_t)a.NT * __umulhi(x, a.nt_magic));
-        if (tA > thrA || tA + tB <= R8) continue;                                  // an escape (done above) / int8 rows only
-        const float v = __uint_as_float((uint32_t)__ldg(a.lut16 + ((aw + o16) >> 1)) << 16);
-        if (c8_fits(v)) continue;
-        atomicAdd(a.D + m * a.N + n, __float2int_rn(v) * (((int)bw >> 30) | 1));
+        const int sg = ((int)bw >> 30) | 1;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (aw[u] == a.zero_word) continue;
+            const uint32_t x = aw[u] >> (a.M + 1);
+            const int tA = (int)(x - (uint32_t)a.NT * __umulhi(x, a.nt_magic));
+            if (tA > thrA || tA + tB <= R8) continue;                              // an escape (done above) / int8 rows only
+            const float v = __uint_as_float((uint32_t)__ldg(a.lut16 + ((aw[u] + o16) >> 1)) << 16);
+            if (c8_fits(v)) continue;
+            const int64_t m = ((int64_t)ch * U + u) * 32 + lane;
+            atomicAdd(a.D + m * a.N + n, __float2int_rn(v) * sg);
+        }
     }
 }
 
@@ -1352,7 +1372,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         ca.esc_total = reinterpret_cast<unsigned*>(flag + 8);
         ca.brare_list = brare_list; ca.brare_cap = brare_cap(Npad, Kpad); ca.brare_count = reinterpret_cast<unsigned*>(flag + 13);
         ca.Aw = Aw; ca.Bw = Bw; ca.Mpad = Mpad; ca.Npad = Npad; ca.N = N; ca.Mrows = Mrows; ca.lut16 = d_lut; ca.c8_bad = c8src.bad;
-        ca.tb_eff = flag + 12; ca.NT = geom.NT; ca.M = M; ca.sidx = geom.sidx; ca.nt_magic = nt_magic;
+        ca.tb_eff = flag + 12; ca.tmax = flag + 4; ca.NT = geom.NT; ca.M = M; ca.sidx = geom.sidx; ca.nt_magic = nt_magic;
         ca.zero_word = 2u * (uint32_t)geom.zeroA_off; ca.D = c8_D;
         c8_correct_kernel<<<(unsigned)(8 * sms), 256, 0, st>>>(ca);
         B200_LAUNCH_CHECK("c8_correct_kernel");
