@@ -262,9 +262,12 @@ __device__ __forceinline__ bool c8_fits(float v) { return v == rintf(v) && fabsf
 __global__ void __launch_bounds__(256) c8_correct_kernel(C8CorrectArgs a)
 {
     const unsigned nbr = *a.brare_count;
+    __shared__ unsigned s_cnt[kEscLists];   // the list counters, fetched together (not one dependent load per list)
+    if (threadIdx.x < kEscLists) s_cnt[threadIdx.x] = a.esc_counters[threadIdx.x];
+    __syncthreads();
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         unsigned tot = 0, ovf = nbr > a.brare_cap;
-        for (int l = 0; l < kEscLists; ++l) { const unsigned c = a.esc_counters[l]; tot += c; ovf |= (c > a.esc_cap); }
+        for (int l = 0; l < kEscLists; ++l) { tot += s_cnt[l]; ovf |= (s_cnt[l] > a.esc_cap); }
         a.esc_total[0] = tot;
         a.esc_total[1] = ovf;
     }
@@ -280,7 +283,8 @@ __global__ void __launch_bounds__(256) c8_correct_kernel(C8CorrectArgs a)
     // (A escape) x (every column)
     const uint32_t nch = (uint32_t)((a.N + 32 * U - 1) / (32 * U));
     for (int l = 0; l < kEscLists; ++l) {
-        const unsigned cnt = min(a.esc_counters[l], a.esc_cap);
+        const unsigned cnt = min(s_cnt[l], a.esc_cap);
+        if (cnt == 0) continue;
         const int64_t items = (int64_t)cnt * nch;
         for (int64_t it = warp; it < items; it += nwarps) {
             const uint32_t e = items < ((int64_t)1 << 32) ? (uint32_t)it / nch : (uint32_t)(it / nch);
@@ -320,13 +324,13 @@ __global__ void __launch_bounds__(256) c8_correct_kernel(C8CorrectArgs a)
         const unsigned long long ent = a.brare_list[e];
         const int64_t n = (int64_t)(ent & 0xFFFFFFFFull), k = (int64_t)(ent >> 32);
         const uint32_t bw = __ldg(a.Bw + k * a.Npad + n);
-        if (tmaxA + (int)((bw & 0xFFFFu) >> (a.M + 1)) <= R8) continue;   // no row reaches beyond the int8 rows with this element
         uint32_t aw[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
+        for (int u = 0; u < U; ++u) {   // issued together with the B word: one latency, not two
             const int64_t m = ((int64_t)ch * U + u) * 32 + lane;
             aw[u] = m < a.Mrows ? __ldg(a.Aw + k * a.Mpad + m) : a.zero_word;
         }
+        if (tmaxA + (int)((bw & 0xFFFFu) >> (a.M + 1)) <= R8) continue;   // no row reaches beyond the int8 rows with this element
         const uint32_t o16 = bw & 0xFFFFu;
         const int tB = (int)(o16 >> (a.M + 1));
         const int sg = ((int)bw >> 30) | 1;
@@ -1314,7 +1318,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
             c8_pick_kernel<<<1, 32, 0, st>>>(c8_hist, flag + 5, K * N, geom.sidx, flag + 12);
             B200_LAUNCH_CHECK("c8_pick_kernel");
             if (!geom.sidx) {
-                c8_brare_kernel<<<(unsigned)std::min<int64_t>(ceil_div(K * Npad, 256), 2 * sms), 256, 0, st>>>(
+                c8_brare_kernel<<<(unsigned)std::min<int64_t>(ceil_div(K * Npad, 256), 16 * sms), 256, 0, st>>>(
                     Bw, Npad, N, K, M, flag + 12, brare_list, brare_cap(Npad, Kpad), reinterpret_cast<unsigned*>(flag + 13));
                 B200_LAUNCH_CHECK("c8_brare_kernel");
             }
