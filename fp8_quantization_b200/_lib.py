@@ -33,8 +33,8 @@ class ApproxParams(ctypes.Structure):
         ("withComp", c_u8), ("with_approx", c_u8), ("with_s2nn2s_opt", c_u8), ("sim_hw_add_OFUF", c_u8),
         ("with_OF_opt", c_u8), ("with_UF_opt", c_u8), ("golden_clip_OF", c_u8), ("quant_btw_mult_accu", c_u8),
         ("self_check_mode", c_u8), ("single_column_quirk", c_u8), ("allow_unpinned_format", c_u8),
-        ("force_generic", c_u8), ("ofuf_mode", c_u8), ("force_table16", c_u8),
-        ("custom_table", c_vp),
+        ("force_generic", c_u8), ("ofuf_mode", c_u8), ("force_table16", c_u8), ("prepared_b_ready", c_u8),
+        ("custom_table", c_vp), ("prepared_b", c_vp), ("prepared_b_bytes", ctypes.c_uint64),
     ]
 
 
@@ -96,6 +96,7 @@ SIGNATURES = {
     "b200_qamaa_gemm_fbias": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_int,
                                       c_f32, c_int, c_vp, c_vp, c_i64, c_vp, c_sz, c_vp]),
     "b200_static_scratch_bytes": (c_sz, []),
+    "b200_approx_gemm_prepared_b_bytes": (c_sz, [c_i64, c_i64]),
     "b200_qamaa_gemm_fbias_static": (c_int, [c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp,
                                              c_int, c_f32, c_int, c_vp, c_vp, c_i64, c_vp]),
     "b200_qamaa_conv2d_workspace_bytes": (c_sz, [ctypes.POINTER(ConvGeom)]),
@@ -116,6 +117,7 @@ SIGNATURES = {
     "b200_im2col": (c_int, [c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp]),
     "b200_exact_grouped_conv2d": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp]),
     "b200_approx_conv2d_workspace_bytes": (c_sz, [ctypes.POINTER(ConvGeom)]),
+    "b200_approx_conv2d_prepared_b_bytes": (c_sz, [ctypes.POINTER(ConvGeom)]),
     "b200_approx_conv2d_fbias": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_vp, c_i64, c_vp,
                                          ctypes.POINTER(ApproxParams), c_vp, c_sz, c_vp]),
     "b200_qamaa_conv2d": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(ConvGeom), c_vp, c_int, c_f32, c_int, c_vp]),

@@ -32,12 +32,31 @@ class _ApproxMixin:
             cache[key] = ops.make_params(cap, single_column_quirk=quirk)
         return cache[key]
 
+    def _prepared_key(self):
+        """Opt-in (quantization.CACHE_FIXED_WEIGHTS): (owner, signature) under which ops keeps this layer's DECODED weight
+        plane between forwards (b200_approx_params.prepared_b).  The plane is a function of the cached quantized weights
+        and of the three exponent biases, i.e. of the ranges of the weight, activation and result quantizers; None
+        whenever any of them is not provably fixed (then every call decodes the weights, like the reference)."""
+        ent = self.__dict__.get("_b200_wcache")
+        if ent is None or not _Q.CACHE_FIXED_WEIGHTS or self.training or not getattr(self, "fix_ranges_flag", False):
+            return None
+        sig = [ent[0]]
+        for name in ("activation_quantizer", "res_quantizer"):
+            q = getattr(getattr(self, name, None), "quantizer", None)
+            if q is None or not hasattr(q, "_range_version") or q._bias_version != q._range_version or q.custom_bias is None:
+                return None
+            mv = q.maxval
+            sig.append((q._range_version, mv.data_ptr(), None if mv.is_inference() else mv._version, float(q.mantissa_bits),
+                        q.sign_bits))
+        return (id(self), tuple(sig))
+
     def approx_multiply(self, x, y, x_bias, y_bias, res_bias):
         if y.shape[1] != 1:
             if self.approx_flag:
                 return ops.approx_matmul(x, y, x_bias, y_bias, res_bias, _ApproxMixin._params(self, False),
                                          act_quant=self.__dict__.pop("_b200_act_quant", None),
-                                         epilogue=self.__dict__.pop("_b200_ep_args", None))
+                                         epilogue=self.__dict__.pop("_b200_ep_args", None),
+                                         prepared=_ApproxMixin._prepared_key(self))
             if self.quantize_after_mult_and_add:
                 q = self.res_quantizer.quantizer
                 return ops.qamaa_matmul(x, y, q.n_bits, q.maxval, q.mantissa_bits, q.sign_bits, x_bias=x_bias,
@@ -116,7 +135,8 @@ class _ConvMixin(_ApproxMixin):
             out = ops.approx_conv2d(x, weight, self.get_acts_fp_bias(), self.get_weights_fp_bias(),
                                     self.get_res_fp_bias(), _ApproxMixin._params(self, Ng == 1), self.stride, self.padding,
                                     self.dilation, self.groups, act_quant=self.__dict__.pop("_b200_act_quant", None),
-                                    epilogue=dict(ep, bias=bias) if ep is not None else None)
+                                    epilogue=dict(ep, bias=bias) if ep is not None else None,
+                                    prepared=_ApproxMixin._prepared_key(self))
             if ep is not None:
                 return out
         elif use_approx and self.quantize_after_mult_and_add and Ng != 1:

@@ -1252,6 +1252,27 @@ static size_t c8_extra_bytes(int64_t Mrows, int64_t N, int64_t Mpad, int64_t Npa
 {
     return 256 + c8_D_bytes(Mrows, N) + (size_t)brare_cap(Npad, Kpad) * 8 + esc_list_bytes(Mpad, Kpad);
 }
+// Prepared right operand (b200_approx_params.prepared_b): [256 B: image of the flag words the B passes produce]
+// [decoded plane Bw[Kpad][Npad]][rare-B list].  fill: the B passes write into it; ready: they are skipped and the
+// flag words restored.
+struct PreparedB {
+    uint8_t* base = nullptr;
+    bool ready = false;
+};
+static size_t prepared_b_bytes(int64_t K, int64_t N)
+{
+    if (K <= 0 || N <= 0) return 0;
+    const int64_t Npad = round_up(N, kPadN), Kpad = round_up(K, kPadK);
+    return 256 + (size_t)Kpad * Npad * 4 + (size_t)brare_cap(Npad, Kpad) * 8;
+}
+// flag words of the B passes: [0] off-grid (OR-ed), [5] largest tB_idx, [12] largest non-rare tB_idx, [13] rare count
+__global__ void b_meta_kernel(int* __restrict__ flag, int* __restrict__ meta, int save)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (save) { meta[0] = flag[0]; meta[1] = flag[5]; meta[2] = flag[12]; meta[3] = flag[13]; }
+    else      { if (meta[0]) flag[0] = 1; flag[5] = meta[1]; flag[12] = meta[2]; flag[13] = meta[3]; }
+}
+
 struct C8Src {
     const int8_t* lut8 = nullptr;
     int lut8_bytes = 0;
@@ -1266,8 +1287,10 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
                         int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const LutGeom& geom,
                         const uint16_t* d_lut, int lut_bytes, int* flag, uint32_t* Aw, uint32_t* Bw, int64_t Mpad,
                         int64_t Npad, int64_t Kpad, const QamaaOp* qop, float* partial, void* conv_ws, size_t conv_ws_bytes,
-                        cudaStream_t st, const Epilogue& ep = Epilogue{}, const C8Src& c8src = C8Src{})
+                        cudaStream_t st, const Epilogue& ep = Epilogue{}, const C8Src& c8src = C8Src{},
+                        const PreparedB& prep = PreparedB{})
 {
+    if (prep.base) Bw = reinterpret_cast<uint32_t*>(prep.base + 256);   // the decoded right operand lives with the caller
     const int M = geom.M;
     static PerDeviceOnce once;
     int sms = 0;
@@ -1291,20 +1314,25 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     const bool c8_inputs = c8src.lut8 && c8src.extra && c8src.bad && !geom.v5 && Mpad < ((int64_t)1 << 31) &&
                            Mpad * Kpad / 8 < ((int64_t)1 << 31);
     PredecodeArgs pa;
-    pa.tmax = (partial || c8_inputs) ? flag + 4 : nullptr;
+    pa.tmax = (partial || c8_inputs || prep.base) ? flag + 4 : nullptr;
     pa.src = nullptr; pa.s_row = 0; pa.s_k = 1; pa.asrc = A; pa.dst = Aw; pa.rows = Mrows; pa.K = K; pa.Rpad = Mpad;
     pa.Kpad = Kpad; pa.M = M; pa.bias = bias; pa.offgrid = flag;
     pa.esc_list = nullptr; pa.esc_cap = esc_list_cap(Mpad, Kpad); pa.esc_counters = reinterpret_cast<unsigned*>(flag + 32);
     pa.c8_bad = c8src.bad; pa.tmaxB = flag + 12; pa.hist = nullptr;
     unsigned* c8_hist = reinterpret_cast<unsigned*>(c8src.extra);
     int* c8_D = c8_inputs ? reinterpret_cast<int*>(c8src.extra + 256) : nullptr;
-    unsigned long long* brare_list = c8_inputs ? reinterpret_cast<unsigned long long*>(c8src.extra + 256 + c8_D_bytes(Mrows, N)) : nullptr;
+    unsigned long long* brare_list =
+        prep.base ? reinterpret_cast<unsigned long long*>(prep.base + 256 + (size_t)Kpad * Npad * 4)
+                  : (c8_inputs ? reinterpret_cast<unsigned long long*>(c8src.extra + 256 + c8_D_bytes(Mrows, N)) : nullptr);
     if (c8_inputs)   // histogram + correction sums start at zero
         B200_CUDA_TRY(cudaMemsetAsync(c8src.extra, 0, 256 + (size_t)Mrows * N * 4, st));
     // v5 flavour: a zero operand is an ordinary code (its product is not zero), so there is nothing to skip
     pa.zero_count = geom.v5 ? nullptr : reinterpret_cast<unsigned long long*>(flag + 2);
     // B first: the A pass of the byte-cell variant compares against the largest tB_idx
-    {
+    if (prep.base && prep.ready) {
+        b_meta_kernel<<<1, 32, 0, st>>>(flag, reinterpret_cast<int*>(prep.base), 0);
+        B200_LAUNCH_CHECK("b_meta_kernel(restore)");
+    } else {
         PredecodeArgs pb = pa;
         pb.zero_count = nullptr;
         pb.tmax = pa.tmax ? flag + 5 : nullptr;
@@ -1322,6 +1350,10 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
                     Bw, Npad, N, K, M, flag + 12, brare_list, brare_cap(Npad, Kpad), reinterpret_cast<unsigned*>(flag + 13));
                 B200_LAUNCH_CHECK("c8_brare_kernel");
             }
+        }
+        if (prep.base) {
+            b_meta_kernel<<<1, 32, 0, st>>>(flag, reinterpret_cast<int*>(prep.base), 1);
+            B200_LAUNCH_CHECK("b_meta_kernel(save)");
         }
     }
     // Conv form: decode the input once and let the GEMM gather (needs 16-byte-aligned images and the extra
@@ -1346,7 +1378,8 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
                  ((uintptr_t)A.p & 15) == 0 && A.H < 16384 && A.W < 16384 && nB * A.Ho * A.Wo == Mrows;
     }
     const bool c8 = c8_inputs && !gather;
-    if (c8) pa.esc_list = brare_list + brare_cap(Npad, Kpad);
+    if (c8)   // the escape lists follow the workspace's own rare-B list room (unused when the caller keeps B prepared)
+        pa.esc_list = reinterpret_cast<unsigned long long*>(c8src.extra + 256 + c8_D_bytes(Mrows, N)) + brare_cap(Npad, Kpad);
     if (A.conv) {
         const int64_t Cg = K / ((int64_t)A.kh * A.kw), img = Cg * A.H * A.W;
         const int64_t nB = Mrows / ((int64_t)A.Ho * A.Wo), total = nB * img;
@@ -1557,6 +1590,8 @@ extern "C" int b200_set_autotune(int on)
 
 extern "C" uint64_t b200_autotune_runs(void) { return g_tune_runs.load(std::memory_order_relaxed); }
 
+extern "C" size_t b200_approx_gemm_prepared_b_bytes(int64_t K, int64_t N) { return prepared_b_bytes(K, N); }
+
 extern "C" size_t b200_approx_gemm_workspace_bytes(int64_t Mrows, int64_t K, int64_t N)
 {
     if (Mrows < 0 || K < 0 || N < 0) return 0;
@@ -1657,8 +1692,17 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     // whatever the caller provides beyond the GEMM-form workspace holds the decoded conv plane
     void* conv_ws = workspace_bytes > words + pbytes ? reinterpret_cast<char*>(workspace) + words + pbytes : nullptr;
     const size_t conv_ws_bytes = conv_ws ? workspace_bytes - words - pbytes : 0;
+    PreparedB prep;
+    if (p->prepared_b) {
+        if (p->prepared_b_bytes < prepared_b_bytes(K, N) || ((uintptr_t)p->prepared_b & 15) != 0) {
+            set_error("b200_approx_gemm: prepared_b too small or misaligned (see b200_approx_gemm_prepared_b_bytes)");
+            return B200_ERR_WORKSPACE;
+        }
+        prep.base = reinterpret_cast<uint8_t*>(p->prepared_b);
+        prep.ready = p->prepared_b_ready != 0;
+    }
     if (int rc = run_lut_gemm(A, B, sb_k, sb_n, C, ldc, Mrows, K, N, bias, lut->geom, lut->d_lut, lut->lut_bytes, flag,
-                              Aw, Bw, Mpad, Npad, Kpad, nullptr, partial, conv_ws, conv_ws_bytes, st, ep, c8src))
+                              Aw, Bw, Mpad, Npad, Kpad, nullptr, partial, conv_ws, conv_ws_bytes, st, ep, c8src, prep))
         return rc;
     // runs only if the predecode found an off-grid operand
     pair_gemm_kernel<ApproxPairOp><<<ggrid, 256, 0, st>>>(A, bsrc, C, ldc, Mrows, K, N, op, flag, 1, ep);

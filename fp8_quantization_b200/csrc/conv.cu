@@ -596,6 +596,13 @@ extern "C" int b200_exact_grouped_conv2d(const float* x, const float* w, float* 
     return B200_OK;
 }
 
+extern "C" size_t b200_approx_conv2d_prepared_b_bytes(const b200_conv_geom* g)
+{
+    ConvDims d;
+    if (!g || conv_dims(g, &d) != B200_OK || d.Ng == 1) return 0;
+    return (size_t)round_up((int64_t)b200_approx_gemm_prepared_b_bytes(d.Kg, d.Ng), 256) * (size_t)g->groups;
+}
+
 extern "C" size_t b200_approx_conv2d_workspace_bytes(const b200_conv_geom* g)
 {
     ConvDims d;
@@ -654,7 +661,16 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
     if (d.Ng != 1) {
         b200_approx_params pp = *p;
         pp.single_column_quirk = 0;
+        const size_t prep_chunk = (size_t)round_up((int64_t)b200_approx_gemm_prepared_b_bytes(d.Kg, d.Ng), 256);
+        if (p->prepared_b && p->prepared_b_bytes < prep_chunk * (size_t)g->groups) {
+            set_error("b200_approx_conv2d: prepared_b too small (see b200_approx_conv2d_prepared_b_bytes)");
+            return B200_ERR_WORKSPACE;
+        }
         for (int grp = 0; grp < g->groups; ++grp) {
+            if (p->prepared_b) {   // one chunk per group
+                pp.prepared_b = reinterpret_cast<char*>(p->prepared_b) + prep_chunk * (size_t)grp;
+                pp.prepared_b_bytes = prep_chunk;
+            }
             BiasSrc b{dflt, dflt, bA_dev, bR_dev, nullptr, bB_dev ? bB_dev + (int64_t)grp * d.Ng * bB_stride : nullptr,
                       bB_stride};
             const float* wg = w + (int64_t)grp * d.Ng * d.Kg;

@@ -10,8 +10,9 @@
 #include "tables.h"
 
 #include <cstddef>
-static_assert(sizeof(b200_approx_params) == 40 && offsetof(b200_approx_params, ofuf_mode) == 24 &&
-                  offsetof(b200_approx_params, custom_table) == 32,
+static_assert(sizeof(b200_approx_params) == 56 && offsetof(b200_approx_params, ofuf_mode) == 24 &&
+                  offsetof(b200_approx_params, prepared_b_ready) == 26 && offsetof(b200_approx_params, custom_table) == 32 &&
+                  offsetof(b200_approx_params, prepared_b) == 40 && offsetof(b200_approx_params, prepared_b_bytes) == 48,
               "b200_approx_params layout is part of the C ABI (fp8_quantization_b200/_lib.py mirrors it)");
 
 namespace b200 {

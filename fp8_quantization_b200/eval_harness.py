@@ -163,7 +163,8 @@ class GraphedForward:
         # (FPQuantizer.forward assigns a fresh custom_bias on every call, fp8_quantizer.py:244)
         for m in self.model.modules():
             cached += [t for t in (getattr(m, "custom_bias", None), getattr(m, "maxval", None)) if torch.is_tensor(t)]
-        return dict(ops._WORKSPACES), cached, dict(ops._BPLANES)
+        # ... and the decoded weight planes ops keeps per layer (approx_matmul / approx_conv2d `prepared`)
+        return dict(ops._WORKSPACES), cached, dict(ops._BPLANES), {k: v[1] for k, v in ops._PREPARED.items()}
 
 
 _N_CLASSES = {}

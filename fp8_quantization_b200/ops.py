@@ -64,6 +64,35 @@ def _workspace(device, nbytes):
     return ws
 
 
+_PREPARED = {}   # owner -> [signature, uint8 tensor, filled]
+
+
+def clear_prepared():
+    """Drops every cached decoded weight plane (see approx_matmul's `prepared`)."""
+    _PREPARED.clear()
+
+
+def _prepared_begin(params, prepared, nbytes, device):
+    """Points `params` at the owner's prepared-B buffer (allocated / invalidated by signature); returns its record."""
+    params.prepared_b, params.prepared_b_bytes, params.prepared_b_ready = None, 0, 0
+    if prepared is None or nbytes == 0:
+        return None
+    owner, sig = prepared
+    ent = _PREPARED.get(owner)
+    if ent is None or ent[0] != sig or ent[1].numel() < nbytes or ent[1].device != device:
+        ent = [sig, torch.empty(int(nbytes), dtype=torch.uint8, device=device), False]
+        _PREPARED[owner] = ent
+    params.prepared_b, params.prepared_b_bytes = ent[1].data_ptr(), ent[1].numel()
+    params.prepared_b_ready = 1 if ent[2] else 0
+    return ent
+
+
+def _prepared_end(params, ent, ok):
+    params.prepared_b, params.prepared_b_bytes, params.prepared_b_ready = None, 0, 0
+    if ent is not None and ok:
+        ent[2] = True
+
+
 def table_variant(device=None):
     """Which variant of the table GEMM computed the last approx / qamaa call on this (device, stream): "byte-cells"
     (int8 cells in shared memory, integer accumulators; picked on the device for mant_width >= 4 when every sum is
@@ -163,7 +192,8 @@ def _epilogue_struct(epilogue, n_channels, device):
     return ep, keep
 
 
-def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out=None, act_quant=None, epilogue=None):
+def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out=None, act_quant=None, epilogue=None,
+                  prepared=None):
     """C = approx_multiply(x [Mrows,K], y [K,N]) in ONE launch sequence.
 
     Biases, two forms:
@@ -201,6 +231,9 @@ def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out
     int_path = isinstance(x_bias, int) and isinstance(res_bias, int)
     if (act_quant is not None or epilogue is not None) and int_path:
         raise ValueError("the fused input quantizer / epilogue need the device-bias form of the call")
+    # `prepared` = (owner, signature), opt-in: the decoded weight plane is kept between calls with the same signature
+    pent = _prepared_begin(params, prepared, lib.b200_approx_gemm_prepared_b_bytes(K, N) if prepared is not None else 0,
+                           x.device)
     with torch.cuda.device(x.device):
         if int_path:
             if isinstance(y_bias, int):
@@ -248,6 +281,7 @@ def approx_matmul(x, y, x_bias, y_bias, res_bias, params, custom_table=None, out
                                                 ctypes.byref(params), _ptr(ws), ws.numel(), _stream())
     if keep is not None:
         params.custom_table = None
+    _prepared_end(params, pent, rc == 0)
     _lib.check(rc)
     return out
 
@@ -419,7 +453,7 @@ def exact_grouped_conv2d(x, weight, stride, padding, dilation, groups):
 
 
 def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, dilation, groups, act_quant=None,
-                  epilogue=None):
+                  epilogue=None, prepared=None):
     """im2col + group loop + approx_multiply of QCustomBNConv2dTorch.run_forward
     (approx/approx_calculation.py:846-906) in one C-ABI call.  Returns [B*Ho*Wo, C_out] fp32.
     Biases are the fake-quantizers' fp32 tensors (or None -> 2^(E-1)); read on the device.
@@ -447,6 +481,8 @@ def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, 
         sB = fb.stride(0)
     nbytes = lib.b200_approx_conv2d_workspace_bytes(ctypes.byref(g))
     ws = _workspace(x.device, nbytes) if nbytes else None
+    pent = _prepared_begin(params, prepared,
+                           lib.b200_approx_conv2d_prepared_b_bytes(ctypes.byref(g)) if prepared is not None else 0, x.device)
     with torch.cuda.device(x.device):
         if epilogue is not None:
             aq, alive = _act_quant_struct(act_quant, x.device) if act_quant is not None else (None, None)
@@ -464,6 +500,7 @@ def approx_conv2d(x, weight, x_bias, w_bias, res_bias, params, stride, padding, 
             rc = lib.b200_approx_conv2d_fbias(_ptr(x), _ptr(weight), _ptr(out), ctypes.byref(g), _ptr(fa), _ptr(fb), sB,
                                               _ptr(fr), ctypes.byref(params), _ptr(ws), ws.numel() if ws is not None else 0,
                                               _stream())
+    _prepared_end(params, pent, rc == 0)
     _lib.check(rc)
     return out
 

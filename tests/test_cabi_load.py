@@ -61,10 +61,13 @@ def test_param_struct_layout():
     import fp8_quantization_b200 as pkg
     p = pkg.ops.make_params(dict(expo_width=3, mant_width=4, dnsmp_factor=5, withComp=False, golden_clip_OF=True))
     assert (p.expo_width, p.mant_width, p.dnsmp_factor, p.withComp, p.golden_clip_OF) == (3, 4, 5, 0, 1)
-    # 3 x int32, 13 x uint8 (the last one: ofuf_mode), padding, one pointer -- static_assert'ed in csrc/runtime.cu
-    assert ctypes.sizeof(pkg._lib.ApproxParams) == 40
+    # 3 x int32, 15 x uint8 (ofuf_mode, force_table16, prepared_b_ready last), padding, custom_table, prepared_b,
+    # prepared_b_bytes -- static_assert'ed in csrc/runtime.cu
+    assert ctypes.sizeof(pkg._lib.ApproxParams) == 56
     assert pkg._lib.ApproxParams.ofuf_mode.offset == 24
+    assert pkg._lib.ApproxParams.prepared_b_ready.offset == 26
     assert pkg._lib.ApproxParams.custom_table.offset == 32
+    assert pkg._lib.ApproxParams.prepared_b.offset == 40 and pkg._lib.ApproxParams.prepared_b_bytes.offset == 48
     assert pkg.ops.make_params(dict(ofuf_mode="v5")).ofuf_mode == 1 and pkg.ops.make_params({}).ofuf_mode == 0
 
 

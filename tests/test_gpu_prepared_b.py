@@ -1,0 +1,160 @@
+"""Prepared right operand (b200_approx_params.prepared_b; opt-in through quantization.enable_fusions / CACHE_FIXED_WEIGHTS):
+the table path keeps a layer's DECODED weight plane -- and what the byte-cell variant derives from it -- in a caller-owned
+buffer between forwards instead of re-decoding the weights in every call, which is what the reference's per-forward
+weight quantizer + per-column loop amount to (hijacker.py:117-123, approx_calculation.py:946-971).  Same bits with the
+buffer being filled, being reused, and without it; a changed signature (weights, ranges) refills it."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def fq():
+    import fp8_quantization_b200 as pkg
+    pkg._lib.load()
+    return pkg
+
+
+def approx_dict(M):
+    return dict(expo_width=7 - M, mant_width=M, dnsmp_factor=3, withComp=True, with_approx=True,
+                with_s2nn2s_opt=True, quant_btw_mult_accu=True)
+
+
+def operands(fq, M, Mr, K, N, seed):
+    g = torch.Generator().manual_seed(seed)
+    x = (torch.randn(Mr, K, generator=g) * 0.5).cuda()
+    w = (torch.randn(N, K, generator=g) * 0.02).cuda()
+    mant = torch.tensor([float(M)])
+    xq, bA = fq.ops.fp8_fakequant(x, 8, x.abs().max().reshape(1), mant, 1)
+    wq, bB = fq.ops.fp8_fakequant(w, 8, w.abs().amax(dim=1), mant, 1)
+    mv = ((xq[:256] @ wq.t()).abs().max() * 1.5).reshape(1)
+    _, bR = fq.ops.fp8_fakequant(mv.clone(), 8, mv, mant, 1)
+    return xq, wq, bA, bB, bR
+
+
+@pytest.mark.parametrize("M", [3, 4, 5])
+@pytest.mark.parametrize("shape", [(300, 520, 200), (640, 1024, 384)])
+def test_gemm_fill_reuse_and_refill(fq, M, shape):
+    Mr, K, N = shape
+    ops = fq.ops
+    ops.clear_prepared()
+    xq, wq, bA, bB, bR = operands(fq, M, Mr, K, N, seed=31 + M)
+    p = ops.make_params(approx_dict(M))
+    want = ops.approx_matmul(xq, wq.t(), bA, bB, bR, p)
+    l0 = ops.kernel_launches()
+    ops.approx_matmul(xq, wq.t(), bA, bB, bR, p)
+    plain_launches = ops.kernel_launches() - l0
+    owner = ("test", M, shape)
+    outs, launches = [], []
+    for _ in range(3):                                    # fill, reuse, reuse
+        l0 = ops.kernel_launches()
+        outs.append(ops.approx_matmul(xq, wq.t(), bA, bB, bR, p, prepared=(owner, "v1")))
+        launches.append(ops.kernel_launches() - l0)
+    for o in outs:
+        assert torch.equal(o.view(torch.int32), want.view(torch.int32))
+    # reuse: the B decode pass (for M >= 4 also the rare-level pick and list kernels) is replaced by one tiny restore
+    assert launches[1] == launches[2] <= plain_launches <= launches[0], (launches, plain_launches)
+    if M >= 4:
+        assert launches[1] < plain_launches, (launches, plain_launches)
+    assert ops._PREPARED[owner][2] is True
+    # other activations against the kept plane
+    x2 = xq.flip(0).contiguous()
+    assert torch.equal(ops.approx_matmul(x2, wq.t(), bA, bB, bR, p, prepared=(owner, "v1")).view(torch.int32),
+                       ops.approx_matmul(x2, wq.t(), bA, bB, bR, p).view(torch.int32))
+    # new weights under a new signature: the buffer is refilled
+    w2 = wq.roll(7, dims=0).contiguous()
+    b2 = bB.reshape(-1).roll(7).reshape(bB.shape).contiguous()
+    got = ops.approx_matmul(xq, w2.t(), bA, b2, bR, p, prepared=(owner, "v2"))
+    assert torch.equal(got.view(torch.int32), ops.approx_matmul(xq, w2.t(), bA, b2, bR, p).view(torch.int32))
+    assert p.prepared_b is None and p.prepared_b_ready == 0      # the shared params struct is left clean
+
+
+@pytest.mark.parametrize("M", [3, 4])
+@pytest.mark.parametrize("conv", [dict(cin=16, cout=32, k=3, groups=4, hw=10), dict(cin=32, cout=320, k=3, groups=1, hw=9),
+                                  dict(cin=64, cout=96, k=1, groups=1, hw=14)])
+def test_conv_groups(fq, M, conv):
+    ops = fq.ops
+    ops.clear_prepared()
+    g = torch.Generator().manual_seed(41)
+    x = (torch.randn(4, conv["cin"], conv["hw"], conv["hw"], generator=g) * 0.5).cuda()
+    w = (torch.randn(conv["cout"], conv["cin"] // conv["groups"], conv["k"], conv["k"], generator=g) * 0.05).cuda()
+    mant = torch.tensor([float(M)])
+    xq, bA = ops.fp8_fakequant(x, 8, x.abs().max().reshape(1), mant, 1)
+    wq, bB = ops.fp8_fakequant(w.reshape(conv["cout"], -1), 8, w.abs().amax(dim=(1, 2, 3)), mant, 1)
+    wq = wq.reshape(w.shape)
+    y = torch.nn.functional.conv2d(xq, wq, padding=conv["k"] // 2, groups=conv["groups"])
+    mv = (y.abs().max() * 4.0).reshape(1)
+    _, bR = ops.fp8_fakequant(mv.clone(), 8, mv, mant, 1)
+    args = ((1, 1), (conv["k"] // 2, conv["k"] // 2), (1, 1), conv["groups"])
+    p = ops.make_params(approx_dict(M))
+    want = ops.approx_conv2d(xq, wq, bA, bB.reshape(-1), bR, p, *args)
+    for _ in range(3):
+        got = ops.approx_conv2d(xq, wq, bA, bB.reshape(-1), bR, p, *args, prepared=(("conv", M), "v1"))
+        assert torch.equal(got.view(torch.int32), want.view(torch.int32))
+
+
+@pytest.mark.parametrize("kind", ["linear", "conv3x3", "conv_grouped", "conv_dw"])
+@pytest.mark.parametrize("M", [3, 4])
+def test_layers_keep_their_decoded_weights(fq, kind, M):
+    """Through the operator classes: with enable_fusions() the second and later eval forwards reuse the plane; an
+    in-place weight update (version counter) or new ranges invalidate it."""
+    from fp8_quantization_b200 import quantization as Q
+    from fp8_quantization_b200.approx_calculation import QCustomBNConv2dTorch, QCustomLinearTorch
+    torch.manual_seed(6)
+    fq.ops.clear_prepared()
+    kw = dict(method="fp_quantizer", act_method="fp_quantizer", weight_range_method="current_minmax",
+              act_range_method="allminmax", n_bits=8, n_bits_act=8, per_channel_weights=True, quantize_input=True,
+              fp8_kwargs=dict(mantissa_bits=M, set_maxval=True), custom_approx_params=approx_dict(M),
+              run_method=dict(approx_flag=True, quantize_after_mult_and_add=False, res_quantizer_flag=True,
+                              original_quantize_res=False))
+    if kind == "linear":
+        layer = QCustomLinearTorch(256, 72, bias=True, **kw)
+        x = torch.randn(150, 256)
+    else:
+        cin, cout, k, groups, hw = {"conv3x3": (16, 32, 3, 1, 14), "conv_grouped": (16, 32, 3, 4, 10),
+                                    "conv_dw": (16, 16, 3, 16, 10)}[kind]
+        layer = QCustomBNConv2dTorch(cin, cout, k, padding=k // 2, groups=groups, bias=False, activation=torch.nn.ReLU(), **kw)
+        x = torch.relu(torch.randn(4, cin, hw, hw))
+    layer = layer.cuda().eval()
+    x = x.cuda()
+    seen = []
+    orig_mm, orig_conv = fq.ops.approx_matmul, fq.ops.approx_conv2d
+
+    def spy(fn):
+        def inner(*a, **k):
+            seen.append(k.get("prepared"))
+            return fn(*a, **k)
+        return inner
+    fq.ops.approx_matmul, fq.ops.approx_conv2d = spy(orig_mm), spy(orig_conv)
+    prev = Q.enable_fusions(False)
+    try:
+        with torch.inference_mode():
+            layer.quantized()
+            layer.estimate_ranges()
+            layer(x)
+            layer.fix_ranges()
+            want = layer(x).clone()
+            assert all(s is None for s in seen)
+            Q.enable_fusions(True)
+            outs = [layer(x).clone() for _ in range(3)]
+            for o in outs:
+                assert torch.equal(o.view(torch.int32), want.view(torch.int32))
+            keys = [s for s in seen if s is not None]
+            assert len(keys) >= 2 and keys[-1] == keys[-2], keys        # later forwards present the same signature
+            if kind != "conv_dw":
+                assert fq.ops._PREPARED[id(layer)][2] is True
+        # in-place weight update: the signature changes, the plane is rebuilt, the output follows the new weights
+        with torch.no_grad():
+            layer.weight.mul_(0.5)
+        with torch.inference_mode():
+            got = layer(x).clone()
+            Q.enable_fusions(False)
+            ref = layer(x).clone()
+        assert torch.equal(got.view(torch.int32), ref.view(torch.int32))
+        assert not torch.equal(got, want)
+    finally:
+        fq.ops.approx_matmul, fq.ops.approx_conv2d = orig_mm, orig_conv
+        Q.enable_fusions(False, input_quant=prev[0], weight_cache=prev[1], gemm_epilogue=prev[2])
+        fq.ops.clear_prepared()
