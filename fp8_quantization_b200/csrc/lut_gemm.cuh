@@ -271,6 +271,12 @@ approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
         crow = a.cp.Pw + b * a.cp.img_words + (int64_t)ch0 * a.cp.W + cw0;
     };
     if (CONV) conv_row_setup();
+    uint32_t greg[CONV ? KT * BM / NTHR : 1];   // CONV: this thread's gathered A words of the tile in flight
+    auto gather_store = [&](int stage) {
+        uint32_t* dst = As + (stage * KT + tid / BM) * BM + tid % BM;
+#pragma unroll
+        for (int j = 0; j < KT * BM / NTHR; ++j) dst[j * (NTHR / BM) * BM] = greg[j];
+    };
     auto load_tile = [&](int kt, int stage) {
         if (tma) {
             if (tid == 0) {
@@ -285,15 +291,17 @@ approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
         }
         const uint32_t* gb = a.Bw + (int64_t)kt * KT * a.Npad + n0;
         if (CONV) {
+            // The gathered A words travel through registers: a 4-byte cp.async costs one shared-memory wavefront PER
+            // LANE (0.5 wavefronts per lookup for 64-column tiles, measured), a warp-wide STS of 32 consecutive words
+            // one.  The loads are issued here; gather_store() writes the stage at the end of the k iteration.
             const int2* ki = a.cp.kinfo + kt * KT + tid / BM;
-            const uint32_t dst = As_u + 4u * (uint32_t)((stage * KT + tid / BM) * BM + tid % BM);
 #pragma unroll
             for (int j = 0; j < KT * BM / NTHR; ++j) {
                 const int2 q = __ldg(ki + j * (NTHR / BM));
                 const int h = ch0 + (int)(short)(q.y & 0xFFFF), w = cw0 + (q.y >> 16);
                 const bool ok = (unsigned)h < (unsigned)a.cp.H && (unsigned)w < (unsigned)a.cp.W;
-                const uint32_t* src = ok ? crow + q.x : a.cp.zero_src;
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + 4u * (uint32_t)(j * (NTHR / BM) * BM)), "l"(src) : "memory");
+                greg[j] = a.zero_word;
+                if (ok) greg[j] = __ldg(crow + q.x);
             }
         } else {
             const uint32_t* ga = a.Aw + (int64_t)kt * KT * a.Mpad + m0;
@@ -354,6 +362,7 @@ approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
 #pragma unroll
     for (int s = 0; s < ST - 1; ++s) {
         if (s < nk) load_tile(kt0 + s, tma ? (int)((it_base + s) % ST) : s);
+        if (CONV && s < nk) gather_store(s);
         cp_async_commit();
     }
     if (C8 && kt0 == 0 && (a.esc_total[0] | *a.brare_count) != 0) {
@@ -476,6 +485,9 @@ approx_gemm_lut_kernel(const __grid_constant__ LutGemmArgs a)
 #pragma unroll
                     for (int j = 0; j < CPL; ++j) macc = fmaxf(macc, fabsf(acc[i][j]));
             }
+            // CONV: the tile gathered at the top of this iteration goes to its stage (last read in iteration kt - 1,
+            // behind this iteration's barrier; next read two barriers from now)
+            if (CONV && kt + ST - 1 < nk) gather_store((kt + ST - 1) % ST);
             if (tma) {   // this warp is done with the stage
                 __syncwarp();
                 if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_u + 8u * (ST + stage)) : "memory");

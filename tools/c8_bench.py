@@ -33,11 +33,13 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--zeros", type=float, default=0.0, help="fraction of activations set to zero (post-ReLU tensors)")
     ap.add_argument("--autotune", type=int, default=1)
+    ap.add_argument("--mants", type=int, nargs="+", default=[4, 5])
+    ap.add_argument("--shape", type=int, nargs=3, action="append", help="rows K N (repeatable); default: 4096^3 and ViT-B shapes")
     a = ap.parse_args()
     ops.set_autotune(bool(a.autotune))
     dev = torch.device("cuda", 0)
-    shapes = [(4096, 4096, 4096), (3152, 768, 768), (3152, 768, 3072), (3152, 3072, 768)]
-    for M in (4, 5):
+    shapes = [tuple(t) for t in a.shape] if a.shape else [(4096, 4096, 4096), (3152, 768, 768), (3152, 768, 3072), (3152, 3072, 768)]
+    for M in a.mants:
         for (rows, K, N) in shapes:
             g = torch.Generator().manual_seed(10)
             x = torch.randn(rows, K, generator=g) * 0.5
