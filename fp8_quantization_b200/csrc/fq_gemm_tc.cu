@@ -260,7 +260,8 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     } else if (warp >= 4) {
         // ===== epilogue: TMEM -> registers -> (+bias) -> global fp32 =====
         const int w = warp - 4;                       // == warp % 4: the TMEM lane quarter this warp may read
-        const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+        const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0) &&
+                            ((reinterpret_cast<uintptr_t>(bias) & 15) == 0);   // bias is read as float4 beside C
         const float omx = oq.maxval ? __ldg(oq.maxval) : 0.0f, ofb = oq.maxval ? __ldg(oq.bias) : 0.0f;   // result quantizer
         const bool ofast = oq.maxval && fp8_ste_fast_ok(ofb);
         int ti = 0;
@@ -461,7 +462,8 @@ fq_gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
     } else if (warp >= 4) {
         // ===== epilogue (both CTAs): own 128 rows x 256 columns, TMEM -> registers -> (+bias) -> global fp32 =====
         const int w = warp - 4;
-        const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+        const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0) &&
+                            ((reinterpret_cast<uintptr_t>(bias) & 15) == 0);   // bias is read as float4 beside C
         const float omx = oq.maxval ? __ldg(oq.maxval) : 0.0f, ofb = oq.maxval ? __ldg(oq.bias) : 0.0f;   // result quantizer
         const bool ofast = oq.maxval && fp8_ste_fast_ok(ofb);
         int ti = 0;

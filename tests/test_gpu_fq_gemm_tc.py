@@ -68,6 +68,21 @@ def test_fq_gemm_tc_exact_on_integers(fq):
         assert torch.equal(got, want), (Mr, K, N, float((got - want).abs().max()))
 
 
+def test_bias_view_that_is_not_16_byte_aligned(fq):
+    """A sliced bias (data_ptr 4 bytes off a 16-byte boundary) must not be read with 128-bit loads: the epilogue falls
+    back to scalar bias loads (the TMA-store and the vector-store paths both require an aligned bias)."""
+    g = torch.Generator().manual_seed(4)
+    for (Mr, K, N) in [(128, 64, 256), (300, 96, 512)]:
+        a = torch.randint(-8, 9, (Mr, K), generator=g).float().cuda()
+        b = torch.randint(-8, 9, (K, N), generator=g).float().cuda()
+        store = torch.randint(-8, 9, (N + 4,), generator=g).float().cuda()
+        bias = store[1:N + 1]
+        assert bias.data_ptr() % 16 == 4
+        got = fq.ops.fq_matmul(a, b, bias=bias)
+        want = (a.double() @ b.double() + bias.double()).float()
+        assert torch.equal(got, want)
+
+
 def test_fq_gemm_tc_offgrid_falls_back_on_device(fq):
     g = torch.Generator().manual_seed(4)
     a = torch.randn(70, 96, generator=g).cuda()            # full fp32 mantissas: not exact in bf16
