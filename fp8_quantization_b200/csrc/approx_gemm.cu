@@ -1611,6 +1611,7 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
                            int64_t Mrows, int64_t K, int64_t N, const BiasSrc& bias, const b200_approx_params* p,
                            void* workspace, size_t workspace_bytes, void* stream, const Epilogue* epp)
 {
+    NvtxRange nvtx_range("b200_approx_gemm");
     const Epilogue ep = epp ? *epp : Epilogue{};
     if (int rc = check_device()) return rc;
     if (!p || Mrows < 0 || K < 0 || N < 0) { set_error("b200_approx_gemm: bad argument"); return B200_ERR_ARGUMENT; }
@@ -1728,6 +1729,7 @@ int b200::qamaa_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t s
                           float mantissa_bits, int sign_bits, const BiasSrc* hint, void* workspace,
                           size_t workspace_bytes, void* stream)
 {
+    NvtxRange nvtx_range("b200_qamaa_gemm");
     cudaStream_t st = (cudaStream_t)stream;
     QamaaOp op;
     op.maxval_dev = maxval_dev;

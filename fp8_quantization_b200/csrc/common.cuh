@@ -63,6 +63,13 @@ struct PerDeviceOnce {
     }
 };
 
+// NVTX range around an entry point (tracing): header-only nvtx3, a no-op unless a tool (nsys, ncu
+// --nvtx) is attached; the ranges name the C-ABI call a kernel belongs to in a timeline.
+struct NvtxRange {
+    explicit NvtxRange(const char* name);
+    ~NvtxRange();
+};
+
 inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 inline int64_t round_up(int64_t a, int64_t b) { return ceil_div(a, b) * b; }
 

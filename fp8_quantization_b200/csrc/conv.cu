@@ -646,6 +646,7 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
                               const b200_act_quant* aq, void* workspace, size_t workspace_bytes, void* stream,
                               const b200_epilogue* epp)
 {
+    NvtxRange nvtx_range("b200_approx_conv2d");
     if (int rc = check_device()) return rc;
     ConvDims d;
     if (int rc = conv_dims(g, &d)) return rc;

@@ -256,6 +256,7 @@ extern "C" int b200_bn_act(const float* x, int64_t sb, int64_t sc, int64_t sp, f
                            const float* mean, const float* var, const float* gamma, const float* beta, float eps, int act,
                            void* stream)
 {
+    NvtxRange nvtx_range("b200_bn_act");
     if (int rc = check_device()) return rc;
     if (B < 0 || C < 1 || HW < 0 || act < 0 || act > 2) { set_error("b200_bn_act: bad argument"); return B200_ERR_ARGUMENT; }
     if (B == 0 || HW == 0) return B200_OK;
@@ -288,6 +289,7 @@ extern "C" int b200_fp8_fakequant(const float* x, float* y, int64_t n, const flo
                                   int64_t inner, int n_bits, float mantissa_bits, int sign_bits, float* bias_out,
                                   void* stream)
 {
+    NvtxRange nvtx_range("b200_fp8_fakequant");
     if (int rc = check_device()) return rc;
     if (n < 0 || n_channels < 1 || !maxval || !bias_out || (n > 0 && (!x || !y))) {
         set_error("b200_fp8_fakequant: bad argument");

@@ -730,6 +730,7 @@ static int fq_gemm_tc_impl(const float* A, int64_t lda, const float* B, int64_t 
                            size_t workspace_bytes, void* stream, const b200_act_quant* aq_in = nullptr,
                            const b200_act_quant* aq_out = nullptr)
 {
+    NvtxRange nvtx_range("b200_fq_gemm_tc");
     if (int rc = check_device()) return rc;
     if (Mrows < 0 || K < 0 || N < 0) { set_error("b200_fq_gemm_tc: bad argument"); return B200_ERR_ARGUMENT; }
     if (Mrows == 0 || N == 0) return B200_OK;

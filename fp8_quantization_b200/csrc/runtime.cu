@@ -15,7 +15,12 @@ static_assert(sizeof(b200_approx_params) == 56 && offsetof(b200_approx_params, o
                   offsetof(b200_approx_params, prepared_b) == 40 && offsetof(b200_approx_params, prepared_b_bytes) == 48,
               "b200_approx_params layout is part of the C ABI (fp8_quantization_b200/_lib.py mirrors it)");
 
+#include <nvtx3/nvToolsExt.h>
+
 namespace b200 {
+
+NvtxRange::NvtxRange(const char* name) { nvtxRangePushA(name); }
+NvtxRange::~NvtxRange() { nvtxRangePop(); }
 
 std::atomic<uint64_t> g_launches{0};
 static std::mutex g_err_mu;
