@@ -89,7 +89,8 @@ def _prepared_begin(params, prepared, nbytes, device):
 
 def _prepared_end(params, ent, ok):
     params.prepared_b, params.prepared_b_bytes, params.prepared_b_ready = None, 0, 0
-    if ent is not None and ok:
+    # (a fill that was only CAPTURED into a CUDA graph has not run yet: the buffer counts as filled only after an eager call)
+    if ent is not None and ok and not torch.cuda.is_current_stream_capturing():
         ent[2] = True
 
 
