@@ -374,11 +374,20 @@ __global__ void __launch_bounds__(256, 4) approx_dw_plane_lut_kernel(DwPlaneLutA
 #pragma unroll
         for (int k = 0; k < KG; ++k) kreg[k] = kinfo[k];
     }
+    // Tiles in group-tile-major order: a CTA's consecutive tiles (stride gridDim.x) mostly share their 32 groups, whose
+    // decoded weight parts and epilogue constants then stay in shared memory (no decode, no barrier per tile).
+    const bool ep_nchw = d.ep.on && d.ep.HW > 0;
+    Epilogue::Col* ecol = reinterpret_cast<Epilogue::Col*>(&tile[0][0]);
+    int last_gt = -1;
     for (int64_t t = blockIdx.x; t < d.n_row_tiles * d.n_grp_tiles; t += gridDim.x) {
         int64_t rt;
         int gt;
-        if (small) { rt = (uint32_t)t / (uint32_t)d.n_grp_tiles; gt = (int)((uint32_t)t - (uint32_t)rt * (uint32_t)d.n_grp_tiles); }
-        else       { rt = t / d.n_grp_tiles; gt = (int)(t - rt * d.n_grp_tiles); }
+        if (small) { gt = (int)((uint32_t)t / (uint32_t)d.n_row_tiles); rt = (uint32_t)t - (uint32_t)gt * (uint32_t)d.n_row_tiles; }
+        else       { gt = (int)(t / d.n_row_tiles); rt = t - (int64_t)gt * d.n_row_tiles; }
+        if (gt == last_gt) {
+            if (!ep_nchw) __syncthreads();        // the previous tile's readers of tile[] are done
+        } else {
+        last_gt = gt;
         __syncthreads();                          // previous tile's wpart / tile readers are done; first pass: lut, kinfo
         for (int i = threadIdx.x; i < 32 * Kg; i += 256) {
             const int gl = i / Kg, k = i - gl * Kg, grp = gt * 32 + gl;
@@ -401,13 +410,12 @@ __global__ void __launch_bounds__(256, 4) approx_dw_plane_lut_kernel(DwPlaneLutA
             }
             wpart[i] = wp;
         }
-        const bool ep_nchw = d.ep.on && d.ep.HW > 0;
-        Epilogue::Col* ecol = reinterpret_cast<Epilogue::Col*>(&tile[0][0]);
         if (ep_nchw && threadIdx.x < 32) {
             const int grp = gt * 32 + threadIdx.x;
             ecol[threadIdx.x] = d.ep.column(grp < d.groups ? grp : d.groups - 1);
         }
         __syncthreads();
+        }
         const int64_t m = rt * 32 + tx;
         int wo, ho;
         int64_t b;
@@ -449,7 +457,8 @@ __global__ void __launch_bounds__(256, 4) approx_dw_plane_lut_kernel(DwPlaneLutA
                         const uint32_t addr = min(aw[k] + wrow[k], zero_addr);   // skip words overshoot: zero cell
                         unsigned short e;
                         asm("ld.shared.u16 %0, [%1];" : "=h"(e) : "r"(addr));
-                        acc += __uint_as_float((uint32_t)e << 16);
+                        // acc += bf16 cell: one FHFMA (cell * 1.0 is exact, the add rounds once) instead of SHL + FADD
+                        asm("fma.rn.f32.bf16 %0, %1, %2, %0;" : "+f"(acc) : "h"(e), "h"((unsigned short)0x3F80));
                     }
                 } else {
                     for (int k = 0; k < Kg; ++k) {
