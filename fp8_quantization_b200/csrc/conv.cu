@@ -331,6 +331,7 @@ __global__ void __launch_bounds__(256) dw_plane_kernel(DwPlaneArgs d)
     if (off) *d.flag = 1;
 }
 
+constexpr int kDwPlaneRows = 256;   // output pixels per tile of approx_dw_plane_lut_kernel (one per thread)
 struct DwPlaneLutArgs {
     DwLutArgs l;             // a.p is unused here; everything else as in approx_dw_lut_kernel
     const uint32_t* plane;   // [B][C][H][W] words written by dw_plane_kernel
@@ -358,7 +359,6 @@ __global__ void __launch_bounds__(256, 4) approx_dw_plane_lut_kernel(DwPlaneLutA
         kinfo[k] = make_int2((c * s.H + ky * s.dh) * s.W + kx * s.dw, (ky * s.dh) | ((kx * s.dw) << 16));
     }
     const uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(dw_smem);
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const LutGeom& g = d.g;
     const int M = g.M;
     const int bA = d.bias.A(), bR = d.bias.R();
@@ -384,9 +384,7 @@ __global__ void __launch_bounds__(256, 4) approx_dw_plane_lut_kernel(DwPlaneLutA
         int gt;
         if (small) { gt = (int)((uint32_t)t / (uint32_t)d.n_row_tiles); rt = (uint32_t)t - (uint32_t)gt * (uint32_t)d.n_row_tiles; }
         else       { gt = (int)(t / d.n_row_tiles); rt = t - (int64_t)gt * d.n_row_tiles; }
-        if (gt == last_gt) {
-            if (!ep_nchw) __syncthreads();        // the previous tile's readers of tile[] are done
-        } else {
+        if (gt != last_gt) {
         last_gt = gt;
         __syncthreads();                          // previous tile's wpart / tile readers are done; first pass: lut, kinfo
         for (int i = threadIdx.x; i < 32 * Kg; i += 256) {
@@ -416,7 +414,10 @@ __global__ void __launch_bounds__(256, 4) approx_dw_plane_lut_kernel(DwPlaneLutA
         }
         __syncthreads();
         }
-        const int64_t m = rt * 32 + tx;
+        // one thread = one output pixel (consecutive pixels across the 256 threads), all 32 groups of the tile in turn:
+        // the pixel's coordinates and tap mask are computed once per 288 MACs
+        const int64_t m = rt * kDwPlaneRows + threadIdx.x;
+        if (m >= d.rows) continue;
         int wo, ho;
         int64_t b;
         if (small) {
@@ -440,53 +441,38 @@ __global__ void __launch_bounds__(256, 4) approx_dw_plane_lut_kernel(DwPlaneLutA
                 inb |= ((unsigned)h < (unsigned)s.H && (unsigned)wi < (unsigned)s.W) ? (1u << k) : 0u;
             }
         }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int gl = ty + 8 * i;
+        const int ngl = min(32, d.groups - gt * 32);
+#pragma unroll 4
+        for (int gl = 0; gl < ngl; ++gl) {
             const int grp = gt * 32 + gl;
             float acc = 0.0f;
-            if (grp < d.groups && m < d.rows) {
-                const uint32_t* p0 = pa.plane + ((b * s.C + (int64_t)grp * d.Cg) * s.H + h0) * (int64_t)s.W + w0;
-                const uint32_t* wrow = wpart + gl * Kg;
-                if (KG > 0) {
-                    uint32_t aw[KG > 0 ? KG : 1];
+            const uint32_t* p0 = pa.plane + ((b * s.C + (int64_t)grp * d.Cg) * s.H + h0) * (int64_t)s.W + w0;
+            const uint32_t* wrow = wpart + gl * Kg;      // the same address in every lane: broadcast loads
+            if (KG > 0) {
+                uint32_t aw[KG > 0 ? KG : 1];
 #pragma unroll
-                    for (int k = 0; k < KG; ++k) aw[k] = ((inb >> k) & 1u) ? __ldg(p0 + kreg[k].x) : kDwPlaneSkip;
+                for (int k = 0; k < KG; ++k) aw[k] = ((inb >> k) & 1u) ? __ldg(p0 + kreg[k].x) : kDwPlaneSkip;
 #pragma unroll
-                    for (int k = 0; k < KG; ++k) {
-                        const uint32_t addr = min(aw[k] + wrow[k], zero_addr);   // skip words overshoot: zero cell
-                        unsigned short e;
-                        asm("ld.shared.u16 %0, [%1];" : "=h"(e) : "r"(addr));
-                        // acc += bf16 cell: one FHFMA (cell * 1.0 is exact, the add rounds once) instead of SHL + FADD
-                        asm("fma.rn.f32.bf16 %0, %1, %2, %0;" : "+f"(acc) : "h"(e), "h"((unsigned short)0x3F80));
-                    }
-                } else {
-                    for (int k = 0; k < Kg; ++k) {
-                        const int2 ki = kinfo[k];
-                        const int h = h0 + (ki.y & 0xFFFF), wi = w0 + (ki.y >> 16);
-                        if ((unsigned)h >= (unsigned)s.H || (unsigned)wi >= (unsigned)s.W) continue;   // F.pad zeros (:727)
-                        const uint32_t addr = min(__ldg(p0 + ki.x) + wrow[k], zero_addr);
-                        unsigned short e;
-                        asm("ld.shared.u16 %0, [%1];" : "=h"(e) : "r"(addr));
-                        acc += __uint_as_float((uint32_t)e << 16);
-                    }
+                for (int k = 0; k < KG; ++k) {
+                    const uint32_t addr = min(aw[k] + wrow[k], zero_addr);   // skip words overshoot: zero cell
+                    unsigned short e;
+                    asm("ld.shared.u16 %0, [%1];" : "=h"(e) : "r"(addr));
+                    // acc += bf16 cell: one FHFMA (cell * 1.0 is exact, the add rounds once) instead of SHL + FADD
+                    asm("fma.rn.f32.bf16 %0, %1, %2, %0;" : "+f"(acc) : "h"(e), "h"((unsigned short)0x3F80));
+                }
+            } else {
+                for (int k = 0; k < Kg; ++k) {
+                    const int2 ki = kinfo[k];
+                    const int h = h0 + (ki.y & 0xFFFF), wi = w0 + (ki.y >> 16);
+                    if ((unsigned)h >= (unsigned)s.H || (unsigned)wi >= (unsigned)s.W) continue;   // F.pad zeros (:727)
+                    const uint32_t addr = min(__ldg(p0 + ki.x) + wrow[k], zero_addr);
+                    unsigned short e;
+                    asm("ld.shared.u16 %0, [%1];" : "=h"(e) : "r"(addr));
+                    acc += __uint_as_float((uint32_t)e << 16);
                 }
             }
-            if (ep_nchw) {
-                if (grp < d.groups && m < d.rows)
-                    d.out[((b * d.ep.Ctot + d.ep.c0 + grp) * (int64_t)s.Ho + ho) * s.Wo + wo] = d.ep.apply(acc * unit, ecol[gl]);
-            } else {
-                tile[gl][tx] = acc * unit;
-            }
-        }
-        if (ep_nchw) continue;
-        __syncthreads();
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int ml = ty + 8 * i;
-            const int64_t mm = rt * 32 + ml;
-            const int grp = gt * 32 + tx;
-            if (mm < d.rows && grp < d.groups) d.ep.store(d.out, d.groups, mm, grp, tile[tx][ml]);
+            if (ep_nchw) d.out[((b * d.ep.Ctot + d.ep.c0 + grp) * (int64_t)s.Ho + ho) * s.Wo + wo] = d.ep.apply(acc * unit, ecol[gl]);
+            else         d.ep.store(d.out, d.groups, m, grp, acc * unit);
         }
     }
     if (off) *d.flag = 1;
@@ -775,8 +761,10 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
                 dw_plane_kernel<<<pblocks, 256, 0, st>>>(dp);
                 B200_LAUNCH_CHECK("dw_plane_kernel");
                 DwPlaneLutArgs pl{la, dp.plane};
-                if (d.Kg == 9) approx_dw_plane_lut_kernel<9><<<blocks, 256, smem, st>>>(pl);
-                else           approx_dw_plane_lut_kernel<0><<<blocks, 256, smem, st>>>(pl);
+                pl.l.n_row_tiles = ceil_div(d.rows, kDwPlaneRows);
+                const unsigned pblk = (unsigned)std::min<int64_t>(pl.l.n_row_tiles * la.n_grp_tiles, (int64_t)sms * per_sm);
+                if (d.Kg == 9) approx_dw_plane_lut_kernel<9><<<pblk, 256, smem, st>>>(pl);
+                else           approx_dw_plane_lut_kernel<0><<<pblk, 256, smem, st>>>(pl);
                 B200_LAUNCH_CHECK("approx_dw_plane_lut_kernel");
                 approx_dw_kernel<<<grid, 256, 0, st>>>(a, la.flag, 1);
                 B200_LAUNCH_CHECK("approx_dw_kernel(conditional)");
