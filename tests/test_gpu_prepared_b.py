@@ -158,3 +158,18 @@ def test_layers_keep_their_decoded_weights(fq, kind, M):
         fq.ops.approx_matmul, fq.ops.approx_conv2d = orig_mm, orig_conv
         Q.enable_fusions(False, input_quant=prev[0], weight_cache=prev[1], gemm_epilogue=prev[2])
         fq.ops.clear_prepared()
+
+
+@pytest.mark.parametrize("M", [3, 4])
+def test_v5_mode_with_prepared_weights(fq, M):
+    """The opt-in v5 overflow / underflow flavour decodes its operands into code exponents; its plane is kept the same way."""
+    ops = fq.ops
+    ops.clear_prepared()
+    xq, wq, bA, bB, bR = operands(fq, M, 300, 520, 200, seed=51)
+    cap = dict(approx_dict(M), sim_hw_add_OFUF=True, with_OF_opt=True, with_UF_opt=True)
+    p = ops.make_params(cap, ofuf_mode=1)
+    want = ops.approx_matmul(xq, wq.t(), bA, bB, bR, p)
+    assert ops.last_path() == "lut-v5"
+    for _ in range(3):
+        got = ops.approx_matmul(xq, wq.t(), bA, bB, bR, p, prepared=(("v5", M), "v1"))
+        assert torch.equal(got.view(torch.int32), want.view(torch.int32))
