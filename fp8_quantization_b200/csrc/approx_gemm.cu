@@ -785,17 +785,19 @@ __global__ void __launch_bounds__(256) streamk_fixup_kernel(const float* __restr
     const float unit = pow2f_i(1 - bias.R() - M);
     if (qamaa) qop.begin();
     const int64_t m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
+    // the tile's segments, once per thread (64-bit divisions do not belong in the element loop): CTA g0 reached the
+    // tile in a LATER segment of its range (slot 1) unless its range starts exactly here; the CTAs after it start
+    // inside the tile (slot 0)
+    int64_t g1 = g0 + 1;
+    while (g1 < G && start(g1) < u_hi) ++g1;
+    const int64_t tile_elems = (int64_t)BM * BN;
+    const float* P0 = P + (g0 * 2 + (start(g0) >= u_lo ? 0 : 1)) * tile_elems;
+    const int bn_shift = 31 - __clz(BN);          // BN is 64 or 128
     for (int e = threadIdx.x; e < BM * BN; e += 256) {
-        const int r = e / BN, c = e - r * BN;
+        const int r = e >> bn_shift, c = e & (BN - 1);
         if (m0 + r >= Mrows || n0 + c >= N) continue;
-        float s = 0.0f;
-        bool have = false;
-        for (int64_t g = g0; g < G && start(g) < u_hi; ++g) {
-            const int slot = start(g) >= u_lo ? 0 : 1;
-            const float v = P[(g * 2 + slot) * (int64_t)(BM * BN) + e];
-            s = have ? s + v : v;
-            have = true;
-        }
+        float s = P0[e];
+        for (int64_t g = g0 + 1; g < g1; ++g) s += P[g * 2 * tile_elems + e];     // k order
         s *= unit;
         if (qamaa) s = qop.quant(s);
         ep.store(C, ldc, m0 + r, n0 + c, s);
