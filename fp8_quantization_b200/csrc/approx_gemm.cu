@@ -243,7 +243,8 @@ __global__ void __launch_bounds__(256) c8_brare_kernel(const uint32_t* __restric
         bool rare = false;
         int64_t k = 0, n = 0;
         if (i < total) {
-            k = i / Npad; n = i - k * Npad;
+            if (total < ((int64_t)1 << 32)) { k = (uint32_t)i / (uint32_t)Npad; n = (uint32_t)i - (uint32_t)k * (uint32_t)Npad; }
+            else                            { k = i / Npad; n = i - k * Npad; }
             rare = n < N && (int)((__ldg(Bw + i) & 0xFFFFu) >> (M + 1)) > thr;
         }
         const unsigned m = __ballot_sync(0xFFFFFFFFu, rare);
@@ -814,13 +815,18 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
     const float unit = pow2f_i(1 - bias.R() - M);
     if (qamaa) qop.begin();
     const int64_t total = Mrows * N, stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    // (row, column) of the element advance incrementally: one 64-bit division per thread, none per element
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t m = i / N, n = i - m * N;
+    const int64_t dm = stride / N, dn = stride - dm * N;
+    for (; i < total; i += stride) {
         float s = P[i];
         for (int z = 1; z < splits; ++z) s += P[(int64_t)z * total + i];
         s *= unit;
         if (qamaa) s = qop.quant(s);
-        const int64_t m = i / N;
-        ep.store(C, ldc, m, i - m * N, s);
+        ep.store(C, ldc, m, n, s);
+        m += dm; n += dn;
+        if (n >= N) { n -= N; ++m; }
     }
 }
 
