@@ -77,12 +77,15 @@ fp8_fakequant_channel_kernel(const float* __restrict__ x, float* __restrict__ y,
     Mf = fminf(fmaxf(Mf, 1.0f), (float)(n_bits - sign_bits));
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const bool small = n < ((int64_t)1 << 32) && inner < ((int64_t)1 << 32) && n_channels < ((int64_t)1 << 32);
     if (vec_ok) {   // inner % 4 == 0: a float4 never straddles two channels
         const int64_t n4 = n >> 2;
         const float4* x4 = reinterpret_cast<const float4*>(x);
         float4* y4 = reinterpret_cast<float4*>(y);
         for (int64_t i = tid; i < n4; i += stride) {
-            const int64_t c = ((i << 2) / inner) % n_channels;
+            // (32-bit division where the tensor allows it: a 64-bit one costs more than the quantizer itself)
+            const int64_t c = small ? (int64_t)((((uint32_t)i << 2) / (uint32_t)inner) % (uint32_t)n_channels)
+                                    : ((i << 2) / inner) % n_channels;
             const float mx = __ldg(maxval + c), b = __ldg(bias + c);
             float4 v = __ldcs(x4 + i);
             if (fp8_ste_fast_ok(b)) {      // exponent-field form: no log2f, no division (pair_math.cuh)
@@ -101,7 +104,7 @@ fp8_fakequant_channel_kernel(const float* __restrict__ x, float* __restrict__ y,
         }
     } else {
         for (int64_t i = tid; i < n; i += stride) {
-            const int64_t c = (i / inner) % n_channels;
+            const int64_t c = small ? (int64_t)(((uint32_t)i / (uint32_t)inner) % (uint32_t)n_channels) : (i / inner) % n_channels;
             y[i] = fp8_ste_quant(x[i], __ldg(maxval + c), __ldg(bias + c), Mf, sign_bits);
         }
     }
