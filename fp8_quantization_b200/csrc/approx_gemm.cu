@@ -794,7 +794,8 @@ __global__ void __launch_bounds__(256) streamk_fixup_kernel(const float* __restr
     const int64_t tile_elems = (int64_t)BM * BN;
     const float* P0 = P + (g0 * 2 + (start(g0) >= u_lo ? 0 : 1)) * tile_elems;
     const int bn_shift = 31 - __clz(BN);          // BN is 64 or 128
-    for (int e = threadIdx.x; e < BM * BN; e += 256) {
+    // gridDim.y CTAs share a tile (a lone CTA per tile walked 64 latency-bound iterations per thread)
+    for (int e = blockIdx.y * 256 + threadIdx.x; e < BM * BN; e += 256 * gridDim.y) {
         const int r = e >> bn_shift, c = e & (BN - 1);
         if (m0 + r >= Mrows || n0 + c >= N) continue;
         float s = P0[e];
@@ -1477,7 +1478,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
                 cfg->sk_kernel8()<<<dim3((unsigned)G), 32 * cfg->warps, cfg->smem(l.lut8_bytes), st>>>(l);
                 B200_LAUNCH_CHECK("approx_gemm_lut_kernel(stream-K, byte cells)");
             }
-            streamk_fixup_kernel<<<(unsigned)tiles, 256, 0, st>>>(partial, (int)G, tiles, (int)tgrid.y, (int)nk_all, cfg->BM(),
+            streamk_fixup_kernel<<<dim3((unsigned)tiles, 16), 256, 0, st>>>(partial, (int)G, tiles, (int)tgrid.y, (int)nk_all, cfg->BM(),
                                                                   cfg->BN(), C, ldc, Mrows, N, bias, M, l.qamaa, l.qop,
                                                                   flag + 6, flag, ep);
             B200_LAUNCH_CHECK("streamk_fixup_kernel");
@@ -1494,7 +1495,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
                 splitk_reduce_nchw_kernel<<<dim3((unsigned)ceil_div(Mrows, 32), (unsigned)ceil_div(N, 32)), 256, 0, st>>>(
                     partial, splits, C, Mrows, N, bias, M, l.qamaa, l.qop, flag + 6, flag, ep);
             else
-                splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(Mrows * N, 256), 4 * sms), 256, 0, st>>>(
+                splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(Mrows * N, 256), 64 * sms), 256, 0, st>>>(
                     partial, splits, C, ldc, Mrows, N, bias, M, l.qamaa, l.qop, flag + 6, flag, ep);
             B200_LAUNCH_CHECK("splitk_reduce_kernel");
         }
