@@ -195,6 +195,7 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 {
     if (*inexact != 0) return;   // an operand does not fit bf16 exactly: the fp32 kernel takes over
     using L = TcSmem<BN, ST>;
+    constexpr int TMEM_COLS = 2 * BN <= 256 ? 256 : 512;   // two accumulator stages; allocations are powers of two
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::BARS);
@@ -214,7 +215,7 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {   // one warp allocates two accumulator stages of BN fp32 columns each
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(tmem_slot)), "r"((uint32_t)(2 * BN)) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(tmem_slot)), "r"((uint32_t)TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
@@ -268,13 +269,16 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++ti) {
             const int m0 = (tile % m_blocks) * TC_BM, n0 = (tile / m_blocks) * BN;
             const int as = ti & 1;
-            // The tile's bias goes to registers (lane L: the tile's columns L * BN/32 ...) BEFORE the wait for the
+            // The tile's bias goes to registers (lane L: the tile's columns L * PER ...) BEFORE the wait for the
             // accumulator: a global load per 32-column chunk sat on the epilogue's critical path (+20 us on
             // 4096 x 768 x 3072 with a bias); the chunks hand the values round by shuffle.
-            float breg[BN / 32];
+            // (PER values per lane over a 32 * PER-wide window from n0; PER is 4 or 8 so that 32 % PER == 0 and the
+            // register a chunk column needs does not depend on the chunk -- a 192-wide tile uses the 256-wide window)
+            constexpr int PER = BN <= 128 ? 4 : 8;
+            float breg[PER];
 #pragma unroll
-            for (int i = 0; i < BN / 32; ++i) {
-                const int64_t nn = (int64_t)n0 + lane * (BN / 32) + i;
+            for (int i = 0; i < PER; ++i) {
+                const int64_t nn = (int64_t)n0 + lane * PER + i;
                 breg[i] = (bias && tma_store && nn < N) ? __ldg(bias + nn) : 0.0f;
             }
             mbar_wait(tmem_full + as, (ti >> 1) & 1);
@@ -288,7 +292,7 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 const int64_t n = (int64_t)n0 + c * 32;
                 if (tma_store) {
                     if (n < N && (int64_t)m0 + w * 32 < Mrows)
-                        epi_store_chunk_tma<BN / 32>(&mapC, smem + L::EPI + (w * 2 + (c & 1)) * 4096, v, lane, bias != nullptr, breg, c, n, N,
+                        epi_store_chunk_tma<PER>(&mapC, smem + L::EPI + (w * 2 + (c & 1)) * 4096, v, lane, bias != nullptr, breg, c, n, N,
                                             m0 + w * 32, oq, omx, ofb, ofast);
                 } else if (row < Mrows && n < N) {
                     if (vec_ok && n + 32 <= N) {
@@ -326,7 +330,7 @@ fq_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     tc_fence_before();
     __syncthreads();
     if (warp == 2)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)(2 * BN)) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)TMEM_COLS) : "memory");
 }
 
 // ---- CTA-pair variant (cta_group::2) ------------------------------------------------------------------------------
@@ -480,13 +484,16 @@ fq_gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
         for (int tile = pair; tile < n_tiles; tile += n_pairs, ++ti) {
             const int m0 = (tile % m_blocks) * (2 * TC_BM) + (int)rank * TC_BM, n0 = (tile / m_blocks) * BN;
             const int as = ti & 1;
-            // The tile's bias goes to registers (lane L: the tile's columns L * BN/32 ...) BEFORE the wait for the
+            // The tile's bias goes to registers (lane L: the tile's columns L * PER ...) BEFORE the wait for the
             // accumulator: a global load per 32-column chunk sat on the epilogue's critical path (+20 us on
             // 4096 x 768 x 3072 with a bias); the chunks hand the values round by shuffle.
-            float breg[BN / 32];
+            // (PER values per lane over a 32 * PER-wide window from n0; PER is 4 or 8 so that 32 % PER == 0 and the
+            // register a chunk column needs does not depend on the chunk -- a 192-wide tile uses the 256-wide window)
+            constexpr int PER = BN <= 128 ? 4 : 8;
+            float breg[PER];
 #pragma unroll
-            for (int i = 0; i < BN / 32; ++i) {
-                const int64_t nn = (int64_t)n0 + lane * (BN / 32) + i;
+            for (int i = 0; i < PER; ++i) {
+                const int64_t nn = (int64_t)n0 + lane * PER + i;
                 breg[i] = (bias && tma_store && nn < N) ? __ldg(bias + nn) : 0.0f;
             }
             mbar_wait(tmem_full + as, (ti >> 1) & 1);
@@ -500,7 +507,7 @@ fq_gemm_tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
                 const int64_t n = (int64_t)n0 + c * 32;
                 if (tma_store) {
                     if (n < N && (int64_t)m0 + w * 32 < Mrows)
-                        epi_store_chunk_tma<BN / 32>(&mapC, smem + L::EPI + (w * 2 + (c & 1)) * 4096, v, lane, bias != nullptr, breg, c, n, N,
+                        epi_store_chunk_tma<PER>(&mapC, smem + L::EPI + (w * 2 + (c & 1)) * 4096, v, lane, bias != nullptr, breg, c, n, N,
                                             m0 + w * 32, oq, omx, ofb, ofast);
                 } else if (row < Mrows && n < N) {
                     if (vec_ok && n + 32 <= N) {
@@ -799,6 +806,7 @@ static int fq_gemm_tc_impl(const float* A, int64_t lda, const float* B, int64_t 
     if (int rc = once.get(&sms, []() -> int {
             B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<256, 4>::TOTAL));
             B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<128, 4>::TOTAL));
+            B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc_kernel<192, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<192, 4>::TOTAL));
             B200_CUDA_TRY(cudaFuncSetAttribute(fq_gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Tc2Smem::TOTAL));
             return B200_OK;
         }))
@@ -823,18 +831,25 @@ static int fq_gemm_tc_impl(const float* A, int64_t lda, const float* B, int64_t 
         const int pairs = std::min(n_tiles, sms / 2);
         fq_gemm_tc2_kernel<<<(unsigned)(2 * pairs), TC_THREADS, Tc2Smem::TOTAL, st>>>(
             mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag, oq);
-    } else if (N > 128) {
-        constexpr int BN = 256, ST = 4;
-        if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
-        const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
-        fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
-            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag, oq);
     } else {
-        constexpr int BN = 128, ST = 4;
-        if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
-        const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
-        fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
-            mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag, oq);
+        // single-CTA tiles 128 x BN: the BN that needs the fewest (waves x tile width) -- 4096 x 768 has 96 tiles of
+        // 128 x 256 on 148 SMs but 128 tiles of 128 x 192
+        auto waves_cost = [&](int bn) { return ceil_div(ceil_div(Mrows, TC_BM) * ceil_div(N, bn), sms) * bn; };
+        int bn = N > 128 ? 256 : 128;
+        if (N > 128 && waves_cost(192) < waves_cost(bn)) bn = 192;
+        if (N > 128 && waves_cost(128) < waves_cost(bn)) bn = 128;
+        if (const char* be = getenv("B200_TC_BN")) { const int v = atoi(be); if (v == 128 || v == 192 || v == 256) bn = v; }   // experiments
+        auto launch1 = [&](auto bn_c) -> int {
+            constexpr int BN = decltype(bn_c)::value, ST = 4;
+            if (int rc = make_map(enc, &mapB, Bh, N, Kp, BN)) return rc;
+            const int m_blocks = (int)ceil_div(Mrows, TC_BM), n_tiles = m_blocks * (int)ceil_div(N, BN);
+            fq_gemm_tc_kernel<BN, ST><<<(unsigned)std::min(n_tiles, sms), TC_THREADS, TcSmem<BN, ST>::TOTAL, st>>>(
+                mapA, mapB, mapC, tma_store, C, ldc, Mrows, N, nkb, m_blocks, n_tiles, bias_dev, flag, oq);
+            return B200_OK;
+        };
+        int rc = bn == 256 ? launch1(std::integral_constant<int, 256>{})
+                           : (bn == 192 ? launch1(std::integral_constant<int, 192>{}) : launch1(std::integral_constant<int, 128>{}));
+        if (rc) return rc;
     }
     B200_LAUNCH_CHECK("fq_gemm_tc_kernel");
     // runs only if the convert pass found an operand that is not exact in bf16

@@ -83,6 +83,23 @@ def test_bias_view_that_is_not_16_byte_aligned(fq):
         assert torch.equal(got, want)
 
 
+@pytest.mark.parametrize("bn", ["128", "192", "256"])
+def test_tile_widths_return_the_same_bits(fq, bn, monkeypatch):
+    """128 x {128, 192, 256} tiles of the single-CTA kernel (chosen by SM fill; B200_TC_BN forces one): same k order per
+    output element, hence the same bits -- with a bias, whose registers are laid out per tile width."""
+    g = torch.Generator().manual_seed(9)
+    monkeypatch.setenv("B200_TC_PAIR", "0")
+    for (Mr, K, N) in [(300, 96, 520), (1024, 128, 768), (130, 64, 200)]:
+        a = torch.randint(-8, 9, (Mr, K), generator=g).float().cuda()
+        b = torch.randint(-8, 9, (K, N), generator=g).float().cuda()
+        bias = torch.randint(-8, 9, (N,), generator=g).float().cuda()
+        want = (a.double() @ b.double() + bias.double()).float()
+        monkeypatch.setenv("B200_TC_BN", bn)
+        got = fq.ops.fq_matmul(a, b, bias=bias)
+        assert fq.ops.last_path() == "tcgen05"
+        assert torch.equal(got, want), (Mr, K, N, bn)
+
+
 def test_fq_gemm_tc_offgrid_falls_back_on_device(fq):
     g = torch.Generator().manual_seed(4)
     a = torch.randn(70, 96, generator=g).cuda()            # full fp32 mantissas: not exact in bf16
