@@ -315,36 +315,40 @@ __global__ void __launch_bounds__(256) c8_correct_kernel(C8CorrectArgs a)
             }
         }
     }
-    // (rare B) x (every row that is not an A escape)
+    // (rare B) x (every row that is not an A escape).  The bulk of the pass: 32-bit index arithmetic (rows < 2^31 is a
+    // condition of the variant), eight row chunks per item, the row pointer formed once per item.
+    constexpr int U2 = 8;
     const unsigned nb = min(nbr, a.brare_cap);
-    const uint32_t mch = (uint32_t)((a.Mrows + 32 * U - 1) / (32 * U));
+    const uint32_t mrows = (uint32_t)a.Mrows;
+    const uint32_t mch = (mrows + 32 * U2 - 1) / (32 * U2);
     const int64_t items = (int64_t)nb * mch;
+    const uint32_t mshift = (uint32_t)(a.M + 1);
     for (int64_t it = warp; it < items; it += nwarps) {
         const uint32_t e = items < ((int64_t)1 << 32) ? (uint32_t)it / mch : (uint32_t)(it / mch);
-        const uint32_t ch = (uint32_t)(it - (int64_t)e * mch);
+        const uint32_t m0 = (uint32_t)(it - (int64_t)e * mch) * (32 * U2) + (uint32_t)lane;
         const unsigned long long ent = a.brare_list[e];
-        const int64_t n = (int64_t)(ent & 0xFFFFFFFFull), k = (int64_t)(ent >> 32);
-        const uint32_t bw = __ldg(a.Bw + k * a.Npad + n);
-        uint32_t aw[U];
+        const uint32_t n = (uint32_t)ent, k = (uint32_t)(ent >> 32);
+        const uint32_t bw = __ldg(a.Bw + (int64_t)k * a.Npad + n);
+        const uint32_t* arow = a.Aw + (int64_t)k * a.Mpad;
+        uint32_t aw[U2];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {   // issued together with the B word: one latency, not two
-            const int64_t m = ((int64_t)ch * U + u) * 32 + lane;
-            aw[u] = m < a.Mrows ? __ldg(a.Aw + k * a.Mpad + m) : a.zero_word;
-        }
-        if (tmaxA + (int)((bw & 0xFFFFu) >> (a.M + 1)) <= R8) continue;   // no row reaches beyond the int8 rows with this element
+        for (int u = 0; u < U2; ++u)    // issued together with the B word: one latency, not two
+            aw[u] = (m0 + 32u * u < mrows) ? __ldg(arow + m0 + 32u * u) : a.zero_word;
         const uint32_t o16 = bw & 0xFFFFu;
-        const int tB = (int)(o16 >> (a.M + 1));
+        const int tB = (int)(o16 >> mshift);
+        if (tmaxA + tB <= R8) continue;                      // no row reaches beyond the int8 rows with this element
+        const int lo = R8 - tB;                              // rows that matter: lo < tA_idx <= thrA
         const int sg = ((int)bw >> 30) | 1;
+        int* dcol = a.D + n;
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
+        for (int u = 0; u < U2; ++u) {
             if (aw[u] == a.zero_word) continue;
-            const uint32_t x = aw[u] >> (a.M + 1);
+            const uint32_t x = aw[u] >> mshift;
             const int tA = (int)(x - (uint32_t)a.NT * __umulhi(x, a.nt_magic));
-            if (tA > thrA || tA + tB <= R8) continue;                              // an escape (done above) / int8 rows only
+            if (tA > thrA || tA <= lo) continue;             // an escape (done above) / int8 rows only
             const float v = __uint_as_float((uint32_t)__ldg(a.lut16 + ((aw[u] + o16) >> 1)) << 16);
             if (c8_fits(v)) continue;
-            const int64_t m = ((int64_t)ch * U + u) * 32 + lane;
-            atomicAdd(a.D + m * a.N + n, __float2int_rn(v) * sg);
+            atomicAdd(dcol + (int64_t)(m0 + 32u * u) * a.N, __float2int_rn(v) * sg);
         }
     }
 }
