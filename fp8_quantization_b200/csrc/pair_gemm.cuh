@@ -95,8 +95,13 @@ __global__ void __launch_bounds__(256) pair_gemm_kernel(ASrc A, BSrc B, float* _
     __shared__ __align__(16) float As[PG_KT][PG_LD];
     __shared__ __align__(16) float Bs[PG_KT][PG_LD];
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-    const int64_t m0 = (int64_t)blockIdx.x * PG_BM, n0 = (int64_t)blockIdx.y * PG_BN;
     op.begin();
+    // 1-D grid, tiles dealt round-robin (column tile fastest): the gated launches that accompany every table GEMM and
+    // exit at once stay small however large the problem is
+    const int64_t tiles_n = (N + PG_BN - 1) / PG_BN, tiles = ((Mrows + PG_BM - 1) / PG_BM) * tiles_n;
+  for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int64_t m0 = (tile / tiles_n) * PG_BM, n0 = (tile % tiles_n) * PG_BN;
+    __syncthreads();   // the previous tile's readers of As / Bs are done
     typename Op::Col col[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -161,11 +166,14 @@ __global__ void __launch_bounds__(256) pair_gemm_kernel(ASrc A, BSrc B, float* _
             if (n < N) ep.store(C, ldc, m, n, op.finish(acc[i][j], col[j]));
         }
     }
+  }   // tile loop
 }
 
+// 1-D grid of at most 8 CTAs per SM (148 SMs assumed for the cap; the kernel loops over its tiles)
 inline dim3 pair_gemm_grid(int64_t Mrows, int64_t N)
 {
-    return dim3((unsigned)((Mrows + PG_BM - 1) / PG_BM), (unsigned)((N + PG_BN - 1) / PG_BN));
+    const int64_t tiles = ((Mrows + PG_BM - 1) / PG_BM) * ((N + PG_BN - 1) / PG_BN);
+    return dim3((unsigned)(tiles < 1 ? 1 : (tiles > 148 * 8 ? 148 * 8 : tiles)));
 }
 
 }  // namespace b200
