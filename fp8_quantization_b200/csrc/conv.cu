@@ -51,13 +51,20 @@ __global__ void __launch_bounds__(256) approx_dw_kernel(DwArgs d, const int* __r
     if (gate && ((*gate != 0) != (gate_run_if_nonzero != 0))) return;
     __shared__ float tile[32][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int64_t m = (int64_t)blockIdx.x * 32 + tx;
     const FmtParam pA = make_param(d.cfg.E, d.cfg.M, d.bias.A(), d.cfg.quirk);
     const FmtParam pR = make_param(d.cfg.E, d.cfg.M, d.bias.R(), d.cfg.quirk);
+    // 1-D grid over the (32 rows x 32 groups) tiles, group tile fastest: the gated launch behind every table-driven
+    // depthwise call exits at once and must not cost tens of thousands of CTAs
+    const int64_t gtiles = (d.groups + 31) / 32, tiles = ((d.rows + 31) / 32) * gtiles;
+  for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const int64_t bx = t / gtiles;
+    const int by = (int)(t - bx * gtiles);
+    const int64_t m = bx * 32 + tx;
+    __syncthreads();   // the previous tile's readers of tile[] are done
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int gl = ty + 8 * i;
-        const int g = blockIdx.y * 32 + gl;
+        const int g = by * 32 + gl;
         float acc = 0.0f;
         if (g < d.groups && m < d.rows) {
             const FmtParam pB = make_param(d.cfg.E, d.cfg.M, d.bias.B(g), d.cfg.quirk);
@@ -77,10 +84,11 @@ __global__ void __launch_bounds__(256) approx_dw_kernel(DwArgs d, const int* __r
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int ml = ty + 8 * i;
-        const int64_t mm = (int64_t)blockIdx.x * 32 + ml;
-        const int g = blockIdx.y * 32 + tx;
+        const int64_t mm = bx * 32 + ml;
+        const int g = by * 32 + tx;
         if (mm < d.rows && g < d.groups) d.ep.store(d.out, d.groups, mm, g, tile[tx][ml]);
     }
+  }   // tile loop
 }
 
 // ---- single-column groups, table driven -----------------------------------------------------------
@@ -717,7 +725,7 @@ static int approx_conv2d_impl(const float* x, const float* w, float* out, const 
         a.cfg.sim_ofuf = p->sim_hw_add_OFUF != 0; a.cfg.of_opt = p->with_OF_opt != 0; a.cfg.uf_opt = p->with_UF_opt != 0;
         a.T = dev_table;
     }
-    const dim3 grid((unsigned)ceil_div(d.rows, 32), (unsigned)ceil_div(g->groups, 32));
+    const dim3 grid((unsigned)std::max<int64_t>(1, std::min<int64_t>(ceil_div(d.rows, 32) * ceil_div(g->groups, 32), (int64_t)148 * 8)));
     cudaStream_t st = (cudaStream_t)stream;
     // table path: main mode only; needs 256 B of workspace for the device-side fallback flag
     const bool lut_mode = !v5 && !p->force_generic && p->with_s2nn2s_opt && p->quant_btw_mult_accu && !p->golden_clip_OF &&
