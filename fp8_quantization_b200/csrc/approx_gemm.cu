@@ -1279,11 +1279,22 @@ static size_t prepared_b_bytes(int64_t K, int64_t N)
     return 256 + (size_t)Kpad * Npad * 4 + (size_t)brare_cap(Npad, Kpad) * 8;
 }
 // flag words of the B passes: [0] off-grid (OR-ed), [5] largest tB_idx, [12] largest non-rare tB_idx, [13] rare count
+// restore (64 threads) also CLEARS the rest of the flag block: the call that reuses a prepared B needs no memset node
 __global__ void b_meta_kernel(int* __restrict__ flag, int* __restrict__ meta, int save)
 {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    if (save) { meta[0] = flag[0]; meta[1] = flag[5]; meta[2] = flag[12]; meta[3] = flag[13]; }
-    else      { if (meta[0]) flag[0] = 1; flag[5] = meta[1]; flag[12] = meta[2]; flag[13] = meta[3]; }
+    if (blockIdx.x != 0) return;
+    if (save) {
+        if (threadIdx.x == 0) { meta[0] = flag[0]; meta[1] = flag[5]; meta[2] = flag[12]; meta[3] = flag[13]; }
+        return;
+    }
+    const int t = threadIdx.x;
+    if (t >= 64) return;            // kFlagBytes / 4 words
+    int v = 0;
+    if (t == 0) v = meta[0] != 0;
+    else if (t == 5) v = meta[1];
+    else if (t == 12) v = meta[2];
+    else if (t == 13) v = meta[3];
+    flag[t] = v;
 }
 
 struct C8Src {
@@ -1343,7 +1354,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
     pa.zero_count = geom.v5 ? nullptr : reinterpret_cast<unsigned long long*>(flag + 2);
     // B first: the A pass of the byte-cell variant compares against the largest tB_idx
     if (prep.base && prep.ready) {
-        b_meta_kernel<<<1, 32, 0, st>>>(flag, reinterpret_cast<int*>(prep.base), 0);
+        b_meta_kernel<<<1, 64, 0, st>>>(flag, reinterpret_cast<int*>(prep.base), 0);   // clears the flag block too
         B200_LAUNCH_CHECK("b_meta_kernel(restore)");
     } else {
         PredecodeArgs pb = pa;
@@ -1691,7 +1702,8 @@ int b200::approx_gemm_impl(const ASrc& A, const float* B, int64_t sb_k, int64_t 
     int* flag = reinterpret_cast<int*>(workspace);
     uint32_t* Aw = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(workspace) + kFlagBytes);
     uint32_t* Bw = Aw + (size_t)Kpad * Mpad;
-    B200_CUDA_TRY(cudaMemsetAsync(flag, 0, kFlagClearBytes, st));
+    if (!(p->prepared_b && p->prepared_b_ready))   // (the restore kernel of a prepared B clears the block itself)
+        B200_CUDA_TRY(cudaMemsetAsync(flag, 0, kFlagClearBytes, st));
     C8Src c8src;
     if (lut->d_lut8 && !p->force_table16) {
         c8src.lut8 = lut->d_lut8; c8src.lut8_bytes = lut->lut8_bytes; c8src.bad = lut->d_bad;
