@@ -217,6 +217,8 @@ struct C8CorrectArgs {
     const int* c8_bad;
     const int* tb_eff;         // largest non-rare tB_idx
     const int* tmax;           // [0] largest tA_idx, [1] largest tB_idx
+    int64_t esc_limit;         // the byte-cell gate (c8_selected, lut_gemm.cuh): above this many escapes nobody reads D
+    int Kpad, t_bias;
     int NT, M, sidx;
     uint32_t nt_magic, zero_word;
     int* D;
@@ -278,6 +280,13 @@ __global__ void __launch_bounds__(256) c8_correct_kernel(C8CorrectArgs a)
     const int thrA = R8 - *a.tb_eff;
     const int tmaxA = a.tmax[0];
     if (tmaxA + a.tmax[1] <= R8) return;   // every pair lies in an all-int8 row: nothing was dropped
+    {   // the gate of the byte-cell GEMM, evaluated here too: when it is closed the 16-bit kernel computes and D is never read
+        unsigned tot = 0, ovf = nbr > a.brare_cap;
+        for (int l = 0; l < kEscLists; ++l) { tot += s_cnt[l]; ovf |= (s_cnt[l] > a.esc_cap); }
+        const int dl = tmaxA + a.tmax[1] - a.t_bias + a.M + 1;
+        const int lgK = 32 - __clz((a.Kpad > 2 ? a.Kpad : 2) - 1);
+        if (ovf || (int64_t)tot > a.esc_limit || dl + lgK > 24) return;
+    }
     // Work items are (list entry, 128-wide chunk of the other dimension), dealt round-robin to the warps: thousands of
     // short independent items, each with its four plane loads in flight together (the pass is latency bound).
     constexpr int U = 4;
@@ -1435,6 +1444,7 @@ static int run_lut_gemm(const ASrc& A, const float* B, int64_t sb_k, int64_t sb_
         ca.Aw = Aw; ca.Bw = Bw; ca.Mpad = Mpad; ca.Npad = Npad; ca.N = N; ca.Mrows = Mrows; ca.lut16 = d_lut; ca.c8_bad = c8src.bad;
         ca.tb_eff = flag + 12; ca.tmax = flag + 4; ca.NT = geom.NT; ca.M = M; ca.sidx = geom.sidx; ca.nt_magic = nt_magic;
         ca.zero_word = 2u * (uint32_t)geom.zeroA_off; ca.D = c8_D;
+        ca.esc_limit = std::min<int64_t>((int64_t)pa.esc_cap * kEscLists, Mrows * K / 1024); ca.Kpad = (int)Kpad; ca.t_bias = geom.RA + M + 2;
         c8_correct_kernel<<<(unsigned)(8 * sms), 256, 0, st>>>(ca);
         B200_LAUNCH_CHECK("c8_correct_kernel");
     }
